@@ -1,0 +1,142 @@
+/* include/vdb.h — C ABI of libvectordb.so, the B200 (sm_100a) implementation of VectorDatabase's batched
+ * query path. This is the drop-in boundary: everything the reference's JNI bridge
+ * (/root/reference/native/bridge/VectorDBJNI.cpp:39-200) does against its C++ `vectordb::VectorIndex`
+ * (/root/reference/native/index/VectorIndex.h:9-35) is expressed here with plain pointers and sizes.
+ * INTEGRATION.md shows the JNI / ctypes stubs that bind it.
+ *
+ * Conventions
+ *   - every call returns an int status (VDB_OK == 0); nothing throws across the boundary (the reference lets
+ *     C++ exceptions cross JNI frames: VectorDBJNI.cpp:132-159). vdb_last_error() gives the message of the
+ *     last failure on the calling thread.
+ *   - all pointers are caller-owned and borrowed for the duration of the call (reference: GetDirectBufferAddress
+ *     / Get..ArrayElements with JNI_ABORT, VectorDBJNI.cpp:136-156,170-198).
+ *   - result slots that hold no hit are filled with id = -1, distance = +inf (the reference forgets to:
+ *     HNSWIndex.cpp:557-566 vs jni/NativeIndex.java:222).
+ *   - there is NO CPU fallback: if no CUDA device / wrong architecture is present, vdb_create fails.
+ */
+#ifndef VDB_H_
+#define VDB_H_
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VDB_OK 0
+#define VDB_ERR_INVALID 1   /* bad argument / state (IllegalArgumentException on the Java side) */
+#define VDB_ERR_CUDA 2      /* CUDA runtime failure, or no sm_100 device */
+#define VDB_ERR_FULL 3      /* max_elements reached (VectorStore.cpp:40-43 throws; Java returns false) */
+#define VDB_ERR_UNTRAINED 4 /* PQ index used before train (PQIndex.cpp:124-126 throws) */
+#define VDB_ERR_IO 5
+
+typedef struct vdb_index vdb_index;
+
+/* which reference class the index reproduces */
+enum {
+    VDB_INDEX_FLAT = 0,    /* brute force (ground truth of RecallOptimizationTest.java:151-164; BatchDistance.cpp:121-147) */
+    VDB_INDEX_PQ = 1,      /* native PQIndex: LUT + ADC scan + (dist,id) top-k   (native/index/PQIndex.cpp:146-213) */
+    VDB_INDEX_HNSW = 2,    /* Java HnswIndex: cosine on normalised vectors       (index/HnswIndex.java) */
+    VDB_INDEX_HNSW_PQ = 3  /* Java HnswPqIndex: sq-L2, PQ upper layers, exact layer 0 + rerank (index/HnswPqIndex.java) */
+};
+enum { VDB_METRIC_SQL2 = 0, VDB_METRIC_COSINE = 1 };
+/* fp32 reduction order of the reference implementation being reproduced */
+enum {
+    VDB_ARITH_JAVA_SEQ = 0,    /* sequential, mul then add (HnswPqIndex.java:741-750, :343-350) */
+    VDB_ARITH_NATIVE_AVX2 = 1  /* 8-lane FMA + horizontal tree (DistanceAVX2.cpp:9-33 / :59-89) */
+};
+/* k-means flavour for vdb_train (oracle: orc_pq_train) */
+enum {
+    VDB_TRAIN_JAVA = 0,          /* HnswPqIndex.java:194-338  k-means++ with java.util.Random(42+m), 25 Lloyd passes */
+    VDB_TRAIN_NATIVE_HNSWPQ = 1, /* HNSWPQIndex.cpp:127-244   k-means++ with std::mt19937(42+m), stop when stable   */
+    VDB_TRAIN_NATIVE_PQ = 2      /* PQIndex.cpp:29-105        256 uniform draws with std::mt19937(42+m)             */
+};
+
+typedef struct vdb_config {
+    int32_t dim;
+    int32_t max_elements;
+    int32_t index_type;      /* VDB_INDEX_* */
+    int32_t metric;          /* VDB_METRIC_*; forced by index_type for HNSW (cosine) and HNSW_PQ / PQ (sq-L2) */
+    int32_t arith;           /* VDB_ARITH_*; default: JAVA_SEQ for HNSW*, NATIVE_AVX2 for PQ */
+    int32_t hnsw_m;          /* 32  (HnswPqIndex.java:27, HnswIndex.java:21) */
+    int32_t ef_construction; /* 64 / 400 */
+    int32_t ef_search;       /* 64 / 400 */
+    int32_t pq_m;            /* subspaces; 0 = CompressionConfig.recommendedConfig(dim) (CompressionConfig.java:114-130) */
+    int32_t pq_bits;         /* only 8 is supported (256 centroids, HnswPqIndex.java:86) */
+    int32_t pq_iters;        /* 25 */
+    int32_t train_flavour;   /* VDB_TRAIN_* */
+    int32_t rerank;          /* PQ index: exact re-score of the best `rerank` ADC candidates (0 = none, as PQIndex.cpp) */
+    int32_t device;          /* CUDA ordinal */
+    int32_t id_offset;       /* multi-GPU id-range sharding: this shard holds global rows [id_offset, id_offset+n) */
+    int32_t reserved0;
+    uint64_t level_seed;     /* seeded stand-in for ThreadLocalRandom level draws (HnswPqIndex.java:752-759) */
+} vdb_config;
+
+typedef struct vdb_stats {
+    int64_t queries;
+    int64_t dist_evals;      /* V: exact distances computed during traversal */
+    int64_t expansions;      /* E: nodes expanded on layer 0 */
+    int64_t adc_rows;        /* PQ code rows scanned */
+    float last_kernel_ms;    /* device time of the dominant kernel of the last search (CUDA events) */
+    float last_total_ms;     /* device time of the whole last search */
+} vdb_stats;
+
+const char* vdb_last_error(void);
+const char* vdb_version(void);
+/* fills *cfg with the defaults of the given reference class */
+int vdb_default_config(int32_t index_type, int32_t dim, int32_t max_elements, vdb_config* cfg);
+
+/* nativeCreateHNSW / nativeCreatePQ (VectorDBJNI.cpp:39-65) — one constructor for all index types */
+int vdb_create(const vdb_config* cfg, vdb_index** out);
+/* nativeDestroy (VectorDBJNI.cpp:161-164) */
+int vdb_destroy(vdb_index* idx);
+/* nativeAdd / nativeAddBatch (VectorDBJNI.cpp:132-139,167-182): ids[n] (NULL = 0..n-1 continuing), vecs[n][dim] */
+int vdb_add_batch(vdb_index* idx, const int32_t* ids, const float* vecs, int64_t n);
+/* NativePqIndex.nativeTrain (VectorDBJNI.cpp:67-75): k-means on samples[n][dim] on the GPU */
+int vdb_train(vdb_index* idx, const float* samples, int64_t n);
+/* VectorIndex.buildIndex / VectorDatabase.rebuildIndex (HnswPqIndex.java:676-718): train if needed,
+ * re-encode, rebuild the graph in ascending id order, upload */
+int vdb_build(vdb_index* idx);
+/* nativeSearch / nativeSearchBatch (VectorDBJNI.cpp:141-159,184-200): HOST buffers; queries[nq][dim],
+ * out_ids[nq][k], out_dists[nq][k] */
+int vdb_search_batch(vdb_index* idx, const float* queries, int64_t nq, int32_t k, int32_t* out_ids, float* out_dists);
+/* same with DEVICE buffers on `stream` (a cudaStream_t; NULL = the index's own stream): no host copies */
+int vdb_search_batch_device(vdb_index* idx, const float* d_queries, int64_t nq, int32_t k, int32_t* d_ids,
+                            float* d_dists, void* stream);
+int64_t vdb_size(const vdb_index* idx);
+int vdb_is_trained(const vdb_index* idx);
+int vdb_get_stats(vdb_index* idx, vdb_stats* out);
+
+/* ---- state import/export: "the same persisted graph and codebooks" for parity runs, and save/load
+ *      (every reference save()/load() is an empty TODO: HNSWIndex.cpp:535-541, HNSWPQIndex.cpp:774-780) ---- */
+int vdb_set_codebooks(vdb_index* idx, const float* codebooks /* [pq_m][256][dim/pq_m] */);
+int vdb_get_codebooks(vdb_index* idx, float* out);
+int vdb_get_codes(vdb_index* idx, uint8_t* out /* [n][pq_m] */);
+int vdb_set_codes(vdb_index* idx, const uint8_t* codes /* [n][pq_m] */);
+/* levels[n]; adj[max_level][n][hnsw_m] (-1 padded, node rows in insertion order); entry = node row */
+int vdb_set_graph(vdb_index* idx, const int32_t* levels, const int32_t* adj, int32_t max_level, int32_t entry);
+int vdb_get_graph(vdb_index* idx, int32_t* levels, int32_t* adj, int32_t* entry);
+int32_t vdb_max_level(const vdb_index* idx);
+int vdb_save(vdb_index* idx, const char* path);
+int vdb_load(vdb_index* idx, const char* path);
+
+/* ---- device-side building blocks (benchmarks, multi-GPU merge, parity tests of single kernels) ---- */
+/* fill rows [row0,row0+n) of the index with the counter-based synthetic generator (seed, (row)*dim+j) directly
+ * in HBM (no PCIe traffic); ids = id_offset+row. Oracle twin: orc_fill_uniform. */
+int vdb_fill_synthetic(vdb_index* idx, uint64_t seed, int64_t n);
+/* encode all stored rows with the current codebooks on the GPU (PQ / HNSW_PQ) */
+int vdb_encode_all(vdb_index* idx);
+/* LUT build only: d_lut[nq][pq_m][256] */
+int vdb_pq_lut_device(vdb_index* idx, const float* d_queries, int64_t nq, float* d_lut, void* stream);
+/* ADC distances of every stored row for ONE query's LUT: d_out[n] (test hook, order R3) */
+int vdb_adc_scan_device(vdb_index* idx, const float* d_lut, float* d_out, void* stream);
+/* merge g per-shard result lists [g][nq][k] (dist,id) into [nq][k] ordered by (dist,id) */
+int vdb_merge_topk_device(const float* d_dists, const int32_t* d_ids, int32_t g, int64_t nq, int32_t k,
+                          float* d_out_dists, int32_t* d_out_ids, void* stream);
+/* standalone exact distance, for known-answer tests: order = VDB_ARITH_*; metric as above */
+int vdb_distance_device(const float* d_a, const float* d_b, int64_t n, int32_t dim, int32_t metric, int32_t order,
+                        float* d_out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VDB_H_ */

@@ -1,0 +1,151 @@
+// host_graph.cpp — see host_graph.h. Product code (not the oracle): own implementation of the Java insert algorithm.
+#include "host_graph.h"
+
+#include <algorithm>
+#include <cmath>
+#include <queue>
+
+namespace {
+inline uint64_t mix64(uint64_t z) {
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+// build-time distances need no particular summation order: 8 independent accumulators vectorise well
+inline float l2sq_fast(const float* a, const float* b, int d) {
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    int i = 0;
+    for (; i + 8 <= d; i += 8)
+        for (int j = 0; j < 8; j++) { float t = a[i + j] - b[i + j]; acc[j] += t * t; }
+    float s = ((acc[0] + acc[4]) + (acc[1] + acc[5])) + ((acc[2] + acc[6]) + (acc[3] + acc[7]));
+    for (; i < d; i++) { float t = a[i] - b[i]; s += t * t; }
+    return s;
+}
+inline float dot_fast(const float* a, const float* b, int d) {
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    int i = 0;
+    for (; i + 8 <= d; i += 8)
+        for (int j = 0; j < 8; j++) acc[j] += a[i + j] * b[i + j];
+    float s = ((acc[0] + acc[4]) + (acc[1] + acc[5])) + ((acc[2] + acc[6]) + (acc[3] + acc[7]));
+    for (; i < d; i++) s += a[i] * b[i];
+    return s;
+}
+struct Nb { float d; int idx; };
+struct NbLess { bool operator()(const Nb& a, const Nb& b) const { return a.d < b.d || (a.d == b.d && a.idx < b.idx); } };
+struct NbGreater { bool operator()(const Nb& a, const Nb& b) const { return NbLess()(b, a); } };
+}  // namespace
+
+void HostGraph::init(int dim_, int M_, int max_elements, int metric_, uint64_t seed) {
+    dim = dim_; M = M_; metric = metric_; level_seed = seed; level_ctr = 0;
+    // maxLevel = (int)(ln(maxElements)/ln(m)) + 1   (HnswPqIndex.java:89, HnswIndex.java:49)
+    max_level = (int)(std::log((double)max_elements) / std::log((double)M)) + 1;
+    if (max_level < 1) max_level = 1;
+    adj.assign(max_level, {}); deg.assign(max_level, {});
+    clear();
+}
+void HostGraph::clear() {
+    level.clear(); entry = -1; level_ctr = 0;
+    for (auto& a : adj) a.clear();
+    for (auto& d : deg) d.clear();
+}
+// seeded stand-in for ThreadLocalRandom (HnswPqIndex.java:752-759): P(level >= l) = e^-l, capped at max_level-1
+int HostGraph::draw_level() {
+    int lv = 0;
+    const double p = 1.0 / M_E;
+    for (;;) {
+        double u = (double)(mix64(level_seed * 0x9E3779B97F4A7C15ull + (level_ctr++)) >> 11) * (1.0 / 9007199254740992.0);
+        if (u < p && lv < max_level - 1) lv++; else break;
+    }
+    return lv;
+}
+
+void HostGraph::import_graph(const int32_t* levels, const int32_t* adj_in, int n, int entry_) {
+    clear();
+    level.assign(levels, levels + n);
+    for (int l = 0; l < max_level; l++) {
+        adj[l].assign(adj_in + (size_t)l * n * M, adj_in + (size_t)(l + 1) * n * M);
+        deg[l].resize(n);
+        for (int i = 0; i < n; i++) {
+            int c = 0;
+            while (c < M && adj[l][(size_t)i * M + c] >= 0) c++;
+            deg[l][i] = (uint8_t)c;
+        }
+    }
+    entry = entry_;
+}
+
+void HostGraph::insert(int index, int ef, int variant) {
+    auto dist = [&](int a, int b) -> float {
+        const float* x = vecs + (size_t)a * dim; const float* y = vecs + (size_t)b * dim;
+        if (metric == 0) return l2sq_fast(x, y, dim);
+        return 1.0f - dot_fast(x, y, dim) / (norms[a] * norms[b]);
+    };
+    const int lv = draw_level();
+    level.push_back(lv);
+    for (int l = 0; l < max_level; l++) { adj[l].resize((size_t)(index + 1) * M, -1); deg[l].push_back(0); }
+    if ((int)visit.size() <= index) visit.resize(std::max<size_t>(1024, (size_t)(index + 1) * 2), 0);
+    if (entry < 0) { entry = index; return; }
+
+    int cur = entry;
+    // greedy descent above the node's level: first improving neighbour wins (HnswPqIndex.java:761-792)
+    for (int l = max_level - 1; l > lv; l--) {
+        float curd = dist(cur, index);
+        bool changed = true;
+        while (changed) {
+            changed = false;
+            const int c = deg[l][cur];
+            for (int j = 0; j < c; j++) {
+                int nb = adj[l][(size_t)cur * M + j];
+                float d = dist(nb, index);
+                if (d < curd) { curd = d; cur = nb; changed = true; break; }
+            }
+        }
+    }
+    std::vector<Nb> found, tmp;
+    std::vector<int> sel;
+    for (int l = std::min(lv, max_level - 1); l >= 0; l--) {
+        // searchLayer with the reference's stale-furthest behaviour (HnswPqIndex.java:829-895 / HnswIndex.java:557-644)
+        std::priority_queue<Nb, std::vector<Nb>, NbLess> results;
+        std::priority_queue<Nb, std::vector<Nb>, NbGreater> cands;
+        if (++epoch == 0) { std::fill(visit.begin(), visit.end(), 0); epoch = 1; }
+        float d0 = dist(cur, index);
+        results.push({d0, cur}); cands.push({d0, cur});
+        visit[cur] = epoch;
+        float furthest = d0;
+        while (!cands.empty()) {
+            Nb c = cands.top(); cands.pop();
+            if (variant == 2) { if (c.d > furthest) break; }
+            else if (c.d > furthest && (int)results.size() >= ef) break;   // `continue` in Java; equivalent (min-heap)
+            const int cn = deg[l][c.idx];
+            for (int j = 0; j < cn; j++) {
+                int nb = adj[l][(size_t)c.idx * M + j];
+                if (visit[nb] == epoch) continue;
+                visit[nb] = epoch;
+                float d = dist(nb, index);
+                if ((int)results.size() < ef || d < furthest) {
+                    cands.push({d, nb}); results.push({d, nb});
+                    if ((int)results.size() > ef) { results.pop(); furthest = results.top().d; }
+                }
+            }
+        }
+        found.resize(results.size());
+        for (int i = (int)results.size() - 1; i >= 0; i--) { found[i] = results.top(); results.pop(); }
+        // selectNeighbors: the M nearest (HnswPqIndex.java:1043-1064); `found` is already ascending
+        sel.clear();
+        for (int i = 0; i < (int)found.size() && i < M; i++) sel.push_back(found[i].idx);
+        for (int j = 0; j < (int)sel.size(); j++) adj[l][(size_t)index * M + j] = sel[j];
+        deg[l][index] = (uint8_t)sel.size();
+        for (int nb : sel) {
+            int c = deg[l][nb];
+            if (c < M) { adj[l][(size_t)nb * M + c] = index; deg[l][nb] = (uint8_t)(c + 1); continue; }
+            // M+1 connections: keep the M nearest to nb, stable in list order (HnswPqIndex.java:512-523)
+            tmp.clear();
+            for (int t = 0; t < c; t++) { int nn = adj[l][(size_t)nb * M + t]; tmp.push_back({dist(nb, nn), nn}); }
+            tmp.push_back({dist(nb, index), index});
+            std::stable_sort(tmp.begin(), tmp.end(), [](const Nb& a, const Nb& b) { return a.d < b.d; });
+            for (int t = 0; t < M; t++) adj[l][(size_t)nb * M + t] = tmp[t].idx;
+        }
+        cur = sel.empty() ? index : sel[0];
+    }
+    if (lv > level[entry]) entry = index;
+}

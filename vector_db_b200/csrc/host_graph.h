@@ -1,0 +1,28 @@
+// host_graph.h — host-side HNSW graph construction ("stays on CPU in the first build").
+// Follows the insert semantics of the Java classes (HnswPqIndex.java:391-539, HnswIndex.java:139-248): exact distances,
+// M nearest neighbours (no diversity heuristic), back-links pruned to the M nearest. The query path never runs here.
+#pragma once
+#include <cstdint>
+#include <vector>
+
+struct HostGraph {
+    int dim = 0, M = 32, max_level = 1, metric = 0;
+    uint64_t level_seed = 0, level_ctr = 0;
+    int entry = -1;
+    const float* vecs = nullptr;     // [n][dim] (normalised rows for cosine), owned by the index
+    const float* norms = nullptr;    // [n] for cosine
+    std::vector<int32_t> level;      // [n]
+    std::vector<std::vector<int32_t>> adj;   // [max_level] flat [n][M], -1 padded
+    std::vector<std::vector<uint8_t>> deg;   // [max_level][n]
+    // scratch
+    std::vector<uint32_t> visit; uint32_t epoch = 0;
+
+    void init(int dim_, int M_, int max_elements, int metric_, uint64_t seed);
+    void clear();
+    int size() const { return (int)level.size(); }
+    int draw_level();
+    // insert row `index` (must equal size()); ef = construction beam; variant 1 = HnswPqIndex.searchLayer, 2 = HnswIndex.searchLayer
+    void insert(int index, int ef, int variant);
+    // import an externally built graph: levels[n], adj_in[max_level][n][M]
+    void import_graph(const int32_t* levels, const int32_t* adj_in, int n, int entry_);
+};

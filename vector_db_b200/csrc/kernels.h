@@ -1,0 +1,51 @@
+// kernels.h — launch entry points shared between the kernel translation units and the C-ABI layer.
+#pragma once
+#include "common.cuh"
+
+// pq_kernels.cu
+void launch_pq_lut(const float* d_q, const float* d_cb, int nq, int dim, int M, int arith, float* d_lut, cudaStream_t st);
+void launch_adc_scan_topr(const uint8_t* d_codes, int64_t n, int M, const float* d_luts, int nq, const int32_t* d_ids,
+                          int id_offset, int R, int nchunks, uint64_t* d_keys_tmp, uint32_t* d_rows_tmp, uint64_t* d_keys,
+                          uint32_t* d_rows, cudaStream_t st);
+void launch_merge_keys(const uint64_t* d_in_keys, const uint32_t* d_in_rows, int nq, int nlists, int R, uint64_t* d_keys,
+                       uint32_t* d_rows, cudaStream_t st);
+void launch_keys_to_results(const uint64_t* d_keys, int R, int k, int64_t nq, int32_t* d_ids, float* d_dists, cudaStream_t st);
+void launch_adc_scan_plain(const uint8_t* d_codes, int64_t n, int M, const float* d_lut, float* d_out, cudaStream_t st);
+void launch_rerank(const float* d_base, const int32_t* d_ids, int id_offset, int dim, const float* d_q, int nq,
+                   const uint32_t* d_rows, int R, int order, int k, int32_t* d_out_ids, float* d_out_d, cudaStream_t st);
+int launch_pq_encode(const float* d_x, int64_t n, int dim, int M, const float* d_cb, int arith, uint8_t* d_codes, cudaStream_t st);
+int launch_kmeans_train(const float* d_samples, int n, int dim, int M, int iters, int flavour, float* d_codebooks,
+                        float* d_sub, float* d_mind, int* d_asg, cudaStream_t st);
+void launch_fill_synth(float* d_out, uint64_t seed, int64_t start, int64_t count, cudaStream_t st);
+void launch_normalize_rows(float* d_x, int64_t n, int dim, float* d_norms, cudaStream_t st);
+void launch_distance(const float* d_a, const float* d_b, int64_t n, int dim, int metric, int order, float* d_out, cudaStream_t st);
+
+// hnsw_kernels.cu
+struct HnswSearchParams {
+    const float* base;        // [n][dim]; normalised rows for cosine
+    const float* norms;       // [n] Java norm of the stored row (cosine), else nullptr
+    const int32_t* ids;       // [n] external ids
+    const int32_t* adj;       // [max_level][n][deg], -1 padded
+    const uint8_t* codes;     // [n][pq_m] or nullptr
+    const float* codebooks;   // [pq_m][256][sd] or nullptr
+    const float* queries;     // [nq][dim]
+    int32_t* out_ids;         // [nq][k]
+    float* out_dists;         // [nq][k]
+    unsigned long long* counters;  // [2] dist evals, expansions
+    uint32_t* visited_scratch;     // [grid][ceil(n/32)] when the bitset does not fit in shared memory
+    int n, dim, deg, max_level, entry;
+    int pq_m, trained;
+    int metric;               // 0 sq-L2 (HnswPqIndex), 1 cosine (HnswIndex)
+    int variant;              // 0 searchLayerWithSize, 1 HnswPqIndex.searchLayer, 2 HnswIndex.searchLayer
+    int ef, cap, k, nq;
+    int visited_in_smem;
+};
+int launch_hnsw_search(const HnswSearchParams& p, int grid, cudaStream_t st);
+size_t hnsw_search_smem_bytes(const HnswSearchParams& p);
+
+// flat_kernels.cu
+void launch_flat_search_exact(const float* d_base, const float* d_norms, const int32_t* d_ids, int id_offset, int64_t n, int dim,
+                              const float* d_q, int nq, int k, int metric, int order, int nchunks, uint64_t* d_keys_tmp,
+                              uint32_t* d_rows_tmp, uint64_t* d_keys, uint32_t* d_rows, cudaStream_t st);
+void launch_merge_topk(const float* d_dists, const int32_t* d_ids, int g, int64_t nq, int k, float* d_out_d, int32_t* d_out_ids,
+                       cudaStream_t st);

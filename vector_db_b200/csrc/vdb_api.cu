@@ -1,0 +1,591 @@
+// vdb_api.cu — C ABI (include/vdb.h) over the CUDA kernels. Host orchestration only: every distance, scan, traversal,
+// top-k, encode and k-means step of the query / rebuild path runs in a kernel of this library (no CPU fallback).
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <numeric>
+
+#include "kernels.h"
+#include "vdb_index.h"
+
+static thread_local std::string g_err;
+void vdb_set_error(const std::string& msg) { g_err = msg; }
+#define FAIL(code, msg) do { vdb_set_error(msg); return (code); } while (0)
+
+extern "C" const char* vdb_last_error(void) { return g_err.c_str(); }
+extern "C" const char* vdb_version(void) { return "vector_db_b200 0.1 (sm_100a)"; }
+
+static int recommended_pq_m(int dim) {   // CompressionConfig.recommendedConfig (CompressionConfig.java:114-130)
+    int m = std::max(8, dim / 8);
+    while (dim % m != 0 && m > 1) m--;
+    return m;
+}
+
+extern "C" int vdb_default_config(int32_t index_type, int32_t dim, int32_t max_elements, vdb_config* c) {
+    if (!c || dim <= 0 || max_elements <= 0) FAIL(VDB_ERR_INVALID, "vdb_default_config: bad arguments");
+    std::memset(c, 0, sizeof(*c));
+    c->dim = dim; c->max_elements = max_elements; c->index_type = index_type;
+    c->hnsw_m = 32; c->pq_bits = 8; c->pq_iters = 25; c->level_seed = 1234;
+    switch (index_type) {
+        case VDB_INDEX_FLAT: c->metric = VDB_METRIC_SQL2; c->arith = VDB_ARITH_JAVA_SEQ; break;
+        case VDB_INDEX_PQ:   // PQIndex.h:10-14 defaults M=8; callers normally pass M explicitly
+            c->metric = VDB_METRIC_SQL2; c->arith = VDB_ARITH_NATIVE_AVX2; c->pq_m = 8; c->train_flavour = VDB_TRAIN_NATIVE_PQ; break;
+        case VDB_INDEX_HNSW:   // HnswIndex.java:21-26
+            c->metric = VDB_METRIC_COSINE; c->arith = VDB_ARITH_JAVA_SEQ; c->ef_construction = 400; c->ef_search = 400; break;
+        case VDB_INDEX_HNSW_PQ:   // HnswPqIndex.java:27-32
+            c->metric = VDB_METRIC_SQL2; c->arith = VDB_ARITH_JAVA_SEQ; c->ef_construction = 64; c->ef_search = 64;
+            c->pq_m = recommended_pq_m(dim); c->train_flavour = VDB_TRAIN_JAVA; break;
+        default: FAIL(VDB_ERR_INVALID, "unknown index_type");
+    }
+    return VDB_OK;
+}
+
+extern "C" int vdb_create(const vdb_config* cfg, vdb_index** out) {
+    if (!cfg || !out) FAIL(VDB_ERR_INVALID, "vdb_create: null argument");
+    *out = nullptr;
+    if (cfg->dim <= 0 || cfg->max_elements <= 0) FAIL(VDB_ERR_INVALID, "dim and max_elements must be positive");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) FAIL(VDB_ERR_CUDA, "no CUDA device: libvectordb has no CPU fallback");
+    if (cfg->device < 0 || cfg->device >= ndev) FAIL(VDB_ERR_INVALID, "bad device ordinal");
+    cudaDeviceProp prop;
+    VDB_CUDA(cudaGetDeviceProperties(&prop, cfg->device));
+    if (prop.major != 10) FAIL(VDB_ERR_CUDA, "libvectordb is built for sm_100a (B200) only");
+    VDB_CUDA(cudaSetDevice(cfg->device));
+    vdb_index* x = new vdb_index();
+    x->cfg = *cfg;
+    x->num_sms = prop.multiProcessorCount;
+    vdb_config& c = x->cfg;
+    if (c.hnsw_m <= 0) c.hnsw_m = 32;
+    if (c.pq_iters <= 0) c.pq_iters = 25;
+    if (c.pq_bits == 0) c.pq_bits = 8;
+    const bool uses_pq = c.index_type == VDB_INDEX_PQ || c.index_type == VDB_INDEX_HNSW_PQ;
+    if (uses_pq) {
+        if (c.pq_bits != 8) { delete x; FAIL(VDB_ERR_INVALID, "only pq_bits == 8 is supported"); }
+        if (c.pq_m <= 0) c.pq_m = recommended_pq_m(c.dim);
+        if (c.dim % c.pq_m != 0) {
+            if (c.index_type == VDB_INDEX_PQ) { delete x; FAIL(VDB_ERR_INVALID, "Dimension must be divisible by M"); }  // PQIndex.cpp:19-21
+            c.pq_m = recommended_pq_m(c.dim);
+        }
+        x->pq_m = c.pq_m; x->sd = c.dim / c.pq_m;
+        if (x->sd > 32) { delete x; FAIL(VDB_ERR_INVALID, "sub-dimension > 32 not supported"); }
+    }
+    if (c.index_type == VDB_INDEX_HNSW) c.metric = VDB_METRIC_COSINE;
+    if (uses_pq) c.metric = VDB_METRIC_SQL2;
+    if (c.index_type == VDB_INDEX_HNSW || c.index_type == VDB_INDEX_HNSW_PQ) {
+        if (c.hnsw_m > 64) { delete x; FAIL(VDB_ERR_INVALID, "hnsw_m > 64 not supported"); }
+        if (c.ef_construction <= 0) c.ef_construction = c.index_type == VDB_INDEX_HNSW ? 400 : 64;
+        if (c.ef_search <= 0) c.ef_search = c.index_type == VDB_INDEX_HNSW ? 400 : 64;
+        x->g.init(c.dim, c.hnsw_m, c.max_elements, c.metric, c.level_seed);
+    }
+    if (cudaStreamCreateWithFlags(&x->stream, cudaStreamNonBlocking) != cudaSuccess) { delete x; FAIL(VDB_ERR_CUDA, "stream create failed"); }
+    cudaEventCreate(&x->ev_total0); cudaEventCreate(&x->ev_total1); cudaEventCreate(&x->ev_k0); cudaEventCreate(&x->ev_k1);
+    if (x->d_counters.ensure(2, 0, x->stream) != VDB_OK) { delete x; return VDB_ERR_CUDA; }
+    cudaMemsetAsync(x->d_counters.p, 0, 2 * sizeof(unsigned long long), x->stream);
+    *out = x;
+    return VDB_OK;
+}
+
+extern "C" int vdb_destroy(vdb_index* x) {
+    if (!x) return VDB_OK;
+    cudaSetDevice(x->cfg.device);
+    if (x->stream) cudaStreamSynchronize(x->stream);
+    x->d_base.release(); x->d_norms.release(); x->d_cb.release(); x->d_ids.release(); x->d_adj.release(); x->d_codes.release();
+    x->d_q.release(); x->d_out_d.release(); x->d_lut.release(); x->d_out_ids.release(); x->d_keys.release(); x->d_keys_tmp.release();
+    x->d_rows.release(); x->d_rows_tmp.release(); x->d_visited.release(); x->d_counters.release();
+    x->d_train.release(); x->d_sub.release(); x->d_mind.release(); x->d_asg.release();
+    x->p_q.release(); x->p_d.release(); x->p_ids.release();
+    if (x->ev_total0) { cudaEventDestroy(x->ev_total0); cudaEventDestroy(x->ev_total1); cudaEventDestroy(x->ev_k0); cudaEventDestroy(x->ev_k1); }
+    if (x->stream) cudaStreamDestroy(x->stream);
+    delete x;
+    return VDB_OK;
+}
+
+extern "C" int64_t vdb_size(const vdb_index* x) { return x ? x->n : -1; }
+extern "C" int vdb_is_trained(const vdb_index* x) { return x && x->trained ? 1 : 0; }
+extern "C" int32_t vdb_max_level(const vdb_index* x) { return x ? x->g.max_level : 0; }
+
+// ---- device store upkeep --------------------------------------------------------------------------------------
+static int upload_rows(vdb_index* x) {
+    // copy host rows [n_dev, n) to the device (cosine rows were normalised on the device at add time)
+    if (x->device_only || x->n_dev >= x->n) return VDB_OK;
+    const int dim = x->cfg.dim;
+    VDB_TRY(x->d_base.ensure((size_t)std::max<int64_t>(x->n, x->n_dev) * dim, (size_t)x->n_dev * dim, x->stream));
+    VDB_TRY(x->d_ids.ensure((size_t)x->n, (size_t)x->n_dev, x->stream));
+    const int64_t cnt = x->n - x->n_dev;
+    VDB_CUDA(cudaMemcpyAsync(x->d_base.p + (size_t)x->n_dev * dim, x->h_vecs.data() + (size_t)x->n_dev * dim, (size_t)cnt * dim * 4,
+                             cudaMemcpyHostToDevice, x->stream));
+    VDB_CUDA(cudaMemcpyAsync(x->d_ids.p + x->n_dev, x->h_ids.data() + x->n_dev, (size_t)cnt * 4, cudaMemcpyHostToDevice, x->stream));
+    if (x->cfg.metric == VDB_METRIC_COSINE) {
+        VDB_TRY(x->d_norms.ensure((size_t)x->n, (size_t)x->n_dev, x->stream));
+        VDB_CUDA(cudaMemcpyAsync(x->d_norms.p + x->n_dev, x->h_norms.data() + x->n_dev, (size_t)cnt * 4, cudaMemcpyHostToDevice, x->stream));
+    }
+    VDB_CUDA(cudaStreamSynchronize(x->stream));
+    x->n_dev = x->n;
+    return VDB_OK;
+}
+
+static int train_on_device(vdb_index* x, const float* h_samples, int64_t ns) {
+    if (ns <= 0) FAIL(VDB_ERR_INVALID, "Invalid training samples");   // PQIndex.cpp:30-32
+    const int dim = x->cfg.dim, M = x->pq_m;
+    VDB_TRY(x->d_train.ensure((size_t)ns * dim, 0, x->stream));
+    VDB_TRY(x->d_sub.ensure((size_t)ns * dim, 0, x->stream));
+    VDB_TRY(x->d_mind.ensure((size_t)ns * M, 0, x->stream));
+    VDB_TRY(x->d_asg.ensure((size_t)ns * M, 0, x->stream));
+    VDB_TRY(x->d_cb.ensure((size_t)M * VDB_NCENT * x->sd, 0, x->stream));
+    VDB_CUDA(cudaMemcpyAsync(x->d_train.p, h_samples, (size_t)ns * dim * 4, cudaMemcpyHostToDevice, x->stream));
+    if (launch_kmeans_train(x->d_train.p, (int)ns, dim, M, x->cfg.pq_iters, x->cfg.train_flavour, x->d_cb.p, x->d_sub.p, x->d_mind.p,
+                            x->d_asg.p, x->stream) != 0)
+        FAIL(VDB_ERR_INVALID, "k-means launch rejected");
+    VDB_CUDA(cudaGetLastError());
+    VDB_CUDA(cudaStreamSynchronize(x->stream));
+    x->trained = true;
+    return VDB_OK;
+}
+
+// encode rows [n_coded, n_dev) on the device; rows below raw_rows keep all-zero codes (HnswPqIndex.java:104)
+static int encode_pending(vdb_index* x) {
+    if (!x->trained || x->n_coded >= x->n_dev) return VDB_OK;
+    const int M = x->pq_m, dim = x->cfg.dim;
+    VDB_TRY(x->d_codes.ensure((size_t)x->n_dev * M, (size_t)x->n_coded * M, x->stream));
+    int64_t from = x->n_coded;
+    if (from < x->raw_rows) {
+        const int64_t upto = std::min(x->raw_rows, x->n_dev);
+        VDB_CUDA(cudaMemsetAsync(x->d_codes.p + (size_t)from * M, 0, (size_t)(upto - from) * M, x->stream));
+        from = upto;
+    }
+    if (from < x->n_dev) {
+        if (launch_pq_encode(x->d_base.p + (size_t)from * dim, x->n_dev - from, dim, M, x->d_cb.p, x->cfg.arith, x->d_codes.p + (size_t)from * M,
+                             x->stream) != 0)
+            FAIL(VDB_ERR_INVALID, "encode launch rejected");
+        VDB_CUDA(cudaGetLastError());
+    }
+    if (x->codes_overridden && (int64_t)x->h_codes_override.size() == x->n_dev * M)
+        VDB_CUDA(cudaMemcpyAsync(x->d_codes.p, x->h_codes_override.data(), x->h_codes_override.size(), cudaMemcpyHostToDevice, x->stream));
+    VDB_CUDA(cudaStreamSynchronize(x->stream));
+    x->n_coded = x->n_dev;
+    return VDB_OK;
+}
+
+static int upload_graph(vdb_index* x) {
+    const int64_t n = x->g.size();
+    const int L = x->g.max_level, M = x->g.M;
+    VDB_TRY(x->d_adj.ensure((size_t)L * n * M, 0, x->stream));
+    for (int l = 0; l < L; l++)
+        VDB_CUDA(cudaMemcpyAsync(x->d_adj.p + (size_t)l * n * M, x->g.adj[l].data(), (size_t)n * M * 4, cudaMemcpyHostToDevice, x->stream));
+    VDB_CUDA(cudaStreamSynchronize(x->stream));
+    x->graph_uploaded = true;
+    return VDB_OK;
+}
+
+// bring the searchable state up to date with everything added so far (Java indexes are searchable after every addVector)
+static int sync_index(vdb_index* x) {
+    VDB_CUDA(cudaSetDevice(x->cfg.device));
+    const int t = x->cfg.index_type;
+    if (t == VDB_INDEX_HNSW || t == VDB_INDEX_HNSW_PQ) {
+        if (x->device_only) FAIL(VDB_ERR_INVALID, "graph indexes need host rows (vdb_fill_synthetic is for FLAT/PQ)");
+        if (x->n_indexed < x->n) {
+            x->g.vecs = x->h_vecs.data(); x->g.norms = x->h_norms.data();
+            const int dim = x->cfg.dim;
+            for (int64_t i = x->n_indexed; i < x->n; i++) {
+                int ef = x->cfg.ef_construction, variant = 2;
+                if (t == VDB_INDEX_HNSW_PQ) {
+                    variant = 1;
+                    // addVector: collect samples until trained; train at min(10000, maxElements/10) (HnswPqIndex.java:170-175)
+                    if (!x->trained && x->n_train < 10000) {
+                        x->h_train.insert(x->h_train.end(), x->h_vecs.begin() + i * dim, x->h_vecs.begin() + (i + 1) * dim);
+                        x->n_train++;
+                        if (x->n_train >= std::min<int64_t>(10000, x->cfg.max_elements / 10)) {
+                            VDB_TRY(train_on_device(x, x->h_train.data(), x->n_train));
+                            x->raw_rows = i;   // rows before this one were added raw
+                        }
+                    }
+                    if (!x->trained) x->raw_rows = i + 1;
+                    ef = x->trained ? std::max(x->cfg.ef_construction, 200) : x->cfg.ef_construction;   // :498 / :417
+                }
+                x->g.insert((int)i, ef, variant);
+            }
+            x->n_indexed = x->n;
+            x->graph_uploaded = false;
+        }
+        VDB_TRY(upload_rows(x));
+        if (t == VDB_INDEX_HNSW_PQ) VDB_TRY(encode_pending(x));
+        if (!x->graph_uploaded) VDB_TRY(upload_graph(x));
+    } else {
+        VDB_TRY(upload_rows(x));
+        if (t == VDB_INDEX_PQ) VDB_TRY(encode_pending(x));
+    }
+    return VDB_OK;
+}
+
+// ---- add / train / build ---------------------------------------------------------------------------------------
+extern "C" int vdb_add_batch(vdb_index* x, const int32_t* ids, const float* vecs, int64_t cnt) {
+    if (!x || (!vecs && cnt > 0) || cnt < 0) FAIL(VDB_ERR_INVALID, "vdb_add_batch: bad arguments");
+    std::lock_guard<std::mutex> lk(x->mu);
+    if (x->device_only) FAIL(VDB_ERR_INVALID, "index holds device-generated rows; host adds are not allowed");
+    if (x->cfg.index_type == VDB_INDEX_PQ && !x->trained)
+        FAIL(VDB_ERR_UNTRAINED, "PQ index must be trained before adding vectors");    // PQIndex.cpp:124-126
+    if (x->n + cnt > x->cfg.max_elements) FAIL(VDB_ERR_FULL, "max_elements exceeded");   // VectorStore.cpp:40-43
+    VDB_CUDA(cudaSetDevice(x->cfg.device));
+    const int dim = x->cfg.dim;
+    const size_t old = x->h_vecs.size();
+    x->h_vecs.insert(x->h_vecs.end(), vecs, vecs + (size_t)cnt * dim);
+    for (int64_t i = 0; i < cnt; i++) x->h_ids.push_back(ids ? ids[i] : (int32_t)(x->cfg.id_offset + x->n + i));
+    if (x->cfg.metric == VDB_METRIC_COSINE && cnt > 0) {
+        // normalise on insert (HnswIndex.java:154) with Java's arithmetic, on the device; keep the normalised copy on the host
+        VDB_TRY(x->d_q.ensure((size_t)cnt * dim, 0, x->stream));
+        VDB_TRY(x->d_out_d.ensure((size_t)cnt, 0, x->stream));
+        VDB_CUDA(cudaMemcpyAsync(x->d_q.p, vecs, (size_t)cnt * dim * 4, cudaMemcpyHostToDevice, x->stream));
+        launch_normalize_rows(x->d_q.p, cnt, dim, x->d_out_d.p, x->stream);
+        x->h_norms.resize(x->n + cnt);
+        VDB_CUDA(cudaMemcpyAsync(x->h_vecs.data() + old, x->d_q.p, (size_t)cnt * dim * 4, cudaMemcpyDeviceToHost, x->stream));
+        VDB_CUDA(cudaMemcpyAsync(x->h_norms.data() + x->n, x->d_out_d.p, (size_t)cnt * 4, cudaMemcpyDeviceToHost, x->stream));
+        VDB_CUDA(cudaStreamSynchronize(x->stream));
+    }
+    x->n += cnt;
+    return VDB_OK;
+}
+
+extern "C" int vdb_train(vdb_index* x, const float* samples, int64_t ns) {
+    if (!x || !samples) FAIL(VDB_ERR_INVALID, "Invalid training samples");
+    std::lock_guard<std::mutex> lk(x->mu);
+    if (x->pq_m == 0) FAIL(VDB_ERR_INVALID, "index has no PQ stage");
+    VDB_CUDA(cudaSetDevice(x->cfg.device));
+    VDB_TRY(train_on_device(x, samples, ns));
+    x->n_coded = 0;
+    return VDB_OK;
+}
+
+extern "C" int vdb_set_codebooks(vdb_index* x, const float* cb) {
+    if (!x || !cb || x->pq_m == 0) FAIL(VDB_ERR_INVALID, "vdb_set_codebooks: bad arguments");
+    std::lock_guard<std::mutex> lk(x->mu);
+    VDB_CUDA(cudaSetDevice(x->cfg.device));
+    const size_t cnt = (size_t)x->pq_m * VDB_NCENT * x->sd;
+    VDB_TRY(x->d_cb.ensure(cnt, 0, x->stream));
+    VDB_CUDA(cudaMemcpyAsync(x->d_cb.p, cb, cnt * 4, cudaMemcpyHostToDevice, x->stream));
+    VDB_CUDA(cudaStreamSynchronize(x->stream));
+    x->trained = true; x->n_coded = 0;
+    return VDB_OK;
+}
+extern "C" int vdb_get_codebooks(vdb_index* x, float* out) {
+    if (!x || !out || !x->trained) FAIL(VDB_ERR_UNTRAINED, "no codebooks");
+    std::lock_guard<std::mutex> lk(x->mu);
+    VDB_CUDA(cudaSetDevice(x->cfg.device));
+    VDB_CUDA(cudaMemcpy(out, x->d_cb.p, (size_t)x->pq_m * VDB_NCENT * x->sd * 4, cudaMemcpyDeviceToHost));
+    return VDB_OK;
+}
+extern "C" int vdb_set_codes(vdb_index* x, const uint8_t* codes) {
+    if (!x || !codes || x->pq_m == 0) FAIL(VDB_ERR_INVALID, "vdb_set_codes: bad arguments");
+    std::lock_guard<std::mutex> lk(x->mu);
+    x->h_codes_override.assign(codes, codes + (size_t)x->n * x->pq_m);
+    x->codes_overridden = true; x->n_coded = 0;
+    return VDB_OK;
+}
+extern "C" int vdb_get_codes(vdb_index* x, uint8_t* out) {
+    if (!x || !out || x->pq_m == 0) FAIL(VDB_ERR_INVALID, "vdb_get_codes: bad arguments");
+    std::lock_guard<std::mutex> lk(x->mu);
+    VDB_TRY(sync_index(x));
+    if (x->n_coded < x->n_dev) FAIL(VDB_ERR_UNTRAINED, "codes not available (untrained)");
+    VDB_CUDA(cudaMemcpy(out, x->d_codes.p, (size_t)x->n_dev * x->pq_m, cudaMemcpyDeviceToHost));
+    return VDB_OK;
+}
+extern "C" int vdb_encode_all(vdb_index* x) {
+    if (!x || x->pq_m == 0) FAIL(VDB_ERR_INVALID, "vdb_encode_all: bad arguments");
+    std::lock_guard<std::mutex> lk(x->mu);
+    if (!x->trained) FAIL(VDB_ERR_UNTRAINED, "train first");
+    VDB_CUDA(cudaSetDevice(x->cfg.device));
+    VDB_TRY(upload_rows(x));
+    x->n_coded = 0; x->raw_rows = 0;
+    return encode_pending(x);
+}
+
+extern "C" int vdb_set_graph(vdb_index* x, const int32_t* levels, const int32_t* adj, int32_t max_level, int32_t entry) {
+    if (!x || !levels || !adj) FAIL(VDB_ERR_INVALID, "vdb_set_graph: bad arguments");
+    std::lock_guard<std::mutex> lk(x->mu);
+    if (max_level != x->g.max_level) FAIL(VDB_ERR_INVALID, "max_level mismatch");
+    x->g.import_graph(levels, adj, (int)x->n, entry);
+    x->n_indexed = x->n; x->graph_uploaded = false;
+    return VDB_OK;
+}
+extern "C" int vdb_get_graph(vdb_index* x, int32_t* levels, int32_t* adj, int32_t* entry) {
+    if (!x) FAIL(VDB_ERR_INVALID, "vdb_get_graph: bad arguments");
+    std::lock_guard<std::mutex> lk(x->mu);
+    VDB_TRY(sync_index(x));
+    const int64_t n = x->g.size();
+    if (levels) std::memcpy(levels, x->g.level.data(), (size_t)n * 4);
+    if (adj) for (int l = 0; l < x->g.max_level; l++) std::memcpy(adj + (size_t)l * n * x->g.M, x->g.adj[l].data(), (size_t)n * x->g.M * 4);
+    if (entry) *entry = x->g.entry;
+    return VDB_OK;
+}
+
+// rebuildIndex (HnswPqIndex.java:676-718, HnswIndex.java:430-478): train if needed, clear, re-add in ascending id order
+extern "C" int vdb_build(vdb_index* x) {
+    if (!x) FAIL(VDB_ERR_INVALID, "vdb_build: null index");
+    std::lock_guard<std::mutex> lk(x->mu);
+    VDB_CUDA(cudaSetDevice(x->cfg.device));
+    const int t = x->cfg.index_type;
+    if (t == VDB_INDEX_FLAT || t == VDB_INDEX_PQ) return sync_index(x);     // NativeIndex.buildIndex() is a no-op (NativeIndex.java:84-87)
+    if (x->device_only) FAIL(VDB_ERR_INVALID, "graph indexes need host rows");
+    const int dim = x->cfg.dim;
+    if (t == VDB_INDEX_HNSW_PQ && !x->trained) {
+        // samples collected so far = the first min(n, 10000) rows in arrival order
+        if (x->n_indexed < x->n) {
+            for (int64_t i = x->n_indexed; i < x->n && x->n_train < 10000; i++) {
+                x->h_train.insert(x->h_train.end(), x->h_vecs.begin() + i * dim, x->h_vecs.begin() + (i + 1) * dim);
+                x->n_train++;
+            }
+        }
+        if (x->n_train > 0) VDB_TRY(train_on_device(x, x->h_train.data(), x->n_train));
+    }
+    // reorder the store by id (stable), as buildIndex sorts the saved vectors by id before re-adding
+    std::vector<int64_t> order(x->n);
+    std::iota(order.begin(), order.end(), 0);
+    std::stable_sort(order.begin(), order.end(), [&](int64_t a, int64_t b) { return x->h_ids[a] < x->h_ids[b]; });
+    bool sorted = true;
+    for (int64_t i = 0; i < x->n; i++) if (order[i] != i) { sorted = false; break; }
+    if (!sorted) {
+        std::vector<float> nv(x->h_vecs.size());
+        std::vector<int32_t> ni(x->n);
+        std::vector<float> nn(x->h_norms.size());
+        for (int64_t i = 0; i < x->n; i++) {
+            std::memcpy(&nv[(size_t)i * dim], &x->h_vecs[(size_t)order[i] * dim], (size_t)dim * 4);
+            ni[i] = x->h_ids[order[i]];
+            if (!nn.empty()) nn[i] = x->h_norms[order[i]];
+        }
+        x->h_vecs.swap(nv); x->h_ids.swap(ni); x->h_norms.swap(nn);
+    }
+    x->g.clear();
+    x->n_indexed = 0; x->n_dev = 0; x->n_coded = 0; x->raw_rows = 0; x->codes_overridden = false;
+    return sync_index(x);
+}
+
+extern "C" int vdb_fill_synthetic(vdb_index* x, uint64_t seed, int64_t cnt) {
+    if (!x || cnt <= 0) FAIL(VDB_ERR_INVALID, "vdb_fill_synthetic: bad arguments");
+    std::lock_guard<std::mutex> lk(x->mu);
+    if (x->cfg.index_type != VDB_INDEX_FLAT && x->cfg.index_type != VDB_INDEX_PQ) FAIL(VDB_ERR_INVALID, "synthetic fill is for FLAT/PQ indexes");
+    if (x->n > 0 && !x->device_only) FAIL(VDB_ERR_INVALID, "index already holds host rows");
+    if (x->n + cnt > x->cfg.max_elements) FAIL(VDB_ERR_FULL, "max_elements exceeded");
+    VDB_CUDA(cudaSetDevice(x->cfg.device));
+    const int dim = x->cfg.dim;
+    VDB_TRY(x->d_base.ensure((size_t)(x->n + cnt) * dim, (size_t)x->n * dim, x->stream));
+    // generator index = (global row) * dim + j so that shards of one logical dataset agree with the oracle
+    launch_fill_synth(x->d_base.p + (size_t)x->n * dim, seed, (int64_t)(x->cfg.id_offset + x->n) * dim, cnt * dim, x->stream);
+    if (x->cfg.metric == VDB_METRIC_COSINE) {
+        VDB_TRY(x->d_norms.ensure((size_t)(x->n + cnt), (size_t)x->n, x->stream));
+        launch_normalize_rows(x->d_base.p + (size_t)x->n * dim, cnt, dim, x->d_norms.p + x->n, x->stream);
+    }
+    VDB_CUDA(cudaGetLastError());
+    VDB_CUDA(cudaStreamSynchronize(x->stream));
+    x->device_only = true;
+    x->n += cnt; x->n_dev = x->n;
+    return VDB_OK;
+}
+
+// ---- search ---------------------------------------------------------------------------------------------------
+static inline int java_search_ef(int64_t n, int k, int ef) {     // HnswPqIndex.java:616-621
+    int byRatio = (int)((double)n * 0.15);
+    int s = std::max(std::max(byRatio, k * 100), ef);
+    s = (int)std::min<int64_t>(s, n);
+    return std::min(s, 5000);
+}
+
+static int search_graph(vdb_index* x, const float* d_q, int64_t nq, int k, int32_t* d_ids, float* d_dists, cudaStream_t st) {
+    HnswSearchParams p{};
+    const bool pq = x->cfg.index_type == VDB_INDEX_HNSW_PQ;
+    p.base = x->d_base.p; p.norms = pq ? nullptr : x->d_norms.p; p.ids = x->d_ids.p; p.adj = x->d_adj.p;
+    p.codes = pq && x->trained ? x->d_codes.p : nullptr; p.codebooks = pq && x->trained ? x->d_cb.p : nullptr;
+    p.queries = d_q; p.out_ids = d_ids; p.out_dists = d_dists; p.counters = x->d_counters.p;
+    p.n = (int)x->n; p.dim = x->cfg.dim; p.deg = x->g.M; p.max_level = x->g.max_level; p.entry = x->g.entry;
+    p.pq_m = x->pq_m; p.trained = pq && x->trained ? 1 : 0;
+    p.metric = pq ? 0 : 1;
+    if (pq) {
+        const int sef = java_search_ef(x->n, k, x->cfg.ef_search);
+        if (x->trained) { p.variant = 0; p.ef = std::max(sef, k * 100); }     // :638-640 searchLayerWithSize
+        else { p.variant = 1; p.ef = sef; }                                    // :643 searchLayer
+    } else { p.variant = 2; p.ef = std::max(x->cfg.ef_search, k * 4); }        // HnswIndex.java:347
+    p.cap = next_pow2(p.ef + 64);
+    p.k = k; p.nq = (int)nq;
+    p.visited_in_smem = 1;
+    size_t smem = hnsw_search_smem_bytes(p);
+    if (smem > 200 * 1024) { p.visited_in_smem = 0; smem = hnsw_search_smem_bytes(p); }
+    if (smem > 227 * 1024) FAIL(VDB_ERR_INVALID, "ef too large for the shared-memory pool");
+    int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (227 * 1024) / (smem + 1024)));
+    int grid = (int)std::min<int64_t>(nq, (int64_t)x->num_sms * per_sm);
+    if (!p.visited_in_smem) {
+        VDB_TRY(x->d_visited.ensure((size_t)grid * ((x->n + 31) / 32), 0, st));
+        p.visited_scratch = x->d_visited.p;
+    }
+    if (x->timed) cudaEventRecord(x->ev_k0, st);
+    int rc = launch_hnsw_search(p, grid, st);
+    if (rc != 0) FAIL(VDB_ERR_INVALID, rc == 1 ? "k or degree too large for the graph kernel" : "shared memory request rejected");
+    if (x->timed) cudaEventRecord(x->ev_k1, st);
+    VDB_CUDA(cudaGetLastError());
+    return VDB_OK;
+}
+
+static int pick_chunks(const vdb_index* x, int64_t nq, int64_t n, int R) {
+    int want = (int)((2 * (int64_t)x->num_sms + nq - 1) / nq);
+    int maxc = std::max(1, 8192 / next_pow2(R));
+    int c = std::max(1, std::min(want, maxc));
+    while (c > 1 && n / c < 4096) c--;
+    return c;
+}
+
+static int search_pq(vdb_index* x, const float* d_q, int64_t nq, int k, int32_t* d_ids, float* d_dists, cudaStream_t st) {
+    if (!x->trained) {   // PQIndex.cpp:147-150 / :259-270: untrained -> no results
+        launch_keys_to_results(nullptr, 0, k, nq, d_ids, d_dists, st);
+        return VDB_OK;
+    }
+    const int M = x->pq_m, dim = x->cfg.dim;
+    const int R = x->cfg.rerank > 0 ? std::max(x->cfg.rerank, k) : k;
+    if (R > 4096) FAIL(VDB_ERR_INVALID, "rerank shortlist > 4096 not supported");
+    const int64_t QB = 1024;   // query sub-batch: bounds the LUT buffer (QB * M * 1 KB)
+    const int32_t* ids = x->device_only ? nullptr : x->d_ids.p;
+    for (int64_t q0 = 0; q0 < nq; q0 += QB) {
+        const int64_t qb = std::min(QB, nq - q0);
+        const int nch = pick_chunks(x, qb, x->n, R);
+        VDB_TRY(x->d_lut.ensure((size_t)qb * M * VDB_NCENT, 0, st));
+        VDB_TRY(x->d_keys.ensure((size_t)qb * R, 0, st));
+        VDB_TRY(x->d_rows.ensure((size_t)qb * R, 0, st));
+        if (nch > 1) { VDB_TRY(x->d_keys_tmp.ensure((size_t)qb * R * nch, 0, st)); VDB_TRY(x->d_rows_tmp.ensure((size_t)qb * R * nch, 0, st)); }
+        launch_pq_lut(d_q + q0 * dim, x->d_cb.p, (int)qb, dim, M, x->cfg.arith, x->d_lut.p, st);
+        if (x->timed && q0 == 0) cudaEventRecord(x->ev_k0, st);
+        launch_adc_scan_topr(x->d_codes.p, x->n, M, x->d_lut.p, (int)qb, ids, x->cfg.id_offset, R, nch, x->d_keys_tmp.p, x->d_rows_tmp.p,
+                             x->d_keys.p, x->d_rows.p, st);
+        if (x->timed && q0 == 0) cudaEventRecord(x->ev_k1, st);
+        if (x->cfg.rerank > 0)
+            launch_rerank(x->d_base.p, ids, x->cfg.id_offset, dim, d_q + q0 * dim, (int)qb, x->d_rows.p, R,
+                          x->cfg.arith == VDB_ARITH_NATIVE_AVX2 ? ORDER_R1 : ORDER_SEQ, k, d_ids + q0 * k, d_dists + q0 * k, st);
+        else
+            launch_keys_to_results(x->d_keys.p, R, k, qb, d_ids + q0 * k, d_dists + q0 * k, st);
+        VDB_CUDA(cudaGetLastError());
+    }
+    x->stats.adc_rows += nq * x->n;
+    return VDB_OK;
+}
+
+static int search_flat(vdb_index* x, const float* d_q, int64_t nq, int k, int32_t* d_ids, float* d_dists, cudaStream_t st) {
+    if (k > 2048) FAIL(VDB_ERR_INVALID, "k > 2048 not supported");
+    const int32_t* ids = x->device_only ? nullptr : x->d_ids.p;
+    const int64_t QB = 16384;
+    for (int64_t q0 = 0; q0 < nq; q0 += QB) {
+        const int64_t qb = std::min(QB, nq - q0);
+        const int nch = pick_chunks(x, qb, x->n, k);
+        VDB_TRY(x->d_keys.ensure((size_t)qb * k, 0, st));
+        VDB_TRY(x->d_rows.ensure((size_t)qb * k, 0, st));
+        if (nch > 1) { VDB_TRY(x->d_keys_tmp.ensure((size_t)qb * k * nch, 0, st)); VDB_TRY(x->d_rows_tmp.ensure((size_t)qb * k * nch, 0, st)); }
+        if (x->timed && q0 == 0) cudaEventRecord(x->ev_k0, st);
+        launch_flat_search_exact(x->d_base.p, x->d_norms.p, ids, x->cfg.id_offset, x->n, x->cfg.dim, d_q + q0 * x->cfg.dim, (int)qb, k,
+                                 x->cfg.metric, x->cfg.arith == VDB_ARITH_NATIVE_AVX2 ? ORDER_R1 : ORDER_SEQ, nch, x->d_keys_tmp.p,
+                                 x->d_rows_tmp.p, x->d_keys.p, x->d_rows.p, st);
+        if (x->timed && q0 == 0) cudaEventRecord(x->ev_k1, st);
+        launch_keys_to_results(x->d_keys.p, k, k, qb, d_ids + q0 * k, d_dists + q0 * k, st);
+        VDB_CUDA(cudaGetLastError());
+    }
+    return VDB_OK;
+}
+
+static int search_device_locked(vdb_index* x, const float* d_q, int64_t nq, int k, int32_t* d_ids, float* d_dists, cudaStream_t st) {
+    VDB_TRY(sync_index(x));
+    if (nq == 0) return VDB_OK;
+    x->timed = true;
+    cudaEventRecord(x->ev_total0, st);
+    int rc;
+    if (x->n == 0 || (x->g.entry < 0 && (x->cfg.index_type == VDB_INDEX_HNSW || x->cfg.index_type == VDB_INDEX_HNSW_PQ))) {
+        launch_keys_to_results(nullptr, 0, k, nq, d_ids, d_dists, st);     // empty index -> empty lists (HnswIndexTest.java:120-129)
+        cudaEventRecord(x->ev_k0, st); cudaEventRecord(x->ev_k1, st);
+        rc = VDB_OK;
+    } else {
+        switch (x->cfg.index_type) {
+            case VDB_INDEX_FLAT: rc = search_flat(x, d_q, nq, k, d_ids, d_dists, st); break;
+            case VDB_INDEX_PQ: rc = search_pq(x, d_q, nq, k, d_ids, d_dists, st); break;
+            default: rc = search_graph(x, d_q, nq, k, d_ids, d_dists, st); break;
+        }
+    }
+    cudaEventRecord(x->ev_total1, st);
+    x->stats.queries += nq;
+    return rc;
+}
+
+extern "C" int vdb_search_batch_device(vdb_index* x, const float* d_q, int64_t nq, int32_t k, int32_t* d_ids, float* d_dists, void* stream) {
+    if (!x || nq < 0 || k <= 0 || (nq > 0 && (!d_q || !d_ids || !d_dists))) FAIL(VDB_ERR_INVALID, "vdb_search_batch_device: bad arguments");
+    std::lock_guard<std::mutex> lk(x->mu);
+    cudaStream_t st = stream ? (cudaStream_t)stream : x->stream;
+    return search_device_locked(x, d_q, nq, k, d_ids, d_dists, st);
+}
+
+extern "C" int vdb_search_batch(vdb_index* x, const float* q, int64_t nq, int32_t k, int32_t* out_ids, float* out_d) {
+    if (!x || nq < 0 || k <= 0 || (nq > 0 && (!q || !out_ids || !out_d))) FAIL(VDB_ERR_INVALID, "vdb_search_batch: bad arguments");
+    std::lock_guard<std::mutex> lk(x->mu);
+    VDB_CUDA(cudaSetDevice(x->cfg.device));
+    if (nq == 0) return VDB_OK;
+    const int dim = x->cfg.dim;
+    cudaStream_t st = x->stream;
+    VDB_TRY(x->d_q.ensure((size_t)nq * dim, 0, st));
+    VDB_TRY(x->d_out_d.ensure((size_t)nq * k, 0, st));
+    VDB_TRY(x->d_out_ids.ensure((size_t)nq * k, 0, st));
+    // caller memory is pageable in general (Java direct ByteBuffers): stage through pinned buffers so the copies are async DMA
+    VDB_TRY(x->p_q.ensure((size_t)nq * dim));
+    VDB_TRY(x->p_d.ensure((size_t)nq * k));
+    VDB_TRY(x->p_ids.ensure((size_t)nq * k));
+    std::memcpy(x->p_q.p, q, (size_t)nq * dim * 4);
+    VDB_CUDA(cudaMemcpyAsync(x->d_q.p, x->p_q.p, (size_t)nq * dim * 4, cudaMemcpyHostToDevice, st));
+    VDB_TRY(search_device_locked(x, x->d_q.p, nq, k, x->d_out_ids.p, x->d_out_d.p, st));
+    VDB_CUDA(cudaMemcpyAsync(x->p_ids.p, x->d_out_ids.p, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, st));
+    VDB_CUDA(cudaMemcpyAsync(x->p_d.p, x->d_out_d.p, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, st));
+    VDB_CUDA(cudaStreamSynchronize(st));
+    std::memcpy(out_ids, x->p_ids.p, (size_t)nq * k * 4);
+    std::memcpy(out_d, x->p_d.p, (size_t)nq * k * 4);
+    return VDB_OK;
+}
+
+extern "C" int vdb_get_stats(vdb_index* x, vdb_stats* out) {
+    if (!x || !out) FAIL(VDB_ERR_INVALID, "vdb_get_stats: bad arguments");
+    std::lock_guard<std::mutex> lk(x->mu);
+    VDB_CUDA(cudaSetDevice(x->cfg.device));
+    if (x->timed) {
+        VDB_CUDA(cudaEventSynchronize(x->ev_total1));
+        cudaEventElapsedTime(&x->stats.last_total_ms, x->ev_total0, x->ev_total1);
+        if (cudaEventElapsedTime(&x->stats.last_kernel_ms, x->ev_k0, x->ev_k1) != cudaSuccess) { x->stats.last_kernel_ms = 0; cudaGetLastError(); }
+    }
+    unsigned long long c[2] = {0, 0};
+    VDB_CUDA(cudaMemcpy(c, x->d_counters.p, sizeof(c), cudaMemcpyDeviceToHost));
+    x->stats.dist_evals = (int64_t)c[0]; x->stats.expansions = (int64_t)c[1];
+    *out = x->stats;
+    return VDB_OK;
+}
+
+// ---- device-side building blocks ------------------------------------------------------------------------------
+extern "C" int vdb_pq_lut_device(vdb_index* x, const float* d_q, int64_t nq, float* d_lut, void* stream) {
+    if (!x || !d_q || !d_lut || x->pq_m == 0) FAIL(VDB_ERR_INVALID, "vdb_pq_lut_device: bad arguments");
+    std::lock_guard<std::mutex> lk(x->mu);
+    if (!x->trained) FAIL(VDB_ERR_UNTRAINED, "train first");
+    cudaStream_t st = stream ? (cudaStream_t)stream : x->stream;
+    launch_pq_lut(d_q, x->d_cb.p, (int)nq, x->cfg.dim, x->pq_m, x->cfg.arith, d_lut, st);
+    VDB_CUDA(cudaGetLastError());
+    return VDB_OK;
+}
+extern "C" int vdb_adc_scan_device(vdb_index* x, const float* d_lut, float* d_out, void* stream) {
+    if (!x || !d_lut || !d_out || x->pq_m == 0) FAIL(VDB_ERR_INVALID, "vdb_adc_scan_device: bad arguments");
+    std::lock_guard<std::mutex> lk(x->mu);
+    VDB_TRY(sync_index(x));
+    if (x->n_coded < x->n) FAIL(VDB_ERR_UNTRAINED, "no codes");
+    cudaStream_t st = stream ? (cudaStream_t)stream : x->stream;
+    launch_adc_scan_plain(x->d_codes.p, x->n, x->pq_m, d_lut, d_out, st);
+    VDB_CUDA(cudaGetLastError());
+    return VDB_OK;
+}
+extern "C" int vdb_merge_topk_device(const float* d_dists, const int32_t* d_ids, int32_t g, int64_t nq, int32_t k, float* d_out_d,
+                                     int32_t* d_out_ids, void* stream) {
+    if (!d_dists || !d_ids || !d_out_d || !d_out_ids || g <= 0 || k <= 0 || (int64_t)g * k > 8192) FAIL(VDB_ERR_INVALID, "vdb_merge_topk_device: bad arguments");
+    launch_merge_topk(d_dists, d_ids, g, nq, k, d_out_d, d_out_ids, (cudaStream_t)stream);
+    VDB_CUDA(cudaGetLastError());
+    return VDB_OK;
+}
+extern "C" int vdb_distance_device(const float* d_a, const float* d_b, int64_t n, int32_t dim, int32_t metric, int32_t order, float* d_out,
+                                   void* stream) {
+    if (!d_a || !d_b || !d_out) FAIL(VDB_ERR_INVALID, "vdb_distance_device: bad arguments");
+    launch_distance(d_a, d_b, n, dim, metric, order, d_out, (cudaStream_t)stream);
+    VDB_CUDA(cudaGetLastError());
+    return VDB_OK;
+}

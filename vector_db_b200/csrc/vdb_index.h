@@ -1,0 +1,109 @@
+// vdb_index.h — the index object behind the C ABI (include/vdb.h).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/vdb.h"
+#include "host_graph.h"
+
+void vdb_set_error(const std::string& msg);
+
+#define VDB_CUDA(call)                                                                          \
+    do {                                                                                        \
+        cudaError_t e__ = (call);                                                               \
+        if (e__ != cudaSuccess) {                                                               \
+            vdb_set_error(std::string(#call) + ": " + cudaGetErrorString(e__));                 \
+            return VDB_ERR_CUDA;                                                                \
+        }                                                                                       \
+    } while (0)
+#define VDB_TRY(call)                    \
+    do {                                 \
+        int rc__ = (call);               \
+        if (rc__ != VDB_OK) return rc__; \
+    } while (0)
+
+// growable device array; ensure() keeps the first `keep` elements
+template <typename T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t cap = 0;
+    int ensure(size_t n, size_t keep, cudaStream_t st) {
+        if (n <= cap) return VDB_OK;
+        size_t ncap = n;
+        T* np = nullptr;
+        VDB_CUDA(cudaMalloc(&np, ncap * sizeof(T)));
+        if (p && keep) VDB_CUDA(cudaMemcpyAsync(np, p, keep * sizeof(T), cudaMemcpyDeviceToDevice, st));
+        if (p) { VDB_CUDA(cudaStreamSynchronize(st)); cudaFree(p); }
+        p = np; cap = ncap;
+        return VDB_OK;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+template <typename T>
+struct PinnedBuf {
+    T* p = nullptr;
+    size_t cap = 0;
+    int ensure(size_t n) {
+        if (n <= cap) return VDB_OK;
+        if (p) cudaFreeHost(p);
+        p = nullptr; cap = 0;
+        VDB_CUDA(cudaMallocHost(&p, n * sizeof(T)));
+        cap = n;
+        return VDB_OK;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
+struct vdb_index {
+    vdb_config cfg;
+    int pq_m = 0, sd = 0, num_sms = 148;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_total0 = nullptr, ev_total1 = nullptr, ev_k0 = nullptr, ev_k1 = nullptr;
+    bool timed = false;
+    std::mutex mu;
+
+    // host store (row = insertion order since the last rebuild)
+    std::vector<float> h_vecs;      // normalised rows for cosine
+    std::vector<float> h_norms;     // cosine only
+    std::vector<int32_t> h_ids;
+    int64_t n = 0;                  // rows stored
+    bool device_only = false;       // rows were generated on the device (vdb_fill_synthetic): no host copy
+
+    // device store
+    DevBuf<float> d_base, d_norms, d_cb;
+    DevBuf<int32_t> d_ids, d_adj;
+    DevBuf<uint8_t> d_codes;
+    int64_t n_dev = 0;              // rows present in d_base / d_ids
+    int64_t n_coded = 0;            // rows with valid codes in d_codes
+
+    // PQ state
+    bool trained = false;
+    std::vector<float> h_train;     // samples collected by addVector (HnswPqIndex.java:170-175)
+    int64_t n_train = 0;
+    int64_t raw_rows = 0;           // rows inserted before training finished: their codes stay zero (HnswPqIndex.java:104,391)
+    std::vector<uint8_t> h_codes_override;  // vdb_set_codes
+    bool codes_overridden = false;
+
+    // graph
+    HostGraph g;
+    int64_t n_indexed = 0;          // rows inserted into the graph
+    bool graph_uploaded = false;
+
+    // search scratch
+    DevBuf<float> d_q, d_out_d, d_lut;
+    DevBuf<int32_t> d_out_ids;
+    DevBuf<uint64_t> d_keys, d_keys_tmp;
+    DevBuf<uint32_t> d_rows, d_rows_tmp, d_visited;
+    DevBuf<unsigned long long> d_counters;
+    PinnedBuf<float> p_q, p_d;
+    PinnedBuf<int32_t> p_ids;
+    // training scratch
+    DevBuf<float> d_train, d_sub, d_mind;
+    DevBuf<int> d_asg;
+
+    vdb_stats stats{};
+};
