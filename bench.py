@@ -1,0 +1,338 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the batched query path (BASELINE.json metric):
+
+    QPS @ Recall@10 >= 0.95, 512-d HNSW+PQ, 1/8 B200  (+ ADC-scan HBM GB/s vs peak)
+
+Workload at N=1 (BASELINE.json configs[2], "C3" in SURVEY.md §8): 100 000 synthetic uniform [-1,1) 512-d vectors,
+HNSW+PQ with CompressionConfig.recommendedConfig(512) = 64 subspaces x 8 bits, one batch of 4 096 queries, k = 10.
+A step = one batch through the GPU search kernel. `value` is timed with queries and outputs resident in HBM,
+`e2e` goes through the reference-facing C-ABI call (vdb_search_batch) with HOST buffers.
+N > 1: HNSW graphs do not shard by id range -> one replica per GPU, each rank serves its own batch
+(weak scaling, no data-path collective); the timing is the max over ranks.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_BASE, DIM, PQ_M, NQ, K = 100_000, 512, 64, 4096, 10
+METRIC = "QPS @ Recall@10>=0.95, 512-d HNSW+PQ"
+WORKLOAD = "C3: 100k x 512-d uniform[-1,1), HNSW+PQ recommendedConfig(512)=(64,8), batch 4096 queries, k=10"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--n", type=int, default=N_BASE, help="base vectors (default: the headline config)")
+    ap.add_argument("--nq", type=int, default=NQ)
+    ap.add_argument("--cpu-sample", type=int, default=192, help="queries in the bounded CPU-baseline sample")
+    ap.add_argument("--adc-rows", type=int, default=2_000_000, help="rows of the auxiliary ADC-scan roofline run (0 = skip)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self._stop, self._t = index, [], threading.Event(), None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([c.strip() for c in out.split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def __enter__(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        self._t.join(timeout=6)
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+            except Exception:
+                continue
+            for name, col in (("hw_slowdown", 5), ("hw_thermal_slowdown", 6), ("sw_thermal_slowdown", 7), ("sw_power_cap", 8)):
+                if len(r) > col and r[col].lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}, "fallback"
+
+
+def make_queries(po, rank, nq):
+    # query seed 43; each replica serves a different slice of the query stream
+    return po.fill_uniform(43, rank * nq * DIM, nq * DIM).reshape(nq, DIM)
+
+
+# ------------------------------------------------------------------------------------------------ reference arm
+def run_reference(args, rank, world):
+    """The reference's own CPU implementation of the path, all host threads. The class that carries the metric
+    (Recall@10 >= 0.95) is Java HnswPqIndex; no JVM exists on this image, so this arm times the oracle's C++
+    restatement of it (kind "port"); the compiled native HNSWPQIndex (oracle/_ref) reaches Recall@10 ~0.04 and is
+    therefore not the reference for this metric (SURVEY.md §0 findings 6, 7)."""
+    if rank != 0:
+        return
+    from oracle import pyoracle as po
+    cores = os.cpu_count() or 1
+    n, nq = args.n, min(args.cpu_sample, args.nq)
+    X = po.synth(42, n, DIM)
+    Q = make_queries(po, 0, nq)
+    t0 = time.time()
+    o = po.OracleHnsw(po.KIND_HNSWPQ, DIM, 2 * n, pq_m=PQ_M, level_seed=1234)
+    # SETUP (untimed): the graph. The oracle's own sequential Java-style builder needs ~10 min at 100k x 512-d, so when
+    # the B200 library is usable the graph/codebooks/codes are built once with it and IMPORTED — both arms then search
+    # the identical graph ("same persisted graph and codebooks"). Everything inside the timed steps is oracle-only CPU code.
+    built = None
+    try:
+        import __graft_entry__ as ge
+        ge.build_product()
+        import vector_db_b200 as v
+        idx = v.NativeHnswPqIndex(DIM, 2 * n, pqM=PQ_M, level_seed=1234, device=0)
+        idx.addBatch(np.arange(n, dtype=np.int32), X)
+        idx.buildIndex()
+        levels, adj, entry = idx.graph()
+        o.import_state(X, levels, adj, entry, codebooks=idx.codebooks(), codes=idx.codes())
+        idx.close()
+        built = "graph/codebooks/codes imported from the libvectordb build (setup only)"
+    except Exception as e:
+        sys.stderr.write("reference arm: falling back to the oracle's own builder (%s)\n" % e)
+        o.add_batch(X)
+        o.rebuild()
+        built = "oracle build"
+    build_s = time.time() - t0
+    for _ in range(args.warmup):
+        o.search(Q[:max(8, nq // 8)], K, nthreads=cores)
+    times = []
+    for _ in range(args.steps):
+        t = time.perf_counter()
+        ids, d, st = o.search(Q, K, nthreads=cores)
+        times.append(time.perf_counter() - t)
+    tot = sum(times)
+    qps = nq * args.steps / tot
+    gt, _ = po.flat_search(X, Q[:64], K, nthreads=cores)
+    rec = float(np.mean([len(set(a) & set(b)) / K for a, b in zip(ids[:64], gt)]))
+    line = {"impl": "reference", "metric": METRIC, "value": qps, "unit": "queries/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * tot / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "n": n, "dim": DIM, "pq_m": PQ_M, "k": K, "sample_queries_per_step": nq, "graph": built},
+            "recall_at_10": rec,
+            "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": cores, "kind": "port",
+                             "sample": "%d queries/step of the %d-query batch, OpenMP over queries, C++ restatement of Java HnswPqIndex" % (nq, args.nq)},
+            "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "setup_s": build_s}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ b200 arm
+def adc_scan_aux(v, po, torch, rows, pk):
+    """Auxiliary measurement for the second half of the metric ("ADC-scan HBM GB/s vs peak"): C5-shaped flat PQ scan
+    (1000-d, 125 subspaces x 8 bit) over `rows` code rows generated in HBM; algorithmic bytes =
+    queries x rows x 125, codes larger than L2."""
+    dim, M, nq, k = 1000, 125, 296, 10
+    p = v.NativePqIndex(dim, rows, M=M)
+    p.train(po.synth(41, 2000, dim))
+    p.fill_synthetic(42, rows)
+    p.encode_all()
+    tq = torch.from_numpy(po.synth(43, nq, dim)).cuda()
+    for _ in range(2):
+        p.search_device(tq, k)
+    torch.cuda.synchronize()
+    ms = []
+    for _ in range(3):
+        p.search_device(tq, k)
+        torch.cuda.synchronize()
+        ms.append(p.stats()["last_kernel_ms"])
+    t = float(np.median(ms)) * 1e-3
+    gbs = nq * rows * M / t / 1e9
+    p.close()
+    return {"workload": "C5-shaped flat ADC scan: %d rows x 125 B codes, %d queries/launch, k=%d" % (rows, nq, k), "bound": "hbm",
+            "achieved": gbs, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": gbs / pk["hbm_gbs"], "kernel_ms": t * 1e3,
+            "gathers_per_s": nq * rows * M / t}
+
+
+def run_b200(args, rank, world):
+    import torch
+    import torch.distributed as dist
+    import __graft_entry__ as ge
+    from oracle import pyoracle as po          # checker + cpu_baseline leg only
+    if rank == 0:
+        ge.build_product()
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ.get("LOCAL_RANK", 0))))
+        dist.barrier()
+    import vector_db_b200 as v
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    pk, pk_kind = peaks()
+    n, nq = args.n, args.nq
+
+    X = po.synth(42, n, DIM)
+    t0 = time.time()
+    idx = v.NativeHnswPqIndex(DIM, 2 * n, pqM=PQ_M, level_seed=1234, device=local)
+    idx.addBatch(np.arange(n, dtype=np.int32), X)
+    idx.buildIndex()
+    build_s = time.time() - t0
+    Q = make_queries(po, rank, nq)
+    tq = torch.from_numpy(Q).cuda()
+    stream = torch.cuda.current_stream().cuda_stream
+    out_i = torch.empty((nq, K), dtype=torch.int32, device="cuda")
+    out_d = torch.empty((nq, K), dtype=torch.float32, device="cuda")
+    flush = torch.empty(192 * 1024 * 1024 // 4, dtype=torch.float32, device="cuda")    # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing (value) ----
+    for _ in range(args.warmup):
+        idx.search_device_into(tq, K, out_i, out_d, stream)
+    torch.cuda.synchronize()
+    s0 = idx.stats()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    kernel_ms = []
+    barrier()
+    with ClockSampler(local) as clk:
+        for a, b in evs:
+            flush.fill_(1.0)                                  # L2 flush between timed iterations (outside the events)
+            a.record()
+            idx.search_device_into(tq, K, out_i, out_d, stream)
+            b.record()
+            b.synchronize()
+            kernel_ms.append(idx.stats()["last_kernel_ms"])
+        barrier()
+    step_ms = [a.elapsed_time(b) for a, b in evs]
+    tot_ms = float(sum(step_ms))
+    s1 = idx.stats()
+    if world > 1:
+        t = torch.tensor([tot_ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        tot_ms = float(t.item())
+    value = world * nq * args.steps / (tot_ms * 1e-3)
+
+    # ---- end to end through the reference-facing C-ABI call with HOST buffers ----
+    ids_h = np.empty((nq, K), dtype=np.int32); d_h = np.empty((nq, K), dtype=np.float32)
+    for _ in range(2):
+        ids_h, d_h = idx.searchBatch(Q, K)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        ids_h, d_h = idx.searchBatch(Q, K)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    e2e = world * nq * args.steps / e2e_s
+
+    if rank != 0:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel (hnsw_search_kernel): algorithmic bytes = V*4D + E*deg*4 ----
+    V = (s1["dist_evals"] - s0["dist_evals"]) / args.steps
+    E = (s1["expansions"] - s0["expansions"]) / args.steps
+    alg_bytes = V * DIM * 4 + E * 32 * 4
+    kms = float(np.mean(kernel_ms))
+    ach = alg_bytes / (kms * 1e-3) / 1e9
+    roofline = {"kernel": "hnsw_search_kernel", "bound": "hbm", "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s",
+                "frac": ach / pk["hbm_gbs"], "traffic": None, "peak_source": pk_kind + " (MEASURED_PEAKS.json hbm_gbs, burst copy)",
+                "algorithmic_bytes_per_launch": alg_bytes, "dist_evals_per_query": V / nq, "expansions_per_query": E / nq,
+                "kernel_ms": kms, "note": "base (%.0f MB) exceeds L2 only partly; random 2 KB row gathers" % (n * DIM * 4 / 1e6)}
+
+    # ---- recall + parity on a bounded sample, and the CPU baseline (oracle port, all host cores) ----
+    cores = os.cpu_count() or 1
+    ns = min(args.cpu_sample, nq)
+    gt, _ = po.flat_search(X, Q[:ns], K, nthreads=cores)
+    rec = float(np.mean([len(set(a) & set(b)) / K for a, b in zip(ids_h[:ns], gt)]))
+    cpu = None
+    extra = {}
+    if not args.no_cpu_baseline:
+        levels, adj, entry = idx.graph()
+        o = po.OracleHnsw(po.KIND_HNSWPQ, DIM, 2 * n, pq_m=PQ_M, level_seed=1234)
+        o.import_state(X, levels, adj, entry, codebooks=idx.codebooks(), codes=idx.codes())
+        o.search(Q[:16], K, nthreads=cores)
+        t0 = time.perf_counter()
+        oid, od, ost = o.search(Q[:ns], K, nthreads=cores)
+        cpu_s = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        o.search(Q[:max(4, ns // 16)], K, nthreads=1)
+        cpu1_s = (time.perf_counter() - t0) / max(4, ns // 16)
+        cpu = {"value": ns / cpu_s, "unit": "queries/s", "cores": cores, "kind": "port",
+               "sample": "%d of the %d queries, same graph/codebooks/codes as the GPU, OpenMP over queries; C++ restatement of Java "
+                         "HnswPqIndex.searchNearest (no JVM on this image)" % (ns, nq),
+               "single_thread_qps": 1.0 / cpu1_s, "recall_at_10": float(np.mean([len(set(a) & set(b)) / K for a, b in zip(oid, gt)]))}
+        extra["parity_sample"] = {"queries": ns, "id_match_vs_oracle": float((ids_h[:ns] == oid).mean()),
+                                  "oracle_dist_evals_per_query": float(ost[0]) / ns}
+        os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    adc = None
+    if args.adc_rows > 0 and world == 1:
+        try:
+            adc = adc_scan_aux(v, po, torch, args.adc_rows, pk)
+        except Exception as e:     # the auxiliary line must never take the headline down
+            adc = {"error": str(e)}
+    line = {"metric": METRIC, "value": value, "unit": "queries/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": tot_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": WORKLOAD, "n": n, "dim": DIM, "pq_m": PQ_M, "k": K, "queries_per_step_per_gpu": nq,
+                       "parallelism": "replicas x%d (query-sharded, no collective on the data path)" % world,
+                       "l2": "192 MB flush write between timed iterations", "graph_build_s": build_s},
+            "recall_at_10": rec, "clocks": clk.summary(),
+            "e2e": {"value": e2e, "unit": "queries/s", "h2d_bytes_per_step": nq * DIM * 4, "d2h_bytes_per_step": nq * K * 8},
+            "gpu_launches": args.steps * 1, "roofline": roofline, "cpu_baseline": cpu, "adc_scan": adc}
+    line.update(extra)
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_b200(args, rank, world)
+
+
+if __name__ == "__main__":
+    main()

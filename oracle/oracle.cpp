@@ -830,3 +830,32 @@ ORC_API void orc_hnsw_search(void* p, const float* queries, int nq, int k, int32
         if (stats) { stats[0] += ls[0]; stats[1] += ls[1]; }
     }
 }
+
+// Import a graph built elsewhere (the product's builder / a snapshot) so the CPU search runs on the SAME graph,
+// codebooks and codes as the GPU ("same persisted graph and codebooks", BASELINE.json north_star).
+// vecs[n][dim] are stored as is (already normalised for kind 1); adj[max_level][n][M] is -1 padded.
+ORC_API void orc_hnsw_import(void* p, int n, const float* vecs, const int32_t* ids, const int32_t* levels,
+                             const int32_t* adj, int entry, const float* codebooks, const uint8_t* codes) {
+    Hnsw& h = *(Hnsw*)p;
+    h.vecs.assign(vecs, vecs + (size_t)n * h.dim);
+    h.ids.resize(n);
+    for (int i = 0; i < n; i++) h.ids[i] = ids ? ids[i] : i;
+    h.norms.resize(n);
+    for (int i = 0; i < n; i++) h.norms[i] = h.kind == 1 ? norm_java(h.vec(i), h.dim) : 0.0f;
+    h.level.assign(levels, levels + n);
+    for (int l = 0; l < h.maxLevel; l++) {
+        h.graph[l].assign(n, {});
+        h.present[l].assign(n, 0);
+        for (int i = 0; i < n; i++) {
+            const int32_t* row = adj + ((size_t)l * n + i) * h.M;
+            for (int j = 0; j < h.M && row[j] >= 0; j++) h.graph[l][i].push_back(row[j]);
+            h.present[l][i] = (levels[i] >= l) ? 1 : 0;
+        }
+    }
+    h.entry = entry;
+    if (h.kind == 0 && codebooks && codes) {
+        h.codebooks.assign(codebooks, codebooks + (size_t)h.pqM * h.ncent * h.sd);
+        h.codes.assign(codes, codes + (size_t)n * h.pqM);
+        h.trained = true;
+    }
+}

@@ -71,6 +71,7 @@ def lib():
         L.orc_hnsw_get_norms.argtypes = [C.c_void_p, _f32p]
         L.orc_hnsw_get_levels.argtypes = [C.c_void_p, _i32p]
         L.orc_hnsw_get_level_adj.argtypes = [C.c_void_p, C.c_int, _i32p, _u8p]
+        L.orc_hnsw_import.argtypes = [C.c_void_p, C.c_int, _f32p, C.c_void_p, _i32p, _i32p, C.c_int, C.c_void_p, C.c_void_p]
         L.orc_java_search_ef.argtypes = [C.c_int] * 3; L.orc_java_search_ef.restype = C.c_int
         L.orc_hnsw_search.argtypes = [C.c_void_p, _f32p, C.c_int, C.c_int, _i32p, _f32p, _i64p, C.c_int]
         _lib = L
@@ -254,6 +255,18 @@ class OracleHnsw:
         present = np.empty(self.size, dtype=np.uint8)
         lib().orc_hnsw_get_level_adj(self.h, lvl, adj, present)
         return adj, present
+
+    def import_state(self, vecs, levels, adj, entry, ids=None, codebooks=None, codes=None):
+        """load vectors + graph (+ PQ state) built elsewhere; adj is [max_level][n][M]"""
+        v = _f32(vecs)
+        lv = np.ascontiguousarray(levels, dtype=np.int32)
+        a = np.ascontiguousarray(adj, dtype=np.int32)
+        assert a.shape == (self.max_level, v.shape[0], self.M), a.shape
+        idp = None if ids is None else np.ascontiguousarray(ids, dtype=np.int32).ctypes.data
+        cb = None if codebooks is None else _f32(codebooks)
+        cd = None if codes is None else np.ascontiguousarray(codes, dtype=np.uint8)
+        lib().orc_hnsw_import(self.h, v.shape[0], v, idp, lv, a, int(entry), None if cb is None else cb.ctypes.data,
+                              None if cd is None else cd.ctypes.data)
 
     def export_graph(self):
         """(levels[n], [adj_l[n][M] for l in range(max_level)], entry) in the layout vdb_set_graph takes."""

@@ -1,0 +1,386 @@
+"""GPU parity suite (-m gpu): every call goes through the C ABI (vector_db_b200._lib -> libvectordb.so) and is compared
+with the CPU oracle on the same seeded inputs, and with the golden vectors the unmodified reference produced
+(tests/golden/ref_native.npz). Bar: bit-exact ids / codes / codebooks / distances wherever the reference's reduction
+order is reproduced; traversal id agreement + Recall@10 within 0.5 pt for the HNSW walk (tolerances stated inline)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def bits(a):
+    return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+
+def recall(a, b):
+    return float(np.mean([len(set(x) & set(y)) / len(y) for x, y in zip(a, b)]))
+
+
+@pytest.fixture(scope="module")
+def v():
+    import __graft_entry__ as ge
+    ge.build_product()
+    import vector_db_b200
+    return vector_db_b200
+
+
+@pytest.fixture(scope="module")
+def torch():
+    import torch
+    return torch
+
+
+# ---------------------------------------------------------------- distances / generator
+def test_distance_orders_bit_exact(v, po, torch, golden_ref):
+    from vector_db_b200 import _lib
+    for d in (3, 8, 13, 64, 512, 1000):
+        a, b = po.synth(7, 20, d), po.synth(8, 20, d)
+        ta, tb = torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda()
+        for name, order in (("seq", 0), ("r1", 1), ("r2", 2)):
+            out = torch.empty(20, device="cuda")
+            _lib.check(_lib.lib().vdb_distance_device(ta.data_ptr(), tb.data_ptr(), 20, d, 0, order, out.data_ptr(), None))
+            torch.cuda.synchronize()
+            want = np.array([po.l2sq(a[i], b[i], order) for i in range(20)], dtype=np.float32)
+            assert np.array_equal(bits(out.cpu().numpy()), bits(want)), (name, d)
+            if d <= 64:
+                assert np.array_equal(bits(out.cpu().numpy()), bits(golden_ref["%s_%d" % (name, d)])), ("golden", name, d)
+        out = torch.empty(20, device="cuda")
+        _lib.check(_lib.lib().vdb_distance_device(ta.data_ptr(), tb.data_ptr(), 20, d, 1, 0, out.data_ptr(), None))
+        torch.cuda.synchronize()
+        want = np.array([1.0 - po.lib().orc_java_cosine_similarity(a[i], b[i], d) for i in range(20)], dtype=np.float32)
+        assert np.array_equal(bits(out.cpu().numpy()), bits(want))
+
+
+def test_synthetic_fill_matches_oracle_generator(v, po):
+    n, dim = 5000, 48
+    f = v.NativeFlatIndex(dim, n, id_offset=1000)
+    f.fill_synthetic(42, n)
+    X = po.fill_uniform(42, 1000 * dim, n * dim).reshape(n, dim)        # rows are keyed by GLOBAL row id
+    ids, d = f.searchBatch(X[[0, 17, 4999]], 1)
+    assert list(ids[:, 0]) == [1000, 1017, 5999] and (d[:, 0] == 0).all()
+    f.close()
+
+
+# ---------------------------------------------------------------- PQ: train / encode / LUT / ADC / top-k
+def test_pq_index_against_reference_golden(v, po, golden_ref):
+    n, dim, M, nq, k, ntrain = [int(x) for x in golden_ref["meta"]]
+    X, Q = po.synth(42, n, dim), po.synth(43, nq, dim)
+    p = v.NativePqIndex(dim, 4096, M=M)
+    with pytest.raises(v.VdbError):                              # PQIndex.cpp:124-126: add before train throws
+        p.addBatch(golden_ref["ids"], X)
+    ids, d = p.searchBatch(Q, k)                                  # untrained search: no hits (PQIndex.cpp:147-150)
+    assert (ids == -1).all() and np.isinf(d).all()
+    p.train(X[:ntrain])
+    assert np.array_equal(bits(p.codebooks()), bits(golden_ref["pq_codebooks"]))          # k-means bit-exact
+    p.addBatch(golden_ref["ids"], X)
+    assert np.array_equal(p.codes(), golden_ref["pq_codes"])                               # codes bit-exact
+    ids, d = p.searchBatch(Q, k)
+    assert np.array_equal(ids, golden_ref["pq_ids"])                                       # (dist,id) top-k
+    assert np.array_equal(bits(d), bits(golden_ref["pq_dists"]))                           # R2 LUT + R3 ADC bit-exact
+    p.close()
+    h = v.NativePqIndex(dim, 4096, M=M, train_flavour=v.TRAIN_NATIVE_HNSWPQ)
+    h.train(X[:ntrain])
+    assert np.array_equal(bits(h.codebooks()), bits(golden_ref["hnswpq_codebooks"]))       # mt19937 k-means++ bit-exact
+    h.addBatch(None, X[:256])
+    assert np.array_equal(h.codes(), golden_ref["hnswpq_codes"])
+    h.close()
+
+
+def test_pq_java_flavour_training(v, po, golden_java):
+    n, dim, M = [int(x) for x in golden_java["meta"][:3]]
+    X = po.synth(42, n, dim)
+    p = v.NativePqIndex(dim, 4096, M=M, train_flavour=v.TRAIN_JAVA, arith=v.ARITH_JAVA_SEQ)
+    p.train(X[:300])
+    assert np.array_equal(bits(p.codebooks()), bits(golden_java["java_codebooks"]))
+    # fewer samples than centroids: HnswPqIndex.java:266 stops seeding at c < n; the rest stay zero
+    p2 = v.NativePqIndex(dim, 4096, M=M, train_flavour=v.TRAIN_JAVA, arith=v.ARITH_JAVA_SEQ)
+    p2.train(X[:100])
+    assert np.array_equal(bits(p2.codebooks()), bits(po.pq_train(X[:100], M, 25, po.TRAIN_JAVA)))
+    p.close(); p2.close()
+
+
+@pytest.mark.parametrize("n,dim,M,nq,rerank", [(10000, 512, 64, 32, 0), (6000, 1000, 125, 16, 0), (6000, 1000, 125, 16, 200),
+                                                 (777, 128, 16, 5, 50)])
+def test_pq_flat_search_vs_oracle(v, po, n, dim, M, nq, rerank):
+    X, Q = po.synth(42, n, dim), po.synth(43, nq, dim)
+    k = 10
+    cb = po.pq_train(X[:600], M, 4, po.TRAIN_NATIVE_PQ)          # a few Lloyd passes are enough for a scan test
+    p = v.NativePqIndex(dim, n, M=M, rerank=rerank)
+    p.set_codebooks(cb)
+    p.addBatch(None, X)
+    codes = po.pq_encode(X, cb, po.ARITH_NATIVE_AVX2)
+    assert np.array_equal(p.codes(), codes)
+    ids, d = p.searchBatch(Q, k)
+    oi, od = po.pq_flat_search(Q, cb, codes, k, po.ARITH_NATIVE_AVX2, rerank=rerank, base=X if rerank else None, exact_order=1,
+                               nthreads=8)
+    assert np.array_equal(ids, oi)
+    assert np.array_equal(bits(d), bits(od))
+    p.close()
+
+
+def test_lut_and_adc_scan_kernels_bit_exact(v, po, torch):
+    from vector_db_b200 import _lib
+    n, dim, M = 4099, 1000, 125
+    X, Q = po.synth(42, n, dim), po.synth(43, 3, dim)
+    cb = po.pq_train(X[:300], M, 2, po.TRAIN_NATIVE_PQ)
+    p = v.NativePqIndex(dim, n, M=M)
+    p.set_codebooks(cb)
+    p.addBatch(None, X)
+    tq = torch.from_numpy(Q).cuda()
+    lut = torch.empty((3, M, 256), device="cuda")
+    _lib.check(_lib.lib().vdb_pq_lut_device(p._h, tq.data_ptr(), 3, lut.data_ptr(), None))
+    torch.cuda.synchronize()
+    want = np.stack([po.pq_lut(Q[i], cb, po.ARITH_NATIVE_AVX2) for i in range(3)])
+    assert np.array_equal(bits(lut.cpu().numpy()), bits(want))
+    out = torch.empty(n, device="cuda")
+    _lib.check(_lib.lib().vdb_adc_scan_device(p._h, lut[1].contiguous().data_ptr(), out.data_ptr(), None))
+    torch.cuda.synchronize()
+    assert np.array_equal(bits(out.cpu().numpy()), bits(po.adc_scan(want[1], po.pq_encode(X, cb, po.ARITH_NATIVE_AVX2))))
+    p.close()
+
+
+# ---------------------------------------------------------------- flat exact search
+@pytest.mark.parametrize("metric,arith", [(0, 0), (0, 1), (1, 0)])
+def test_flat_exact_search_bit_exact(v, po, metric, arith):
+    n, dim, nq, k = 20000, 96, 24, 100
+    X, Q = po.synth(42, n, dim), po.synth(43, nq, dim)
+    ids_ext = (np.arange(n, dtype=np.int32) * 13 + 5) % 100003
+    f = v.NativeFlatIndex(dim, n, metric=metric, arith=arith)
+    f.addBatch(ids_ext, X)
+    ids, d = f.searchBatch(Q, k)
+    if metric == 1:
+        oi, od = po.flat_search(po.java_normalize(X), po.java_normalize(Q), k, metric=1, ids=ids_ext, nthreads=8)
+    else:
+        oi, od = po.flat_search(X, Q, k, metric=0, order=arith, ids=ids_ext, nthreads=8)
+    assert np.array_equal(ids, oi)
+    assert np.array_equal(bits(d), bits(od))
+    f.close()
+
+
+def test_flat_ties_broken_by_id_and_padding(v, po):
+    dim = 16
+    base = np.zeros((6, dim), dtype=np.float32)
+    base[3:] = 1.0
+    f = v.NativeFlatIndex(dim, 10)
+    f.addBatch(np.array([50, 40, 30, 20, 10, 5], dtype=np.int32), base)
+    ids, d = f.searchBatch(np.zeros((1, dim), dtype=np.float32), 8)
+    assert list(ids[0]) == [30, 40, 50, 5, 10, 20, -1, -1]          # (dist,id) order; unused slots -1 / +inf
+    assert np.isinf(d[0, 6:]).all() and (d[0, :3] == 0).all()
+    f.close()
+
+
+# ---------------------------------------------------------------- HNSW(+PQ) traversal
+def _load_oracle_state(g, o, codes=None):
+    g.set_codebooks(o.codebooks())
+    levels, adj, entry = o.export_graph()
+    g.set_graph(levels, adj, entry)
+    if codes is not None:
+        g.set_codes(codes)
+
+
+def test_hnswpq_golden_same_graph_same_codebooks(v, po, golden_java):
+    n, dim, M, nq, k, maxel = [int(x) for x in golden_java["meta"]]
+    X, Q = po.synth(42, n, dim), po.synth(43, nq, dim)
+    g = v.NativeHnswPqIndex(dim, maxel, pqM=M)
+    g.addBatch(None, X)
+    g.set_codebooks(golden_java["hp_codebooks"])
+    g.set_graph(golden_java["hp_levels"], list(golden_java["hp_adj"]), int(golden_java["hp_entry"][0]))
+    g.set_codes(golden_java["hp_codes"])            # incremental build: the first 149 rows carry all-zero codes
+    ids, d = g.searchBatch(Q, k)
+    assert np.array_equal(ids, golden_java["hp_ids"])
+    assert np.array_equal(bits(d), bits(golden_java["hp_dists"]))          # re-scored in Java's sequential order
+    g.close()
+
+
+def test_hnsw_cosine_golden(v, po, golden_java):
+    n, dim, M, nq, k, maxel = [int(x) for x in golden_java["meta"]]
+    X, Q = po.synth(42, n, dim), po.synth(43, nq, dim)
+    g = v.NativeHnswIndex(dim, maxel)
+    g.addBatch(None, X)
+    g.set_graph(golden_java["hc_levels"], list(golden_java["hc_adj"]), int(golden_java["hc_entry"][0]))
+    ids, d = g.searchBatch(Q, k)
+    assert np.array_equal(ids, golden_java["hc_ids"])
+    assert np.array_equal(bits(d), bits(golden_java["hc_dists"]))
+    g.close()
+
+
+@pytest.mark.parametrize("n,dim,M,rebuilt", [(10000, 128, 16, False), (4000, 512, 64, True)])
+def test_hnswpq_traversal_vs_oracle(v, po, n, dim, M, rebuilt):
+    """Same graph, same codebooks, same codes -> the GPU walk must return what the Java-semantics oracle returns.
+    Layer-0 distances use the warp-tree order (1e-5 relative of Java's), so: (a) against the oracle run with the SAME
+    arithmetic the result must be identical; (b) against the Java-order oracle ids may differ only on near-ties
+    (>= 99.5 % equal) and Recall@10 must be within 0.5 pt."""
+    nq, k = 200, 10
+    X, Q = po.synth(42, n, dim), po.synth(43, nq, dim)
+    o = po.OracleHnsw(po.KIND_HNSWPQ, dim, 2 * n, pq_m=M, level_seed=5)
+    o.add_batch(X)
+    if rebuilt:
+        o.rebuild()
+    g = v.NativeHnswPqIndex(dim, 2 * n, pqM=M)
+    g.addBatch(None, X)
+    _load_oracle_state(g, o, o.codes())
+    ids, d = g.searchBatch(Q, k)
+    jid, jd, jst = o.search(Q, k, nthreads=8)
+    o.set_arith(po.ARITH_GPU_TREE)
+    tid, td, tst = o.search(Q, k, nthreads=8)
+    assert np.array_equal(ids, tid) and np.array_equal(bits(d), bits(td))                 # (a) logic parity, exact
+    assert (ids == jid).mean() >= 0.995                                                     # (b) arithmetic parity
+    same = ids == jid
+    assert np.array_equal(bits(d[same]), bits(jd[same]))
+    gt, _ = po.flat_search(X, Q, k, nthreads=8)
+    assert abs(recall(ids, gt) - recall(jid, gt)) <= 0.005
+    assert recall(ids, gt) >= 0.95
+    st = g.stats()
+    assert abs(st["dist_evals"] / nq - tst[0] / nq) / (tst[0] / nq) < 0.02                  # same amount of work as the oracle
+    g.close()
+
+
+def test_hnsw_cosine_traversal_vs_oracle(v, po):
+    n, dim, nq, k = 10000, 128, 200, 10
+    X, Q = po.synth(42, n, dim), po.synth(43, nq, dim)
+    o = po.OracleHnsw(po.KIND_HNSW, dim, n, level_seed=5)
+    o.add_batch(X)
+    g = v.NativeHnswIndex(dim, n)
+    g.addBatch(None, X)
+    levels, adj, entry = o.export_graph()
+    g.set_graph(levels, adj, entry)
+    ids, d = g.searchBatch(Q, k)
+    jid, jd, _ = o.search(Q, k)
+    o.set_arith(po.ARITH_GPU_TREE)
+    tid, td, _ = o.search(Q, k)
+    assert np.array_equal(ids, tid) and np.array_equal(bits(d), bits(td))
+    assert (ids == jid).mean() >= 0.99
+    g.close()
+
+
+def test_untrained_hnswpq_and_product_built_graph(v, po):
+    """The library's own build path (host insert + GPU k-means + GPU encode), incremental like Java's addVector:
+    before the training trigger the index answers through searchLayer with exact distances (HnswPqIndex.java:643)."""
+    n, dim, M, nq, k = 3000, 64, 8, 100, 10
+    X, Q = po.synth(42, n, dim), po.synth(43, nq, dim)
+    g = v.NativeHnswPqIndex(dim, 2 * n, pqM=M, level_seed=77)
+    g.addBatch(None, X[:300])
+    assert not g.trained
+    ids, d = g.searchBatch(Q, k)
+    gt, _ = po.flat_search(X[:300], Q, k)
+    assert recall(ids, gt) >= 0.95
+    g.addBatch(None, X[300:])
+    ids, d = g.searchBatch(Q, k)
+    assert g.trained                                        # training fired at min(10000, maxElements/10) = 600 rows
+    gt, gd = po.flat_search(X, Q, k)
+    o = po.OracleHnsw(po.KIND_HNSWPQ, dim, 2 * n, pq_m=M, level_seed=77)
+    o.add_batch(X)
+    jid, _, _ = o.search(Q, k)
+    assert abs(recall(ids, gt) - recall(jid, gt)) <= 0.005  # Recall@10 within 0.5 pt of the reference algorithm
+    assert np.array_equal(bits(g.codebooks()), bits(o.codebooks()))       # GPU k-means == Java k-means, bit for bit
+    assert np.array_equal(g.codes(), o.codes())                            # incl. the all-zero codes of the 599 raw rows
+    assert g.buildIndex()
+    ids2, d2 = g.searchBatch(Q, k)
+    o.rebuild()
+    assert np.array_equal(g.codes(), o.codes())
+    jid2, _, _ = o.search(Q, k)
+    assert abs(recall(ids2, gt) - recall(jid2, gt)) <= 0.005
+    same = ids2 == gt
+    assert np.array_equal(bits(d2[same]), bits(gd[same]))
+    g.close()
+
+
+# ---------------------------------------------------------------- edges, snapshot, merge, façade
+def test_edge_cases(v, po):
+    dim = 32
+    g = v.NativeHnswPqIndex(dim, 100, pqM=4)
+    ids, d = g.searchBatch(np.zeros((2, dim), dtype=np.float32), 5)       # empty index -> empty lists
+    assert (ids == -1).all() and np.isinf(d).all()
+    assert g.searchNearest(np.zeros(dim, dtype=np.float32), 5) == []
+    X = po.synth(1, 7, dim)
+    g.addBatch(np.arange(7, dtype=np.int32) + 100, X)
+    ids, d = g.searchBatch(X[:2], 10)                                       # k > n: 7 hits then padding
+    assert (ids[:, :7] >= 100).all() and (ids[:, 7:] == -1).all() and ids[0, 0] == 100 and ids[1, 0] == 101
+    ids0, d0 = g.searchBatch(np.zeros((0, dim), dtype=np.float32), 3)       # ragged: empty batch
+    assert ids0.shape == (0, 3)
+    with pytest.raises(ValueError):
+        g.searchBatch(np.zeros((1, dim + 1), dtype=np.float32), 3)
+    with pytest.raises(ValueError):
+        g.searchBatch(X[:1], 0)
+    with pytest.raises(ValueError):
+        g.addVector(1, np.zeros(dim - 1, dtype=np.float32))
+    g.addBatch(None, po.synth(2, 93, dim))
+    assert g.size() == 100
+    assert g.addVector(5000, X[0]) is False                                 # capacity reached -> false (HnswPqIndex.java:162)
+    g.close()
+    with pytest.raises(v.VdbError):
+        v.NativePqIndex(30, 10, M=8)                                        # Dimension must be divisible by M
+
+
+def test_snapshot_round_trip(v, po, tmp_path):
+    n, dim, M = 1200, 32, 4
+    X, Q = po.synth(42, n, dim), po.synth(43, 20, dim)
+    g = v.NativeHnswPqIndex(dim, 2 * n, pqM=M)
+    g.addBatch(None, X)
+    ids, d = g.searchBatch(Q, 10)
+    path = tmp_path / "idx.vdb"
+    g.save(path)
+    h = v.NativeHnswPqIndex(dim, 2 * n, pqM=M)
+    h.load(path)
+    assert h.size() == n and h.trained
+    ids2, d2 = h.searchBatch(Q, 10)
+    assert np.array_equal(ids, ids2) and np.array_equal(bits(d), bits(d2))
+    assert np.array_equal(g.codes(), h.codes())
+    g.close(); h.close()
+
+
+def test_sharded_merge_kernel(v, po, torch):
+    from vector_db_b200 import _lib
+    from vector_db_b200.sharded import merge_topk_host, plan_shards
+    n, dim, nq, k, gsz = 9001, 64, 33, 10, 4
+    X, Q = po.synth(42, n, dim), po.synth(43, nq, dim)
+    parts_d, parts_i = [], []
+    tq = torch.from_numpy(Q).cuda()
+    for lo, hi in plan_shards(n, gsz):
+        f = v.NativeFlatIndex(dim, hi - lo, id_offset=lo)
+        f.fill_synthetic(42, hi - lo)                                       # every shard generates its own rows in HBM
+        i, d = f.search_device(tq, k)
+        parts_i.append(i); parts_d.append(d)
+        f.close()
+    all_d, all_i = torch.stack(parts_d).contiguous(), torch.stack(parts_i).contiguous()
+    out_d = torch.empty((nq, k), device="cuda"); out_i = torch.empty((nq, k), dtype=torch.int32, device="cuda")
+    _lib.check(_lib.lib().vdb_merge_topk_device(all_d.data_ptr(), all_i.data_ptr(), gsz, nq, k, out_d.data_ptr(), out_i.data_ptr(),
+                                                torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+    gi, gd = po.flat_search(X, Q, k, nthreads=8)
+    assert np.array_equal(out_i.cpu().numpy(), gi) and np.array_equal(bits(out_d.cpu().numpy()), bits(gd))
+    hd, hi_ = merge_topk_host(all_d.cpu().numpy(), all_i.cpu().numpy(), k)
+    assert np.array_equal(hi_, gi)
+
+
+def test_vector_database_facade_like_integration_test(v, po):
+    # VectorDatabaseIntegrationTest.java:121-165 — planted target is found; RecallOptimizationTest.java:100 — exactly K
+    dim, n = 64, 1500
+    db = (v.VectorDatabase.Builder().withDimension(dim).withMaxElements(2 * n)
+          .withCompression(v.CompressionConfig.recommendedConfig(dim)).build())
+    X = po.synth(42, n, dim)
+    for i in range(50):
+        assert db.addVector(i, X[i])
+    assert db.addVector(3, X[3]) is False                                   # duplicate id
+    db.addVectors(np.arange(50, n), X[50:])
+    target = np.ones(dim, dtype=np.float32)
+    db.addVector(99999, target)
+    res = db.search(np.full(dim, 0.9, dtype=np.float32), 5)
+    assert len(res) == 5 and res[0].id == 99999
+    assert all(res[i].distance <= res[i + 1].distance for i in range(4))
+    with pytest.raises(ValueError):
+        db.search(np.zeros(dim + 1), 5)
+    assert db.rebuildIndex()
+    res = db.search(np.full(dim, 0.9, dtype=np.float32), 5)
+    assert res[0].id == 99999 and db.size() == n + 1
+    db.close()
+    plain = v.VectorDatabase.Builder().withDimension(10).withMaxElements(1000).withIndexType(v.IndexType.HNSW).build()
+    rng = np.random.default_rng(42)
+    Y = (rng.random((100, 10)) * 2 - 1).astype(np.float32)
+    plain.addVectors(np.arange(100), Y)
+    plain.addVector(777, np.ones(10, dtype=np.float32))
+    r = plain.search(np.full(10, 0.9, dtype=np.float32), 10)                # HnswIndexTest.java:135-164
+    assert len(r) == 10 and r[0].id == 777
+    plain.close()

@@ -1,0 +1,76 @@
+"""Multi-GPU sharding of the flat / PQ query path: one process per GPU (torch.distributed), base
+vectors and PQ codes split by contiguous id range, query batch replicated, every rank returns its local top-k with
+GLOBAL ids, and only those small lists cross NVLink: one all_gather of [nq][k] (dist,id) per rank followed by the
+(dist,id) merge kernel (vdb_merge_topk_device). The reference has no multi-device path at all (SURVEY.md §2
+"Parallelism / communication components: none exist"); this is new design, the merge order is the reference's
+(dist,id) rule (PQIndex.cpp:200-205).
+
+HNSW graphs do not shard by id range (a walk touches arbitrary nodes): for those, `shard_queries` splits the QUERY
+batch over replicas and gathers the results — no data-path collective."""
+import numpy as np
+
+
+def plan_shards(n_total, world_size):
+    """contiguous id ranges [start, stop) per rank; sizes differ by at most one row"""
+    base, rem = divmod(int(n_total), int(world_size))
+    out, start = [], 0
+    for r in range(world_size):
+        size = base + (1 if r < rem else 0)
+        out.append((start, start + size))
+        start += size
+    return out
+
+
+def shard_queries(nq, world_size):
+    return plan_shards(nq, world_size)
+
+
+def merge_topk_host(dists, ids, k):
+    """numpy statement of the merge rule, used by the CPU (gloo) tests and as documentation of the kernel's contract:
+    dists/ids [g][nq][k] -> [nq][k] ordered by (dist, id); id < 0 = empty slot."""
+    g, nq, kk = dists.shape
+    d = np.transpose(dists, (1, 0, 2)).reshape(nq, g * kk)
+    i = np.transpose(ids, (1, 0, 2)).reshape(nq, g * kk)
+    out_d = np.full((nq, k), np.inf, dtype=np.float32)
+    out_i = np.full((nq, k), -1, dtype=np.int32)
+    for q in range(nq):
+        valid = i[q] >= 0
+        order = np.lexsort((i[q][valid], d[q][valid]))[:k]
+        out_d[q, :order.size] = d[q][valid][order]
+        out_i[q, :order.size] = i[q][valid][order]
+    return out_d, out_i
+
+
+class ShardedSearcher:
+    """Wraps one local GpuIndex shard per rank. `search(d_queries, k)` returns the merged global top-k on every rank."""
+
+    def __init__(self, local_index, rank, world_size, group=None, merge_fn=None):
+        self.index, self.rank, self.world, self.group = local_index, rank, world_size, group
+        self._merge_fn = merge_fn            # injectable for CPU tests; default = CUDA merge kernel
+
+    def _merge(self, all_d, all_i, k):
+        if self._merge_fn is not None:
+            return self._merge_fn(all_d, all_i, k)
+        import torch
+        from . import _lib
+        g, nq, _ = all_d.shape
+        out_d = torch.empty((nq, k), dtype=torch.float32, device=all_d.device)
+        out_i = torch.empty((nq, k), dtype=torch.int32, device=all_d.device)
+        st = torch.cuda.current_stream(all_d.device).cuda_stream
+        _lib.check(_lib.lib().vdb_merge_topk_device(all_d.data_ptr(), all_i.data_ptr(), g, nq, k, out_d.data_ptr(),
+                                                    out_i.data_ptr(), st))
+        return out_d, out_i
+
+    def search(self, d_queries, k, local_search=None):
+        import torch
+        import torch.distributed as dist
+        ids, d = (local_search or self.index.search_device)(d_queries, k)
+        if self.world == 1:
+            return ids, d
+        nq = d.shape[0]
+        all_d = torch.empty((self.world * nq, k), dtype=d.dtype, device=d.device)
+        all_i = torch.empty((self.world * nq, k), dtype=ids.dtype, device=ids.device)
+        dist.all_gather_into_tensor(all_d, d.contiguous(), group=self.group)      # rank-major concatenation
+        dist.all_gather_into_tensor(all_i, ids.contiguous(), group=self.group)
+        out_d, out_i = self._merge(all_d.view(self.world, nq, k), all_i.view(self.world, nq, k), k)
+        return out_i, out_d
