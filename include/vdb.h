@@ -39,6 +39,7 @@ enum {
     VDB_INDEX_HNSW_PQ = 3  /* Java HnswPqIndex: sq-L2, PQ upper layers, exact layer 0 + rerank (index/HnswPqIndex.java) */
 };
 enum { VDB_METRIC_SQL2 = 0, VDB_METRIC_COSINE = 1 };
+enum { VDB_TRAV_BF16 = 0, VDB_TRAV_F32 = 1 };
 /* fp32 reduction order of the reference implementation being reproduced */
 enum {
     VDB_ARITH_JAVA_SEQ = 0,    /* sequential, mul then add (HnswPqIndex.java:741-750, :343-350) */
@@ -67,8 +68,12 @@ typedef struct vdb_config {
     int32_t rerank;          /* PQ index: exact re-score of the best `rerank` ADC candidates (0 = none, as PQIndex.cpp) */
     int32_t device;          /* CUDA ordinal */
     int32_t id_offset;       /* multi-GPU id-range sharding: this shard holds global rows [id_offset, id_offset+n) */
-    int32_t reserved0;
+    int32_t search_ef_cap;   /* HNSW_PQ: cap of the layer-0 beam; 0 = 5000, the constant of HnswPqIndex.java:621 */
     uint64_t level_seed;     /* seeded stand-in for ThreadLocalRandom level draws (HnswPqIndex.java:752-759) */
+    int32_t trav_store;      /* HNSW*: rows read during traversal: 0 = bf16 copy (default), 1 = fp32 (strict order) */
+    int32_t trav_batch;      /* HNSW*: candidates expanded per round: 0 = auto (ef/128 in [4,32]), 1 = the Java pop order */
+    int32_t reserved1;
+    int32_t reserved2;
 } vdb_config;
 
 typedef struct vdb_stats {
@@ -99,7 +104,8 @@ int vdb_build(vdb_index* idx);
 /* nativeSearch / nativeSearchBatch (VectorDBJNI.cpp:141-159,184-200): HOST buffers; queries[nq][dim],
  * out_ids[nq][k], out_dists[nq][k] */
 int vdb_search_batch(vdb_index* idx, const float* queries, int64_t nq, int32_t k, int32_t* out_ids, float* out_dists);
-/* same with DEVICE buffers on `stream` (a cudaStream_t; NULL = the index's own stream): no host copies */
+/* same with DEVICE buffers on `stream` (a cudaStream_t taken verbatim: NULL = CUDA's legacy default stream, which is
+ * also torch's default stream): no host copies, nothing is synchronised */
 int vdb_search_batch_device(vdb_index* idx, const float* d_queries, int64_t nq, int32_t k, int32_t* d_ids,
                             float* d_dists, void* stream);
 int64_t vdb_size(const vdb_index* idx);

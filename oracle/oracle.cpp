@@ -113,9 +113,9 @@ static inline float l2sq_gpu(const float* a, const float* b, int d) {
             lane[l] = fmaf(diff, diff, lane[l]);
         }
     }
-    for (int i = nch * 4; i < d; i++) {           // ragged tail: element i on lane (i-nch*4)
+    for (int i = nch * 4; i < d; i++) {           // ragged tail: rows are zero-padded, so it is one more (partial) chunk
         float diff = a[i] - b[i];
-        int l = (i - nch * 4) & 31;
+        int l = nch & 31;
         lane[l] = fmaf(diff, diff, lane[l]);
     }
     return warp_tree(lane);
@@ -133,7 +133,7 @@ static inline float dot_gpu(const float* a, const float* b, int d) {
         int l = c & 31;
         for (int e = 0; e < 4; e++) lane[l] = fmaf(a[4 * c + e], b[4 * c + e], lane[l]);
     }
-    for (int i = nch * 4; i < d; i++) { int l = (i - nch * 4) & 31; lane[l] = fmaf(a[i], b[i], lane[l]); }
+    for (int i = nch * 4; i < d; i++) { int l = nch & 31; lane[l] = fmaf(a[i], b[i], lane[l]); }
     return warp_tree(lane);
 }
 // core/Vector.java:93-102 — sqrt of the sequential sum of squares ((float)Math.sqrt(double) of a
@@ -515,6 +515,7 @@ struct Hnsw {
     int kind, dim, maxElements, M = 32, efC, ef, maxLevel;
     uint64_t level_seed, level_ctr = 0;
     int arith = 0;                  // 0 = Java sequential (reference), 2 = product's warp-tree order
+    int efCap = 5000;               // HnswPqIndex.java:621 hard-codes 5000; settable only for the recall-vs-ef study (bench.py)
     // PQ
     int pqM = 0, ncent = 256, pqIters = 25, sd = 0;
     bool trained = false;
@@ -772,14 +773,15 @@ ORC_API void orc_hnsw_get_level_adj(void* p, int lvl, int32_t* adj, uint8_t* pre
     }
 }
 
-static inline int java_search_ef(int n, int k, int ef) {           // HnswPqIndex.java:616-621
+static inline int java_search_ef(int n, int k, int ef, int cap = 5000) {   // HnswPqIndex.java:616-621
     int byRatio = (int)(n * 0.15);
     int byK = k * 100;
     int s = std::max(std::max(byRatio, byK), ef);
     s = std::min(s, n);
-    return std::min(s, 5000);
+    return std::min(s, cap);
 }
 ORC_API int orc_java_search_ef(int n, int k, int ef) { return java_search_ef(n, k, ef); }
+ORC_API void orc_hnsw_set_ef_cap(void* p, int cap) { ((Hnsw*)p)->efCap = cap > 0 ? cap : 5000; }
 
 // searchNearest: HnswPqIndex.java:599-669 / HnswIndex.java:328-365. stats[0]=distance evals, [1]=expansions.
 static void hnsw_search_one(const Hnsw& h, Hnsw::Scratch& sc, const float* qin, int k, int32_t* out_ids, float* out_d, int64_t* stats) {
@@ -791,7 +793,7 @@ static void hnsw_search_one(const Hnsw& h, Hnsw::Scratch& sc, const float* qin, 
     int cur = h.entry;
     std::vector<Cand> cands;
     if (h.kind == 0) {
-        int searchEf = java_search_ef(h.size(), k, h.ef);
+        int searchEf = java_search_ef(h.size(), k, h.ef, h.efCap);
         for (int l = h.maxLevel - 1; l > 0; l--) cur = search_closest(h, q, qn, cur, l, h.trained, &st);
         if (h.trained) search_layer(h, sc, q, qn, cur, std::max(searchEf, k * 100), 0, 0, cands, &st);
         else search_layer(h, sc, q, qn, cur, searchEf, 0, 1, cands, &st);

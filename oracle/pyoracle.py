@@ -59,6 +59,7 @@ def lib():
         L.orc_hnsw_create.argtypes = [C.c_int] * 8 + [C.c_uint64]; L.orc_hnsw_create.restype = C.c_void_p
         L.orc_hnsw_destroy.argtypes = [C.c_void_p]
         L.orc_hnsw_set_arith.argtypes = [C.c_void_p, C.c_int]
+        L.orc_hnsw_set_ef_cap.argtypes = [C.c_void_p, C.c_int]
         L.orc_hnsw_add.argtypes = [C.c_void_p, C.c_int, _f32p]; L.orc_hnsw_add.restype = C.c_int
         L.orc_hnsw_add_batch.argtypes = [C.c_void_p, C.c_void_p, _f32p, C.c_int64]
         L.orc_hnsw_rebuild.argtypes = [C.c_void_p]
@@ -197,6 +198,10 @@ class OracleHnsw:
 
     def set_arith(self, arith):
         lib().orc_hnsw_set_arith(self.h, arith)
+
+    def set_ef_cap(self, cap):
+        """searchEf cap (HnswPqIndex.java:621 hard-codes 5000); other values are a documented extension"""
+        lib().orc_hnsw_set_ef_cap(self.h, int(cap))
 
     def add_batch(self, vecs, ids=None):
         v = _f32(vecs)

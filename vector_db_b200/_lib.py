@@ -11,6 +11,7 @@ INDEX_FLAT, INDEX_PQ, INDEX_HNSW, INDEX_HNSW_PQ = 0, 1, 2, 3
 METRIC_SQL2, METRIC_COSINE = 0, 1
 ARITH_JAVA_SEQ, ARITH_NATIVE_AVX2 = 0, 1
 TRAIN_JAVA, TRAIN_NATIVE_HNSWPQ, TRAIN_NATIVE_PQ = 0, 1, 2
+TRAV_BF16, TRAV_F32 = 0, 1
 
 # every symbol include/vdb.h declares (checked by tests/test_abi.py)
 SYMBOLS = [
@@ -25,7 +26,8 @@ SYMBOLS = [
 class VdbConfig(C.Structure):
     _fields_ = [(n, C.c_int32) for n in (
         "dim", "max_elements", "index_type", "metric", "arith", "hnsw_m", "ef_construction", "ef_search", "pq_m", "pq_bits",
-        "pq_iters", "train_flavour", "rerank", "device", "id_offset", "reserved0")] + [("level_seed", C.c_uint64)]
+        "pq_iters", "train_flavour", "rerank", "device", "id_offset", "search_ef_cap")] + [("level_seed", C.c_uint64)] + [
+        (n, C.c_int32) for n in ("trav_store", "trav_batch", "reserved1", "reserved2")]
 
 
 class VdbStats(C.Structure):

@@ -22,7 +22,8 @@ void launch_distance(const float* d_a, const float* d_b, int64_t n, int dim, int
 
 // hnsw_kernels.cu
 struct HnswSearchParams {
-    const float* base;        // [n][dim]; normalised rows for cosine
+    const float* base;        // [n][dim]; normalised rows for cosine (exact re-score, greedy descent)
+    const void* tbase;        // traversal rows [n][tstride bytes]: fp32 or bf16, zero-padded to a multiple of 8 elements
     const float* norms;       // [n] Java norm of the stored row (cosine), else nullptr
     const int32_t* ids;       // [n] external ids
     const int32_t* adj;       // [max_level][n][deg], -1 padded
@@ -37,11 +38,15 @@ struct HnswSearchParams {
     int pq_m, trained;
     int metric;               // 0 sq-L2 (HnswPqIndex), 1 cosine (HnswIndex)
     int variant;              // 0 searchLayerWithSize, 1 HnswPqIndex.searchLayer, 2 HnswIndex.searchLayer
-    int ef, cap, k, nq;
+    int ef, k, nq;
+    int tstride, tstore;      // bytes per traversal row (multiple of 16); 0 = fp32, 1 = bf16
+    int batch;                // candidates expanded per round (1 = the Java order)
     int visited_in_smem;
 };
 int launch_hnsw_search(const HnswSearchParams& p, int grid, cudaStream_t st);
 size_t hnsw_search_smem_bytes(const HnswSearchParams& p);
+int hnsw_max_batch(int deg);
+void launch_make_traversal_rows(const float* d_base, int64_t n, int dim, int dpad, int bf16, void* d_out, cudaStream_t st);
 
 // flat_kernels.cu
 void launch_flat_search_exact(const float* d_base, const float* d_norms, const int32_t* d_ids, int id_offset, int64_t n, int dim,

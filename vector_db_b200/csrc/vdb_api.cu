@@ -92,7 +92,7 @@ extern "C" int vdb_destroy(vdb_index* x) {
     if (x->stream) cudaStreamSynchronize(x->stream);
     x->d_base.release(); x->d_norms.release(); x->d_cb.release(); x->d_ids.release(); x->d_adj.release(); x->d_codes.release();
     x->d_q.release(); x->d_out_d.release(); x->d_lut.release(); x->d_out_ids.release(); x->d_keys.release(); x->d_keys_tmp.release();
-    x->d_rows.release(); x->d_rows_tmp.release(); x->d_visited.release(); x->d_counters.release();
+    x->d_rows.release(); x->d_rows_tmp.release(); x->d_visited.release(); x->d_counters.release(); x->d_trav.release();
     x->d_train.release(); x->d_sub.release(); x->d_mind.release(); x->d_asg.release();
     x->p_q.release(); x->p_d.release(); x->p_ids.release();
     if (x->ev_total0) { cudaEventDestroy(x->ev_total0); cudaEventDestroy(x->ev_total1); cudaEventDestroy(x->ev_k0); cudaEventDestroy(x->ev_k1); }
@@ -122,6 +122,21 @@ static int upload_rows(vdb_index* x) {
     }
     VDB_CUDA(cudaStreamSynchronize(x->stream));
     x->n_dev = x->n;
+    return VDB_OK;
+}
+
+// traversal copy of rows [n_trav, n_dev): zero-padded to 8 elements, bf16 (default) or fp32 (strict mode)
+static inline int trav_dpad(const vdb_index* x) { return (x->cfg.dim + 7) & ~7; }
+static inline int trav_stride(const vdb_index* x) { return trav_dpad(x) * (x->cfg.trav_store == VDB_TRAV_F32 ? 4 : 2); }
+static int build_traversal_rows(vdb_index* x) {
+    if (x->n_trav >= x->n_dev) return VDB_OK;
+    const size_t stride = (size_t)trav_stride(x);
+    VDB_TRY(x->d_trav.ensure((size_t)x->n_dev * stride, (size_t)x->n_trav * stride, x->stream));
+    launch_make_traversal_rows(x->d_base.p + (size_t)x->n_trav * x->cfg.dim, x->n_dev - x->n_trav, x->cfg.dim, trav_dpad(x),
+                               x->cfg.trav_store == VDB_TRAV_F32 ? 0 : 1, x->d_trav.p + (size_t)x->n_trav * stride, x->stream);
+    VDB_CUDA(cudaGetLastError());
+    VDB_CUDA(cudaStreamSynchronize(x->stream));
+    x->n_trav = x->n_dev;
     return VDB_OK;
 }
 
@@ -209,6 +224,7 @@ static int sync_index(vdb_index* x) {
             x->graph_uploaded = false;
         }
         VDB_TRY(upload_rows(x));
+        VDB_TRY(build_traversal_rows(x));
         if (t == VDB_INDEX_HNSW_PQ) VDB_TRY(encode_pending(x));
         if (!x->graph_uploaded) VDB_TRY(upload_graph(x));
     } else {
@@ -355,7 +371,7 @@ extern "C" int vdb_build(vdb_index* x) {
         x->h_vecs.swap(nv); x->h_ids.swap(ni); x->h_norms.swap(nn);
     }
     x->g.clear();
-    x->n_indexed = 0; x->n_dev = 0; x->n_coded = 0; x->raw_rows = 0; x->codes_overridden = false;
+    x->n_indexed = 0; x->n_dev = 0; x->n_trav = 0; x->n_coded = 0; x->raw_rows = 0; x->codes_overridden = false;
     return sync_index(x);
 }
 
@@ -382,11 +398,11 @@ extern "C" int vdb_fill_synthetic(vdb_index* x, uint64_t seed, int64_t cnt) {
 }
 
 // ---- search ---------------------------------------------------------------------------------------------------
-static inline int java_search_ef(int64_t n, int k, int ef) {     // HnswPqIndex.java:616-621
+static inline int java_search_ef(int64_t n, int k, int ef, int cap) {     // HnswPqIndex.java:616-621 (cap = 5000 there)
     int byRatio = (int)((double)n * 0.15);
     int s = std::max(std::max(byRatio, k * 100), ef);
     s = (int)std::min<int64_t>(s, n);
-    return std::min(s, 5000);
+    return std::min(s, cap > 0 ? cap : 5000);
 }
 
 static int search_graph(vdb_index* x, const float* d_q, int64_t nq, int k, int32_t* d_ids, float* d_dists, cudaStream_t st) {
@@ -399,17 +415,20 @@ static int search_graph(vdb_index* x, const float* d_q, int64_t nq, int k, int32
     p.pq_m = x->pq_m; p.trained = pq && x->trained ? 1 : 0;
     p.metric = pq ? 0 : 1;
     if (pq) {
-        const int sef = java_search_ef(x->n, k, x->cfg.ef_search);
+        const int sef = java_search_ef(x->n, k, x->cfg.ef_search, x->cfg.search_ef_cap);
         if (x->trained) { p.variant = 0; p.ef = std::max(sef, k * 100); }     // :638-640 searchLayerWithSize
         else { p.variant = 1; p.ef = sef; }                                    // :643 searchLayer
     } else { p.variant = 2; p.ef = std::max(x->cfg.ef_search, k * 4); }        // HnswIndex.java:347
-    p.cap = next_pow2(p.ef + 64);
+    p.ef = (int)std::min<int64_t>(p.ef, std::max<int64_t>(x->n, 1));
     p.k = k; p.nq = (int)nq;
+    p.tbase = x->d_trav.p; p.tstride = trav_stride(x); p.tstore = x->cfg.trav_store == VDB_TRAV_F32 ? 0 : 1;
+    p.batch = x->cfg.trav_batch > 0 ? x->cfg.trav_batch : std::max(4, std::min(32, p.ef / 128));
+    p.batch = std::max(1, std::min(p.batch, hnsw_max_batch(p.deg)));
     p.visited_in_smem = 1;
     size_t smem = hnsw_search_smem_bytes(p);
-    if (smem > 200 * 1024) { p.visited_in_smem = 0; smem = hnsw_search_smem_bytes(p); }
+    if (smem > 110 * 1024) { p.visited_in_smem = 0; smem = hnsw_search_smem_bytes(p); }
     if (smem > 227 * 1024) FAIL(VDB_ERR_INVALID, "ef too large for the shared-memory pool");
-    int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (227 * 1024) / (smem + 1024)));
+    int per_sm = (int)std::max<size_t>(1, std::min<size_t>(2, (227 * 1024) / (smem + 1024)));
     int grid = (int)std::min<int64_t>(nq, (int64_t)x->num_sms * per_sm);
     if (!p.visited_in_smem) {
         VDB_TRY(x->d_visited.ensure((size_t)grid * ((x->n + 31) / 32), 0, st));
@@ -510,7 +529,7 @@ static int search_device_locked(vdb_index* x, const float* d_q, int64_t nq, int 
 extern "C" int vdb_search_batch_device(vdb_index* x, const float* d_q, int64_t nq, int32_t k, int32_t* d_ids, float* d_dists, void* stream) {
     if (!x || nq < 0 || k <= 0 || (nq > 0 && (!d_q || !d_ids || !d_dists))) FAIL(VDB_ERR_INVALID, "vdb_search_batch_device: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
-    cudaStream_t st = stream ? (cudaStream_t)stream : x->stream;
+    cudaStream_t st = (cudaStream_t)stream;   // verbatim cudaStream_t: NULL is CUDA's legacy default stream
     return search_device_locked(x, d_q, nq, k, d_ids, d_dists, st);
 }
 
@@ -560,7 +579,7 @@ extern "C" int vdb_pq_lut_device(vdb_index* x, const float* d_q, int64_t nq, flo
     if (!x || !d_q || !d_lut || x->pq_m == 0) FAIL(VDB_ERR_INVALID, "vdb_pq_lut_device: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
     if (!x->trained) FAIL(VDB_ERR_UNTRAINED, "train first");
-    cudaStream_t st = stream ? (cudaStream_t)stream : x->stream;
+    cudaStream_t st = (cudaStream_t)stream;   // verbatim cudaStream_t: NULL is CUDA's legacy default stream
     launch_pq_lut(d_q, x->d_cb.p, (int)nq, x->cfg.dim, x->pq_m, x->cfg.arith, d_lut, st);
     VDB_CUDA(cudaGetLastError());
     return VDB_OK;
@@ -570,7 +589,7 @@ extern "C" int vdb_adc_scan_device(vdb_index* x, const float* d_lut, float* d_ou
     std::lock_guard<std::mutex> lk(x->mu);
     VDB_TRY(sync_index(x));
     if (x->n_coded < x->n) FAIL(VDB_ERR_UNTRAINED, "no codes");
-    cudaStream_t st = stream ? (cudaStream_t)stream : x->stream;
+    cudaStream_t st = (cudaStream_t)stream;   // verbatim cudaStream_t: NULL is CUDA's legacy default stream
     launch_adc_scan_plain(x->d_codes.p, x->n, x->pq_m, d_lut, d_out, st);
     VDB_CUDA(cudaGetLastError());
     return VDB_OK;
