@@ -71,7 +71,7 @@ typedef struct vdb_config {
     int32_t search_ef_cap;   /* HNSW_PQ: cap of the layer-0 beam; 0 = 5000, the constant of HnswPqIndex.java:621 */
     uint64_t level_seed;     /* seeded stand-in for ThreadLocalRandom level draws (HnswPqIndex.java:752-759) */
     int32_t trav_store;      /* HNSW*: rows read during traversal: 0 = bf16 copy (default), 1 = fp32 (strict order) */
-    int32_t trav_batch;      /* HNSW*: candidates expanded per round: 0 = auto (ef/128 in [4,32]), 1 = the Java pop order */
+    int32_t trav_batch;      /* HNSW*: candidates expanded per round: 0 = auto (ef/128 in [4,32]; 64 from ef 4096), 1 = the Java pop order */
     int32_t reserved1;
     int32_t reserved2;
 } vdb_config;

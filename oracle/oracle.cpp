@@ -418,6 +418,24 @@ static inline float pq_direct(const float* q, const uint8_t* code, const float* 
     }
     return dist;
 }
+// Twin of the product's CTA-wide upper-layer PQ distance (hnsw_kernels.cu greedy_level_pq): the same quantity summed as
+// 8 partial sums of ceil(M/8) consecutive subspaces each (every subspace term summed sequentially from 0), partials added
+// in order. Not the Java order (R5) — within 1e-6 relative of it; used only when arith == ARITH_GPU_TREE.
+static inline float pq_direct_parts(const float* q, const uint8_t* code, const float* codebooks, int M, int ncent, int sd) {
+    const int mp = (M + 7) / 8;
+    float total = 0.0f;
+    for (int part = 0; part < 8; part++) {
+        float ps = 0.0f;
+        for (int m = part * mp; m < M && m < (part + 1) * mp; m++) {
+            const float* cen = codebooks + ((size_t)m * ncent + code[m]) * sd;
+            float t = 0.0f;
+            for (int d = 0; d < sd; d++) { float diff = q[m * sd + d] - cen[d]; t += diff * diff; }
+            ps += t;
+        }
+        total = part == 0 ? ps : total + ps;
+    }
+    return total;
+}
 ORC_API float orc_pq_direct(const float* q, const uint8_t* code, const float* codebooks, int dim, int M, int ncent) {
     return pq_direct(q, code, codebooks, M, ncent, dim / M);
 }
@@ -543,7 +561,10 @@ struct Hnsw {
         float dot = arith == ARITH_GPU_TREE ? dot_gpu(vec(i), q, dim) : dot_seq(vec(i), q, dim);
         return 1.0f - dot / (norms[i] * qnorm);                   // HnswIndex.java:126-133
     }
-    float pqdist(const float* q, int i) const { return pq_direct(q, &codes[(size_t)i * pqM], codebooks.data(), pqM, ncent, sd); }
+    float pqdist(const float* q, int i) const {
+        if (arith == 2) return pq_direct_parts(q, &codes[(size_t)i * pqM], codebooks.data(), pqM, ncent, sd);
+        return pq_direct(q, &codes[(size_t)i * pqM], codebooks.data(), pqM, ncent, sd);
+    }
 
     int assignLevel() {                                            // HnswPqIndex.java:752-759 (seeded)
         int lv = 0;

@@ -26,22 +26,9 @@
 #define HN_NT 256
 #define HN_WARPS (HN_NT / 32)
 #define EXP_BIT 0x80000000ull
-#define HN_FMAX 1024      // fresh rows per round (batch * deg <= HN_FMAX)
+#define HN_FMAX 2048      // fresh rows per round (batch * deg <= HN_FMAX)
 #define HN_MAXB 64
 
-struct HnswShared {
-    int sel[HN_MAXB];
-    int wsum[HN_WARPS];
-    int nsel;
-    int nfresh;
-    int nacc;
-    int count;        // entries in pool (<= ef)
-    int evicted;      // Java: first results.poll() has happened (furthest is live)
-    int lb0;
-    float dentry;
-    float qnorm;
-    int cur;
-};
 
 __device__ __forceinline__ uint64_t pool_key(float d, int node) { return ((uint64_t)f2ord(d) << 32) | (uint32_t)node; }
 __device__ __forceinline__ float pool_dist(uint64_t k) { return ord2f((uint32_t)(k >> 32)); }
@@ -152,6 +139,74 @@ __device__ int greedy_level(const HnswSearchParams& p, const float* sq, float qn
     return cur;
 }
 
+// searchLayerClosestCompressed (HnswPqIndex.java:794-827) with the whole CTA: thread (neighbour = tid/8, part = tid%8)
+// sums ceil(M/8) consecutive subspace terms of the direct PQ distance (a3, HnswPqIndex.java:371-386), the 8 partials are
+// added in order (oracle twin: pq_direct_parts), the first improving neighbour in list order wins (`break` :821).
+// ~1 memory round trip per hop instead of a 512-term serial chain on one lane. Barriers inside; all threads call.
+struct GreedyShared { float d[64]; int best; int cur; float curd; };
+__device__ __forceinline__ float pq_partial(const HnswSearchParams& p, const float* __restrict__ sq, int node, int part) {
+    const int sd = p.dim / p.pq_m, mp = (p.pq_m + 7) >> 3;
+    const uint8_t* code = p.codes + (size_t)node * p.pq_m;
+    float ps = 0.0f;
+    const int m1 = min(p.pq_m, (part + 1) * mp);
+    for (int m = part * mp; m < m1; m++) {
+        const float* cen = p.codebooks + ((size_t)m * VDB_NCENT + code[m]) * sd;
+        float t = 0.0f;
+        if ((sd & 3) == 0) {
+            for (int c = 0; c < (sd >> 2); c++) {
+                const float4 x = __ldg(reinterpret_cast<const float4*>(cen) + c);
+                const float4 y = reinterpret_cast<const float4*>(sq + m * sd)[c];
+                float df;
+                df = __fsub_rn(y.x, x.x); t = __fadd_rn(t, __fmul_rn(df, df));
+                df = __fsub_rn(y.y, x.y); t = __fadd_rn(t, __fmul_rn(df, df));
+                df = __fsub_rn(y.z, x.z); t = __fadd_rn(t, __fmul_rn(df, df));
+                df = __fsub_rn(y.w, x.w); t = __fadd_rn(t, __fmul_rn(df, df));
+            }
+        } else {
+            for (int d = 0; d < sd; d++) { const float df = __fsub_rn(sq[m * sd + d], __ldg(cen + d)); t = __fadd_rn(t, __fmul_rn(df, df)); }
+        }
+        ps = __fadd_rn(ps, t);
+    }
+    return ps;
+}
+__device__ __forceinline__ float pq_combine8(float ps, int lane) {      // partials of lanes 8k..8k+7 added in order
+    const int base = lane & ~7;
+    float total = __shfl_sync(0xffffffffu, ps, base);
+#pragma unroll
+    for (int i = 1; i < 8; i++) total = __fadd_rn(total, __shfl_sync(0xffffffffu, ps, base + i));
+    return total;
+}
+__device__ int greedy_level_pq(const HnswSearchParams& p, const float* sq, int cur, int level, GreedyShared& G) {
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int32_t* adjl = p.adj + (size_t)level * p.n * p.deg;
+    const int nbr = tid >> 3, part = tid & 7;
+    {
+        const float d = pq_combine8(pq_partial(p, sq, cur, part), lane);
+        if (tid == 0) { G.cur = cur; G.curd = d; }
+    }
+    __syncthreads();
+    while (true) {
+        cur = G.cur;
+        const float curd = G.curd;
+        if (tid == 0) G.best = 0x7fffffff;
+        __syncthreads();
+        for (int j0 = 0; j0 < p.deg; j0 += HN_NT / 8) {
+            const int j = j0 + nbr;
+            const int nb = j < p.deg ? __ldg(adjl + (size_t)cur * p.deg + j) : -1;
+            const float ps = nb >= 0 ? pq_partial(p, sq, nb, part) : 0.0f;
+            const float d = pq_combine8(ps, lane);
+            if (part == 0 && nb >= 0) { G.d[j] = d; if (d < curd) atomicMin(&G.best, j); }
+        }
+        __syncthreads();
+        const int best = G.best;
+        if (best == 0x7fffffff) break;
+        __syncthreads();
+        if (tid == 0) { G.cur = __ldg(adjl + (size_t)cur * p.deg + best); G.curd = G.d[best]; }
+        __syncthreads();
+    }
+    return G.cur;
+}
+
 // ---- traversal distance: a group of G lanes per row, NCH 16-byte chunks per lane, U rows in flight ----------------
 // fp32 rows: chunk = 4 floats; the per-lane fma order and the xor butterfly are mirrored by the oracle (l2sq_gpu/dot_gpu).
 // bf16 rows: chunk = 8 elements widened to fp32 (exact), same accumulation.
@@ -171,19 +226,68 @@ __device__ __forceinline__ void unpack(const uint4& v, float* x) {
     }
 }
 
-// distances of fresh rows fnode[0..nf) -> accepted keys appended to fkey (slot via shared atomic). All threads call.
+
+// Distance of one traversal row from its per-lane partial sums.
+//   fp32 rows (strict): acc = sum (x-q)^2  (sq-L2)  or  sum x*q (cosine)  — the oracle's l2sq_gpu / dot_gpu order.
+//   bf16 rows (fast)  : acc = sum x*q for both metrics; sq-L2 is ||q||^2 + ||x||^2 - 2 x.q with ||x||^2 precomputed from
+//                       the bf16 row (2 instructions per element instead of 3; the answer is re-scored exactly anyway).
+// rowscal = the row's scalar fetched together with the row: Java norm (cosine) or ||x_bf16||^2 (bf16 sq-L2)
+template <bool BF16>
+__device__ __forceinline__ float row_scalar(const HnswSearchParams& p, int node) {
+    if (p.metric == 1) return __ldg(p.norms + node);
+    if (BF16) return __ldg(p.tnorm + node);
+    return 0.0f;
+}
+template <bool BF16>
+__device__ __forceinline__ float finish_dist(const HnswSearchParams& p, float acc, float rowscal, float qnorm, float qq) {
+    if (p.metric == 1) return cosine_dist_from_dot(acc, rowscal, qnorm);
+    if (BF16) return fmaxf(__fmaf_rn(-2.0f, acc, __fadd_rn(qq, rowscal)), 0.0f);
+    return acc;
+}
+
+struct FreshOut {
+    uint64_t* fkey;   // accepted keys, appended
+    int* nacc;        // shared counter
+    bool full;        // results.size() >= ef
+    float bound;      // furthest (live or stale)
+};
+__device__ __forceinline__ void accept_key(const FreshOut& o, float d, int node) {
+    if (!o.full || d < o.bound) {
+        const int slot = atomicAdd(o.nacc, 1);
+        o.fkey[slot] = pool_key(d, node);
+    }
+}
+
+// issue the loads of one pass: U rows x NCH chunks per lane (+ the row scalar on the group's first lane)
 template <bool BF16, int G, int NCH, int U>
-__device__ __forceinline__ void fresh_distances(const HnswSearchParams& p, const float* __restrict__ sq, float qnorm,
-                                                const int* __restrict__ fnode, int nf, uint64_t* __restrict__ fkey,
-                                                int* nacc, bool full, float bound) {
+__device__ __forceinline__ void issue_rows(const HnswSearchParams& p, const unsigned char* __restrict__ tb, const int* __restrict__ fnode,
+                                           int nf, int base, int grp, int g, int nchunk, int (&nd)[U], float (&sc)[U], uint4 (&vv)[U][NCH]) {
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+        const int j = base + grp * U + u;
+        nd[u] = j < nf ? fnode[j] : -1;
+        sc[u] = (g == 0 && nd[u] >= 0) ? row_scalar<BF16>(p, nd[u]) : 0.0f;
+#pragma unroll
+        for (int c = 0; c < NCH; c++) {
+            const int ch = g + c * G;
+            vv[u][c] = make_uint4(0u, 0u, 0u, 0u);
+            if (nd[u] >= 0 && ch < nchunk) vv[u][c] = __ldg(reinterpret_cast<const uint4*>(tb + (size_t)nd[u] * p.tstride) + ch);
+        }
+    }
+}
+
+// distances of fresh rows fnode[0..nf): a group of G lanes per row, NCH 16-byte chunks per lane, U rows per pass and the
+// next pass's loads issued before the current pass is reduced (software pipeline). All threads of the CTA call.
+template <bool BF16, int G, int NCH, int U, bool PIPE>
+__device__ __noinline__ void fresh_distances(const HnswSearchParams& p, const float* __restrict__ sq, float qnorm, float qq,
+                                                const int* __restrict__ fnode, int nf, const FreshOut& o) {
     constexpr int EL = Chunk<BF16>::EL;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     constexpr int GPW = 32 / G;
     const int g = lane % G, grp = warp * GPW + lane / G;
     constexpr int NG = HN_WARPS * GPW;
     const int nchunk = p.tstride >> 4;                 // 16-byte chunks per row
-    // query slice of this lane, in registers
-    float qr[NCH][EL];
+    float qr[NCH][EL];                                 // query slice of this lane, in registers
 #pragma unroll
     for (int c = 0; c < NCH; c++) {
         const int ch = g + c * G;
@@ -191,21 +295,13 @@ __device__ __forceinline__ void fresh_distances(const HnswSearchParams& p, const
         for (int e = 0; e < EL; e++) qr[c][e] = ch < nchunk ? sq[ch * EL + e] : 0.0f;
     }
     const unsigned char* tb = reinterpret_cast<const unsigned char*>(p.tbase);
+    int node[U], nnode[U];
+    float rs[U], nrs[U];
+    uint4 v[U][NCH], nv[U][NCH];
+    issue_rows<BF16, G, NCH, U>(p, tb, fnode, nf, 0, grp, g, nchunk, node, rs, v);
     for (int base = 0; base < nf; base += NG * U) {
-        int node[U];
-        uint4 v[U][NCH];
-#pragma unroll
-        for (int u = 0; u < U; u++) {
-            const int j = base + grp * U + u;
-            node[u] = j < nf ? fnode[j] : -1;
-#pragma unroll
-            for (int c = 0; c < NCH; c++) {
-                const int ch = g + c * G;
-                v[u][c] = make_uint4(0u, 0u, 0u, 0u);
-                if (node[u] >= 0 && ch < nchunk)
-                    v[u][c] = __ldg(reinterpret_cast<const uint4*>(tb + (size_t)node[u] * p.tstride) + ch);
-            }
-        }
+        const bool more = PIPE && base + NG * U < nf;
+        if (more) issue_rows<BF16, G, NCH, U>(p, tb, fnode, nf, base + NG * U, grp, g, nchunk, nnode, nrs, nv);
 #pragma unroll
         for (int u = 0; u < U; u++) {
             float acc = 0.0f;
@@ -213,7 +309,7 @@ __device__ __forceinline__ void fresh_distances(const HnswSearchParams& p, const
             for (int c = 0; c < NCH; c++) {
                 float x[EL];
                 unpack<BF16>(v[u][c], x);
-                if (p.metric == 0) {
+                if (!BF16 && p.metric == 0) {
 #pragma unroll
                     for (int e = 0; e < EL; e++) { const float df = __fsub_rn(x[e], qr[c][e]); acc = __fmaf_rn(df, df, acc); }
                 } else {
@@ -223,22 +319,25 @@ __device__ __forceinline__ void fresh_distances(const HnswSearchParams& p, const
             }
 #pragma unroll
             for (int off = G / 2; off >= 1; off >>= 1) acc = __fadd_rn(acc, __shfl_xor_sync(0xffffffffu, acc, off));
-            if (g == 0 && node[u] >= 0) {
-                const float d = p.metric == 0 ? acc : cosine_dist_from_dot(acc, p.norms[node[u]], qnorm);
-                if (!full || d < bound) {
-                    const int slot = atomicAdd(nacc, 1);
-                    fkey[slot] = pool_key(d, node[u]);
-                }
+            if (g == 0 && node[u] >= 0) accept_key(o, finish_dist<BF16>(p, acc, rs[u], qnorm, qq), node[u]);
+        }
+        if (more) {
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                node[u] = nnode[u]; rs[u] = nrs[u];
+#pragma unroll
+                for (int c = 0; c < NCH; c++) v[u][c] = nv[u][c];
             }
+        } else if (!PIPE && base + NG * U < nf) {
+            issue_rows<BF16, G, NCH, U>(p, tb, fnode, nf, base + NG * U, grp, g, nchunk, node, rs, v);
         }
     }
 }
 
 // rows with more than 4*32 chunks (D > 512 fp32 / 1024 bf16): chunks are walked in passes of 128 per row
 template <bool BF16>
-__device__ __forceinline__ void fresh_distances_long(const HnswSearchParams& p, const float* __restrict__ sq, float qnorm,
-                                                     const int* __restrict__ fnode, int nf, uint64_t* __restrict__ fkey,
-                                                     int* nacc, bool full, float bound) {
+__device__ __noinline__ void fresh_distances_long(const HnswSearchParams& p, const float* __restrict__ sq, float qnorm, float qq,
+                                                     const int* __restrict__ fnode, int nf, const FreshOut& o) {
     constexpr int EL = Chunk<BF16>::EL;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int nchunk = p.tstride >> 4;
@@ -268,7 +367,7 @@ __device__ __forceinline__ void fresh_distances_long(const HnswSearchParams& p, 
                 for (int u = 0; u < 2; u++) {
                     float x[EL];
                     unpack<BF16>(v[u][c], x);
-                    if (p.metric == 0) {
+                    if (!BF16 && p.metric == 0) {
 #pragma unroll
                         for (int e = 0; e < EL; e++) { const float df = __fsub_rn(x[e], qv[e]); acc[u] = __fmaf_rn(df, df, acc[u]); }
                     } else {
@@ -283,26 +382,23 @@ __device__ __forceinline__ void fresh_distances_long(const HnswSearchParams& p, 
             float a = acc[u];
 #pragma unroll
             for (int off = 16; off >= 1; off >>= 1) a = __fadd_rn(a, __shfl_xor_sync(0xffffffffu, a, off));
-            if (lane == 0 && node[u] >= 0) {
-                const float d = p.metric == 0 ? a : cosine_dist_from_dot(a, p.norms[node[u]], qnorm);
-                if (!full || d < bound) { const int slot = atomicAdd(nacc, 1); fkey[slot] = pool_key(d, node[u]); }
-            }
+            if (lane == 0 && node[u] >= 0) accept_key(o, finish_dist<BF16>(p, a, row_scalar<BF16>(p, node[u]), qnorm, qq), node[u]);
         }
     }
 }
 
 template <bool BF16>
-__device__ __forceinline__ void fresh_dispatch(const HnswSearchParams& p, const float* sq, float qnorm, const int* fnode, int nf,
-                                               uint64_t* fkey, int* nacc, bool full, float bound) {
+__device__ __forceinline__ void fresh_dispatch(const HnswSearchParams& p, const float* sq, float qnorm, float qq, const int* fnode,
+                                               int nf, const FreshOut& o) {
     const int nchunk = p.tstride >> 4;
-    if (nchunk <= 4) fresh_distances<BF16, 4, 1, 8>(p, sq, qnorm, fnode, nf, fkey, nacc, full, bound);
-    else if (nchunk <= 8) fresh_distances<BF16, 8, 1, 8>(p, sq, qnorm, fnode, nf, fkey, nacc, full, bound);
-    else if (nchunk <= 16) fresh_distances<BF16, 16, 1, 8>(p, sq, qnorm, fnode, nf, fkey, nacc, full, bound);
-    else if (nchunk <= 32) fresh_distances<BF16, 32, 1, 8>(p, sq, qnorm, fnode, nf, fkey, nacc, full, bound);
-    else if (nchunk <= 64) fresh_distances<BF16, 32, 2, 4>(p, sq, qnorm, fnode, nf, fkey, nacc, full, bound);
-    else if (nchunk <= 96) fresh_distances<BF16, 32, 3, 2>(p, sq, qnorm, fnode, nf, fkey, nacc, full, bound);
-    else if (nchunk <= 128) fresh_distances<BF16, 32, 4, 2>(p, sq, qnorm, fnode, nf, fkey, nacc, full, bound);
-    else fresh_distances_long<BF16>(p, sq, qnorm, fnode, nf, fkey, nacc, full, bound);
+    if (nchunk <= 4) fresh_distances<BF16, 4, 1, 4, true>(p, sq, qnorm, qq, fnode, nf, o);
+    else if (nchunk <= 8) fresh_distances<BF16, 8, 1, 4, true>(p, sq, qnorm, qq, fnode, nf, o);
+    else if (nchunk <= 16) fresh_distances<BF16, 16, 1, 4, true>(p, sq, qnorm, qq, fnode, nf, o);
+    else if (nchunk <= 32) fresh_distances<BF16, 32, 1, 4, true>(p, sq, qnorm, qq, fnode, nf, o);
+    else if (nchunk <= 64) fresh_distances<BF16, 32, 2, 4, true>(p, sq, qnorm, qq, fnode, nf, o);
+    else if (nchunk <= 96) fresh_distances<BF16, 32, 3, 2, false>(p, sq, qnorm, qq, fnode, nf, o);
+    else if (nchunk <= 128) fresh_distances<BF16, 32, 4, 2, false>(p, sq, qnorm, qq, fnode, nf, o);
+    else fresh_distances_long<BF16>(p, sq, qnorm, qq, fnode, nf, o);
 }
 
 // first index whose key (expanded bit ignored) is >= key. The expanded bit is NOT part of the order, so marking an
@@ -315,26 +411,203 @@ __device__ __forceinline__ int lower_bound_u64(const uint64_t* __restrict__ a, i
     }
     return lo;
 }
+// number of entries of the ascending int array r[0..n) that are <= x
+__device__ __forceinline__ int count_le_i32(const int* __restrict__ r, int n, int x) {
+    int lo = 0, hi = n;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (r[mid] <= x) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+// ---- bf16 traversal distances on the tensor pipe ------------------------------------------------------------------------
+// The fresh rows of a round form a [rows x D] bf16 matrix that is multiplied by ONE vector (the query): a gather-bound
+// matrix-vector product. It is issued as mma.sync m16n8k16 (16 rows per warp tile; the 8 result columns all hold the same
+// query, column 0 is read) because the rows arrive straight from global memory in registers — each lane's 16-byte load
+// IS its A fragment for two MMAs (the k index is permuted consistently between A and B, a dot product does not care) —
+// so there is no shared-memory staging for a tcgen05 descriptor to point at. ~110 instructions per 16 rows instead of
+// ~1000 on the FMA pipe; the kernel is issue-bound, not tensor-bound (profiles/).
+__device__ __forceinline__ void mma_bf16_16816(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+// sqh: the query rounded to bf16, zero padded, in shared memory ([tstride/2] elements). All threads of the CTA call.
+__device__ __forceinline__ void fresh_distances_mma(const HnswSearchParams& p, const uint4* __restrict__ sqh, float qnorm, float qq,
+                                                    const int* __restrict__ fnode, int nf, const FreshOut& o) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int g = lane >> 2, c = lane & 3;
+    const int nblk = p.tstride >> 4;                  // 16-byte column blocks per row
+    const int nst = (nblk + 15) >> 4;                 // stages of 16 blocks (4 per lane)
+    const unsigned char* tb = reinterpret_cast<const unsigned char*>(p.tbase);
+    for (int tile = warp; tile * 16 < nf; tile += HN_WARPS) {
+        const int j0 = tile * 16 + g, j1 = j0 + 8;
+        const int n0 = fnode[min(j0, nf - 1)], n1 = fnode[min(j1, nf - 1)];
+        const uint4* r0 = reinterpret_cast<const uint4*>(tb + (size_t)n0 * p.tstride);
+        const uint4* r1 = reinterpret_cast<const uint4*>(tb + (size_t)n1 * p.tstride);
+        const float sc0 = (c == 0 && j0 < nf) ? row_scalar<true>(p, n0) : 0.0f;
+        const float sc1 = (c == 0 && j1 < nf) ? row_scalar<true>(p, n1) : 0.0f;
+        float acc0[4] = {0.0f, 0.0f, 0.0f, 0.0f}, acc1[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+        uint4 A0[4], A1[4], N0[4], N1[4];
+        const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+        for (int i = 0; i < 4; i++) { const int cb = c + 4 * i; A0[i] = cb < nblk ? __ldg(r0 + cb) : z; A1[i] = cb < nblk ? __ldg(r1 + cb) : z; }
+        for (int st = 0; st < nst; st++) {
+            if (st + 1 < nst) {
+#pragma unroll
+                for (int i = 0; i < 4; i++) { const int cb = c + 4 * (4 * (st + 1) + i); N0[i] = cb < nblk ? __ldg(r0 + cb) : z; N1[i] = cb < nblk ? __ldg(r1 + cb) : z; }
+            }
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const int cb = c + 4 * (4 * st + i);
+                const uint4 qv = cb < nblk ? sqh[cb] : z;
+                mma_bf16_16816(acc0, A0[i].x, A1[i].x, A0[i].y, A1[i].y, qv.x, qv.y);
+                mma_bf16_16816(acc1, A0[i].z, A1[i].z, A0[i].w, A1[i].w, qv.z, qv.w);
+            }
+            if (st + 1 < nst) {
+#pragma unroll
+                for (int i = 0; i < 4; i++) { A0[i] = N0[i]; A1[i] = N1[i]; }
+            }
+        }
+        if (c == 0) {
+            if (j0 < nf) accept_key(o, finish_dist<true>(p, acc0[0] + acc1[0], sc0, qnorm, qq), n0);
+            if (j1 < nf) accept_key(o, finish_dist<true>(p, acc0[2] + acc1[2], sc1, qnorm, qq), n1);
+        }
+    }
+}
+
+#define HN_FCAP 2048      // side buffer capacity (entries)
+#define HN_FTH 1024       // side buffer is folded into the main array when it holds more than this
+
+struct HnswShared {
+    int candP[HN_MAXB], candF[HN_MAXB];   // indices of the first unexpanded entries of the main array / side buffer
+    int sel[HN_MAXB];
+    int wsum[HN_WARPS];
+    int nfresh, nacc;
+    int countP, countF;   // entries in the main array (<= ef) / side buffer
+    int frontP, frontF;   // every entry below these indices carries the expanded bit
+    int whichF;           // which of the two side-buffer halves is current
+    int evicted;          // Java: first results.poll() has happened (furthest is live)
+    float dentry, qnorm, qq;
+    long long ph[8];      // profile: per-phase cycles of thread 0
+    long long tp;
+};
+
+// Collect the indices of the first (up to) B unexpanded entries of the sorted array a[from..lim) into cand[] (sorted
+// order). Returns the number found (may exceed B: only the first B are recorded); *resume = an index below which every
+// entry that was not recorded is expanded (the new front if all recorded ones get taken is computed by the caller).
+// Contains barriers: all threads call with uniform arguments.
+__device__ __forceinline__ int scan_unexpanded(const uint64_t* __restrict__ a, int from, int lim, int B, int* cand, int* wsum,
+                                               int* scanned_to) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    int found = 0, pos = from;
+    while (found < B && pos < lim) {
+        const int i = pos + tid;
+        const bool un = i < lim && !(a[i] & EXP_BIT);
+        const unsigned bal = __ballot_sync(0xffffffffu, un);
+        if (lane == 0) wsum[warp] = __popc(bal);
+        __syncthreads();
+        int before = found, total = 0;
+#pragma unroll
+        for (int w = 0; w < HN_WARPS; w++) { const int c = wsum[w]; if (w < warp) before += c; total += c; }
+        before += __popc(bal & ((1u << lane) - 1u));
+        if (un && before < B) cand[before] = i;
+        found += total; pos += HN_NT;
+        __syncthreads();
+    }
+    *scanned_to = min(pos, lim);
+    return found;
+}
+
+// Merge the sorted keys s[0..ns) into the sorted array a[0..na) writing out[0..min(na+ns,cap)) (out != a): every
+// element finds its final slot by ranking (rr[j] = #a-entries below s[j]). Barriers inside; rr is scratch [ns].
+__device__ __forceinline__ void merge_ranked(const uint64_t* __restrict__ a, int na, const uint64_t* __restrict__ s, int ns,
+                                             uint64_t* __restrict__ out, int cap, int* __restrict__ rr) {
+    const int tid = threadIdx.x;
+    for (int j = tid; j < ns; j += HN_NT) rr[j] = lower_bound_u64(a, na, s[j] & ~EXP_BIT);
+    __syncthreads();
+    const int r0 = rr[0];
+#pragma unroll 4
+    for (int i = tid; i < na; i += HN_NT) {
+        const uint64_t e = a[i];
+        const int np = i < r0 ? i : i + count_le_i32(rr, ns, i);
+        if (np < cap) out[np] = e;
+    }
+    for (int j = tid; j < ns; j += HN_NT) { const int np = rr[j] + j; if (np < cap) out[np] = s[j]; }
+    __syncthreads();
+}
+
+// Same merge IN PLACE (out == a, capacity cap): entries only move up, so the array is walked top chunk first; a chunk
+// overwrites only slots of chunks already moved or of itself (read before the barrier). s must not alias a.
+__device__ __forceinline__ void merge_ranked_inplace(uint64_t* __restrict__ a, int na, const uint64_t* __restrict__ s, int ns, int cap,
+                                                     int* __restrict__ rr) {
+    const int tid = threadIdx.x;
+    for (int j = tid; j < ns; j += HN_NT) rr[j] = lower_bound_u64(a, na, s[j] & ~EXP_BIT);
+    __syncthreads();
+    const int r0 = rr[0];
+    constexpr int PERC = 4;
+    for (int hi = na; hi > r0; hi -= HN_NT * PERC) {
+        const int lo = max(r0, hi - HN_NT * PERC);
+        uint64_t e[PERC]; int np[PERC];
+#pragma unroll
+        for (int t = 0; t < PERC; t++) {
+            const int i = lo + tid + t * HN_NT;
+            np[t] = -1;
+            if (i < hi) { e[t] = a[i]; np[t] = i + count_le_i32(rr, ns, i); }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int t = 0; t < PERC; t++) if (np[t] >= 0 && np[t] < cap) a[np[t]] = e[t];
+        __syncthreads();
+    }
+    for (int j = tid; j < ns; j += HN_NT) { const int np = rr[j] + j; if (np < cap) a[np] = s[j]; }
+    __syncthreads();
+}
+
+// Fold the side buffer into the main array (in place) and remap the bookkeeping. Barriers inside; uniform call.
+__device__ __forceinline__ void fold_side_buffer(uint64_t* P, const uint64_t* F0, HnswShared& S, int ef, int* rr) {
+    const int cP = S.countP, cF = S.countF, fP = S.frontP, fF = S.frontF;
+    const uint64_t* Fc = F0 + (size_t)S.whichF * HN_FCAP;
+    __syncthreads();
+    merge_ranked_inplace(P, cP, Fc, cF, ef, rr);
+    if (threadIdx.x == 0) {
+        // old P[fP] lands after every buffer entry ranked at or below it (rr <= fP)
+        int nf_ = fP + count_le_i32(rr, cF, fP);
+        if (fF < cF) nf_ = min(nf_, rr[fF] + fF);                          // first possibly-unexpanded buffer entry
+        S.frontP = min(nf_, ef);
+        if (cP + cF > ef) S.evicted = 1;
+        S.countP = min(cP + cF, ef); S.countF = 0; S.frontF = 0;
+    }
+    __syncthreads();
+}
 
 template <bool BF16>
 __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int qpad = (p.dim + 7) & ~7;
-    float* sq = reinterpret_cast<float*>(smem_raw);                       // [qpad] query (zero padded)
-    uint64_t* pool = reinterpret_cast<uint64_t*>(sq + qpad);              // [ef] sorted
-    uint64_t* fkey = pool + p.ef;                                         // [HN_FMAX] accepted fresh keys
-    int* fnode = reinterpret_cast<int*>(fkey + HN_FMAX);                  // [HN_FMAX] fresh nodes
+    float* sq = reinterpret_cast<float*>(smem_raw);                       // [qpad] query, fp32 (zero padded)
+    uint4* sqh = reinterpret_cast<uint4*>(sq + qpad);                     // [qpad] query, bf16 (tensor-pipe B operand)
+    uint64_t* P = reinterpret_cast<uint64_t*>(reinterpret_cast<unsigned char*>(sqh) + qpad * 2);   // [ef] main sorted array
+    uint64_t* F0 = P + p.ef;                                              // [2][HN_FCAP] side buffer, ping-pong
+    uint64_t* fkey = F0 + 2 * HN_FCAP;                                    // [HN_FMAX] accepted keys of the round; rank scratch
+    int* fnode = reinterpret_cast<int*>(fkey + HN_FMAX);                  // [HN_FMAX] fresh nodes; rank scratch
     const int vwords = (p.n + 31) >> 5;
     uint32_t* vis = p.visited_in_smem ? reinterpret_cast<uint32_t*>(fnode + HN_FMAX)
                                       : p.visited_scratch + (size_t)blockIdx.x * vwords;
     __shared__ HnswShared S;
+    __shared__ GreedyShared GS;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int ef = p.ef, variant = p.variant, B = p.batch;
+    const int uncertain_ok = B == 1 ? 1 : 128;    // side-buffer entries tolerated while candidates come from the array's tail
     unsigned long long evals = 0, exps = 0;
+    if (tid < 8) S.ph[tid] = 0;
+#define HN_MARK(slot) do { if (p.profile && tid == 0) { const long long now_ = clock64(); S.ph[slot] += now_ - S.tp; S.tp = now_; } } while (0)
 
     for (int q = blockIdx.x; q < p.nq; q += gridDim.x) {
         // ---- A. stage the query (HnswIndex normalises it: HnswIndex.java:344, core/Vector.java:107-116) ----
         __syncthreads();
+        if (p.profile && tid == 0) S.tp = clock64();
         for (int i = tid; i < qpad; i += HN_NT) sq[i] = i < p.dim ? p.queries[(size_t)q * p.dim + i] : 0.0f;
         for (int i = tid; i < vwords; i += HN_NT) vis[i] = 0u;
         __syncthreads();
@@ -347,163 +620,246 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
             __syncthreads();
             if (tid == 0) S.qnorm = norm_java(sq, p.dim);
         } else if (tid == 0) S.qnorm = 0.0f;
-        __syncthreads();
-        const float qnorm = S.qnorm;
-
-        // ---- B. greedy descent on levels max_level-1 .. 1 (warp 0), then the entry point's layer-0 distance ----
-        if (warp == 0) {
-            int cur = p.entry;
-            const bool comp = (p.metric == 0) && p.trained;
-            for (int l = p.max_level - 1; l > 0; l--) cur = greedy_level(p, sq, qnorm, cur, l, comp, evals);
-            if (lane == 0) { S.cur = cur; fnode[0] = cur; S.nacc = 0; vis[cur >> 5] |= 1u << (cur & 31); }
+        if (BF16) {
+            __nv_bfloat16* h = reinterpret_cast<__nv_bfloat16*>(sqh);
+            for (int i = tid; i < qpad; i += HN_NT) h[i] = __float2bfloat16_rn(sq[i]);
+            __syncthreads();
+            if (warp == 1) {                                           // ||q||^2 of the ROUNDED query (bf16 sq-L2 form)
+                float a = 0.0f;
+                for (int i = lane; i < qpad; i += 32) { const float v = __bfloat162float(h[i]); a = __fmaf_rn(v, v, a); }
+                a = warp_tree_sum(a);
+                if (lane == 0) S.qq = a;
+            }
         }
         __syncthreads();
-        fresh_dispatch<BF16>(p, sq, qnorm, fnode, 1, fkey, &S.nacc, false, 0.0f);
+        const float qnorm = S.qnorm, qq = S.qq;
+
+        // ---- B. greedy descent on levels max_level-1 .. 1 (warp 0), then the entry point's layer-0 distance ----
+        if ((p.metric == 0) && p.trained) {
+            int cur = p.entry;
+            for (int l = p.max_level - 1; l > 0; l--) cur = greedy_level_pq(p, sq, cur, l, GS);
+            if (tid == 0) { fnode[0] = cur; S.nacc = 0; vis[cur >> 5] |= 1u << (cur & 31); }
+        } else if (warp == 0) {
+            int cur = p.entry;
+            for (int l = p.max_level - 1; l > 0; l--) cur = greedy_level(p, sq, qnorm, cur, l, false, evals);
+            if (lane == 0) { fnode[0] = cur; S.nacc = 0; vis[cur >> 5] |= 1u << (cur & 31); }
+        }
+        __syncthreads();
+        {
+            FreshOut o{fkey, &S.nacc, false, 0.0f};
+            if (BF16) fresh_distances_mma(p, sqh, qnorm, qq, fnode, 1, o);
+            else fresh_dispatch<false>(p, sq, qnorm, qq, fnode, 1, o);
+        }
         __syncthreads();
         if (tid == 0) {
-            pool[0] = fkey[0];
+            P[0] = fkey[0];
             S.dentry = pool_dist(fkey[0]);
-            S.count = 1; S.evicted = 0;
+            S.countP = 1; S.countF = 0; S.frontP = 0; S.frontF = 0; S.whichF = 0; S.evicted = 0; S.nfresh = 0; S.nacc = 0;
             evals++;
         }
         __syncthreads();
 
         // ---- C. layer-0 search in rounds ----
+        HN_MARK(0);
         while (true) {
-            // C1. candidates.poll() x B: the first B unexpanded entries of the eligible prefix (sorted array)
-            const int count = S.count;
-            const bool full = count >= ef;
-            int lim = count;
-            if ((variant == 2 && !S.evicted) || (variant == 1 && full && !S.evicted))
-                lim = lower_bound_u64(pool, count, ((uint64_t)f2ord(S.dentry) << 32) | 0x7fffffffull);   // entries with d <= dentry (Java: `c.d > furthest` stops)
-            const int per = (lim + HN_NT - 1) / HN_NT;
-            const int i0 = min(lim, tid * per), i1 = min(lim, i0 + per);
-            int c = 0;
-            for (int i = i0; i < i1; i++) c += (pool[i] & EXP_BIT) ? 0 : 1;
-            int incl = c;
-#pragma unroll
-            for (int off = 1; off < 32; off <<= 1) { const int o = __shfl_up_sync(0xffffffffu, incl, off); if (lane >= off) incl += o; }
-            if (lane == 31) S.wsum[warp] = incl;
-            __syncthreads();
-            int before = incl - c;
-            for (int w = 0; w < warp; w++) before += S.wsum[w];
-            int total = 0;
-            for (int w = 0; w < HN_WARPS; w++) total += S.wsum[w];
-            if (total == 0) break;                                    // no eligible candidate left: search ends
-            if (before < B && c > 0) {
-                int s = before;
-                for (int i = i0; i < i1 && s < B; i++) {
-                    const uint64_t kk = pool[i];
-                    if (!(kk & EXP_BIT)) { S.sel[s++] = (int)(kk & 0x7fffffffull); pool[i] = kk | EXP_BIT; }
+            // C0. fold the side buffer into the main array when (a) the array is not full yet (early phase: exact
+            //     Java bookkeeping), (b) the buffer is large, (c) candidates are about to come from the array's tail while
+            //     the buffer holds entries that may push that tail out of the best ef
+            {
+                const int cP = S.countP, cF = S.countF;
+                if (cF > 0 && (cP < ef || cF > HN_FTH || (S.frontP + B > ef - cF && cF >= uncertain_ok)))
+                    fold_side_buffer(P, F0, S, ef, reinterpret_cast<int*>(fkey));     // fkey is idle here
+            }
+            const uint64_t* Fc = F0 + (size_t)S.whichF * HN_FCAP;
+            uint64_t* Fc_w = F0 + (size_t)S.whichF * HN_FCAP;
+            uint64_t* Fn = F0 + (size_t)(S.whichF ^ 1) * HN_FCAP;
+            const int countP = S.countP;
+            int countF = S.countF;
+            const bool full = countP >= ef;
+            const int evicted = S.evicted | ((countP + countF > ef) ? 1 : 0);
+            int lim = countP;
+            if ((variant == 2 && !evicted) || (variant == 1 && full && !evicted))     // Java: `c.d > furthest` stops; furthest is
+                lim = lower_bound_u64(P, countP, ((uint64_t)f2ord(S.dentry) << 32) | 0x7fffffffull);   // the entry distance here
+            // C1. candidates.poll() x B: the B best unexpanded entries of array + buffer
+            int toP, toF;
+            const int fndP = scan_unexpanded(P, S.frontP, lim, B, S.candP, S.wsum, &toP);
+            const int fndF = scan_unexpanded(Fc, S.frontF, countF, B, S.candF, S.wsum, &toF);
+            const int a = min(fndP, B), b = min(fndF, B);
+            if (a + b == 0) break;                                    // no eligible candidate left: the search ends
+            const int nsel = min(a + b, B);
+            if (tid < a + b) {                                        // rank in the union of the two sorted candidate lists
+                const bool fromP = tid < a;
+                const int me = fromP ? tid : tid - a;
+                const int idx = fromP ? S.candP[me] : S.candF[me];
+                const uint64_t key = (fromP ? P[idx] : Fc[idx]) & ~EXP_BIT;
+                int r = me;
+                if (fromP) { for (int t = 0; t < b; t++) r += ((Fc[S.candF[t]] & ~EXP_BIT) < key) ? 1 : 0; }
+                else { for (int t = 0; t < a; t++) r += ((P[S.candP[t]] & ~EXP_BIT) < key) ? 1 : 0; }
+                if (r < B) {
+                    S.sel[r] = (int)(key & 0x7fffffffull);
+                    if (fromP) P[idx] |= EXP_BIT; else Fc_w[idx] |= EXP_BIT;
                 }
             }
-            if (tid == 0) { S.nsel = min(total, B); S.nfresh = 0; S.nacc = 0; }
             __syncthreads();
-            const int nsel = S.nsel;
-            // C2. neighbour lists + visited test-and-set; fresh nodes appended warp-aggregated
-            for (int s = warp; s < nsel; s += HN_WARPS) {
-                const int32_t* row = p.adj + (size_t)S.sel[s] * p.deg;
-                for (int j0 = 0; j0 < p.deg; j0 += 32) {
-                    const int j = j0 + lane;
-                    const int nb = j < p.deg ? __ldg(row + j) : -1;
-                    bool fresh = false;
-                    if (nb >= 0) {
-                        const uint32_t bit = 1u << (nb & 31);
-                        const uint32_t old = atomicOr(&vis[nb >> 5], bit);
-                        fresh = !(old & bit);
+            // new fronts: the first candidate that was NOT taken, else where the scan stopped
+            int newfrontP, newfrontF;
+            {
+                int takenP = 0;
+                for (int t = 0; t < a; t++) takenP += (P[S.candP[t]] & EXP_BIT) ? 1 : 0;      // taken ones form a prefix
+                const int takenF = nsel - takenP;
+                newfrontP = takenP < a ? S.candP[takenP] : (fndP > B ? S.candP[B - 1] + 1 : toP);
+                newfrontF = takenF < b ? S.candF[takenF] : (fndF > B ? S.candF[B - 1] + 1 : toF);
+            }
+            HN_MARK(1);
+            // C2. neighbour lists (loads of four rows in flight per warp) + visited test-and-set; fresh nodes appended
+            {
+                const int nj = (p.deg + 31) >> 5;
+                const int nitems = nsel * nj;
+                for (int it0 = warp; it0 < nitems; it0 += HN_WARPS * 4) {
+                    int nb[4];
+#pragma unroll
+                    for (int t = 0; t < 4; t++) {
+                        const int it = it0 + t * HN_WARPS;
+                        nb[t] = -1;
+                        if (it < nitems) {
+                            const int s = it / nj, j = (it - s * nj) * 32 + lane;
+                            if (j < p.deg) nb[t] = __ldg(p.adj + (size_t)S.sel[s] * p.deg + j);
+                        }
                     }
-                    const unsigned m = __ballot_sync(0xffffffffu, fresh);
-                    int basec = 0;
-                    if (lane == 0 && m) basec = atomicAdd(&S.nfresh, __popc(m));
-                    basec = __shfl_sync(0xffffffffu, basec, 0);
-                    if (fresh) fnode[basec + __popc(m & ((1u << lane) - 1u))] = nb;
+#pragma unroll
+                    for (int t = 0; t < 4; t++) {
+                        bool fresh = false;
+                        if (nb[t] >= 0) {
+                            const uint32_t bit = 1u << (nb[t] & 31);
+                            const uint32_t old = atomicOr(&vis[nb[t] >> 5], bit);
+                            fresh = !(old & bit);
+                        }
+                        const unsigned m = __ballot_sync(0xffffffffu, fresh);
+                        int basec = 0;
+                        if (lane == 0 && m) basec = atomicAdd(&S.nfresh, __popc(m));
+                        basec = __shfl_sync(0xffffffffu, basec, 0);
+                        if (fresh) fnode[basec + __popc(m & ((1u << lane) - 1u))] = nb[t];
+                    }
                 }
             }
             __syncthreads();
             const int nf = S.nfresh;
-            if (tid == 0) { exps += nsel; evals += nf; }
+            if (tid == 0) { exps += nsel; evals += nf; S.ph[7]++; }
+            // pull every fresh row towards L2 now: the misses (rows not resident) overlap in ONE memory round trip instead
+            // of stalling each stage of the distance loop in turn
+            {
+                const int lines = (p.tstride + 127) >> 7;
+                const unsigned char* tb = reinterpret_cast<const unsigned char*>(p.tbase);
+                for (int t = tid; t < nf * lines; t += HN_NT) {
+                    const int r = t / lines, l = t - r * lines;
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(tb + (size_t)fnode[r] * p.tstride + ((size_t)l << 7)));
+                }
+            }
+            HN_MARK(2);
             // C3. distances of the fresh rows; acceptance: results.size() < ef || d < furthest
             //     (furthest live: HnswPqIndex.java:953-963; stale == entry distance until the first eviction: :876-884,
-            //      HnswIndex.java:611-625)
-            float bound = 0.0f;
-            if (full) bound = (variant == 0 || S.evicted) ? pool_dist(pool[ef - 1]) : S.dentry;
-            fresh_dispatch<BF16>(p, sq, qnorm, fnode, nf, fkey, &S.nacc, full, bound);
+            //      HnswIndex.java:611-625). With a non-empty side buffer P[ef-1] is an upper bound of the live furthest:
+            //      a few more keys are accepted and fall off at the next fold — the kept set is the same.
+            {
+                float bound = 0.0f;
+                if (full) bound = (variant == 0 || evicted) ? pool_dist(P[ef - 1]) : S.dentry;
+                FreshOut o{fkey, &S.nacc, full, bound};
+                if (BF16) fresh_distances_mma(p, sqh, qnorm, qq, fnode, nf, o);
+                else fresh_dispatch<false>(p, sq, qnorm, qq, fnode, nf, o);
+            }
             __syncthreads();
             const int nacc = S.nacc;
-            if (nacc == 0) continue;
-            // C4. sort the accepted keys, merge into the sorted array by ranking, truncate at ef
-            int fp2 = 1; while (fp2 < nacc) fp2 <<= 1;
-            for (int i = nacc + tid; i < fp2; i += HN_NT) fkey[i] = KEY_MAX;
-            if (fp2 > 1) block_bitonic_sort<false>(fkey, nullptr, fp2); else __syncthreads();
-            // positions of the fresh keys against the OLD array (<= HN_FMAX / HN_NT per thread)
-            uint64_t fk[HN_FMAX / HN_NT]; int fpos[HN_FMAX / HN_NT];
-#pragma unroll
-            for (int t = 0; t < HN_FMAX / HN_NT; t++) {
-                const int j = tid + t * HN_NT;
-                fpos[t] = -1;
-                if (j < nacc) { fk[t] = fkey[j]; fpos[t] = j + lower_bound_u64(pool, count, fk[t]); }
-            }
-            if (tid == 0) S.lb0 = lower_bound_u64(pool, count, fkey[0]);
-            __syncthreads();
-            const int lb0 = S.lb0;
-            // move array entries upward, top chunk first (an entry never moves down, so a chunk only overwrites slots of
-            // chunks already moved or of itself, which were read before the barrier)
-            constexpr int PERC = 4;
-            for (int hi = count; hi > lb0; hi -= HN_NT * PERC) {
-                const int lo = max(lb0, hi - HN_NT * PERC);
-                uint64_t e[PERC]; int pos[PERC];
-#pragma unroll
-                for (int t = 0; t < PERC; t++) {
-                    const int i = lo + tid + t * HN_NT;
-                    pos[t] = -1;
-                    if (i < hi) { e[t] = pool[i]; pos[t] = i + lower_bound_u64(fkey, nacc, e[t] & ~EXP_BIT); }
+            HN_MARK(3);
+            int r0 = newfrontF;
+            if (nacc > 0) {
+                // C4. sort the accepted keys (rank sort: no barriers inside; bitonic for the rare large case)
+                if (nacc <= HN_NT) {
+                    // 2-D rank sort: key j = tid % n2 is compared with the slice `part` = tid / n2 of all keys; partial
+                    // ranks meet in shared memory. No barrier inside the counting loop, all 8 warps busy.
+                    int* rank = fnode;                                 // fnode is idle after the distance phase
+                    int n2 = 32; while (n2 < nacc) n2 <<= 1;
+                    const int parts = HN_NT / n2, j = tid & (n2 - 1), part = tid / n2;
+                    if (tid < nacc) rank[tid] = 0;
+                    __syncthreads();
+                    uint64_t kj = KEY_MAX;
+                    if (j < nacc) {
+                        kj = fkey[j];
+                        const int per = (nacc + parts - 1) / parts;
+                        const int i0 = part * per, i1 = min(nacc, i0 + per);
+                        int r = 0;
+                        for (int i = i0; i < i1; i++) r += fkey[i] < kj ? 1 : 0;
+                        if (r) atomicAdd(&rank[j], r);
+                    }
+                    __syncthreads();
+                    if (part == 0 && j < nacc) fkey[rank[j]] = kj;
+                    __syncthreads();
+                } else {
+                    int fp2 = 1; while (fp2 < nacc) fp2 <<= 1;
+                    for (int i = nacc + tid; i < fp2; i += HN_NT) fkey[i] = KEY_MAX;
+                    block_bitonic_sort<false>(fkey, nullptr, fp2);
                 }
-                __syncthreads();
-#pragma unroll
-                for (int t = 0; t < PERC; t++) if (pos[t] >= 0 && pos[t] < ef) pool[pos[t]] = e[t];
-                __syncthreads();
+                HN_MARK(4);
+                // C5. merge into the side buffer (other half), by ranking; a buffer that would overflow is folded first
+                if (countF + nacc > HN_FCAP) {
+                    if (tid == 0) { S.frontP = newfrontP; S.frontF = newfrontF; }
+                    fold_side_buffer(P, F0, S, ef, fnode);
+                    newfrontP = S.frontP; newfrontF = 0; r0 = 0; countF = 0;
+                }
+                merge_ranked(Fc, countF, fkey, nacc, Fn, HN_FCAP, fnode);
+                r0 = fnode[0];
             }
-#pragma unroll
-            for (int t = 0; t < HN_FMAX / HN_NT; t++) if (fpos[t] >= 0 && fpos[t] < ef) pool[fpos[t]] = fk[t];
             if (tid == 0) {
-                const int nc = count + nacc;
-                if (nc > ef) S.evicted = 1;
-                S.count = min(nc, ef);
+                if (nacc > 0) { S.countF = countF + nacc; S.whichF ^= 1; }
+                S.frontP = newfrontP;
+                S.frontF = min(newfrontF, r0);
+                S.nfresh = 0; S.nacc = 0;
             }
             __syncthreads();
+            HN_MARK(5);
         }
 
-        // ---- D. final: best entries by traversal distance -> exact re-score in the reference's sequential order
-        //         (HnswPqIndex.java:646-664 reranks every candidate; with exact traversal distances the values are
-        //         identical, with bf16 rows the shortlist margin covers the rounding) -> (dist,id) sort -> top-k ----
+        // ---- D. final: fold the side buffer, then best entries by traversal distance -> exact re-score in the
+        //         reference's sequential order (HnswPqIndex.java:646-664 reranks every candidate; with exact traversal
+        //         distances the values are identical, with bf16 rows the shortlist margin covers the rounding)
+        //         -> (dist,id) sort -> top-k ----
         __syncthreads();
-        int rs = 32;
-        while (rs < p.k + 22) rs <<= 1;
-        if (rs > HN_FMAX) rs = HN_FMAX;
-        const int have = min(S.count, rs);
-        for (int j = tid; j < rs; j += HN_NT) {
-            uint64_t key = KEY_MAX;
-            if (j < have) {
-                const int node = (int)(pool[j] & 0x7fffffffull);
-                key = make_key(exact_seq_dist(p, sq, qnorm, node), p.ids[node]);
+        if (S.countF > 0) {
+            const int cP = S.countP, cF = S.countF;
+            merge_ranked_inplace(P, cP, F0 + (size_t)S.whichF * HN_FCAP, cF, ef, reinterpret_cast<int*>(fkey));
+            if (tid == 0) { S.countP = min(cP + cF, ef); S.countF = 0; }
+            __syncthreads();
+        }
+        {
+            int rs = 32;
+            while (rs < p.k + 22) rs <<= 1;
+            if (rs > HN_FMAX) rs = HN_FMAX;
+            const int have = min(S.countP, rs);
+            for (int j = tid; j < rs; j += HN_NT) {
+                uint64_t key = KEY_MAX;
+                if (j < have) {
+                    const int node = (int)(P[j] & 0x7fffffffull);
+                    key = make_key(exact_seq_dist(p, sq, qnorm, node), p.ids[node]);
+                }
+                fkey[j] = key;
             }
-            fkey[j] = key;
+            block_bitonic_sort<false>(fkey, nullptr, rs);
+            for (int j = tid; j < p.k; j += HN_NT) {
+                const uint64_t key = j < rs ? fkey[j] : KEY_MAX;
+                if (key == KEY_MAX) { p.out_ids[(size_t)q * p.k + j] = -1; p.out_dists[(size_t)q * p.k + j] = __int_as_float(0x7f800000); }
+                else { p.out_ids[(size_t)q * p.k + j] = key_id(key); p.out_dists[(size_t)q * p.k + j] = key_dist(key); }
+            }
         }
-        block_bitonic_sort<false>(fkey, nullptr, rs);
-        for (int j = tid; j < p.k; j += HN_NT) {
-            const uint64_t key = j < rs ? fkey[j] : KEY_MAX;
-            if (key == KEY_MAX) { p.out_ids[(size_t)q * p.k + j] = -1; p.out_dists[(size_t)q * p.k + j] = __int_as_float(0x7f800000); }
-            else { p.out_ids[(size_t)q * p.k + j] = key_id(key); p.out_dists[(size_t)q * p.k + j] = key_dist(key); }
-        }
+        HN_MARK(6);
     }
     if (p.counters && tid == 0) {
         if (evals) atomicAdd(&p.counters[0], evals);
         if (exps) atomicAdd(&p.counters[1], exps);
+        if (p.profile) for (int i = 0; i < 8; i++) atomicAdd(&p.counters[2 + i], (unsigned long long)S.ph[i]);
     }
 }
 
 size_t hnsw_search_smem_bytes(const HnswSearchParams& p) {
-    size_t b = (size_t)((p.dim + 7) & ~7) * 4 + (size_t)p.ef * 8 + (size_t)HN_FMAX * 12;
+    size_t b = (size_t)((p.dim + 7) & ~7) * 6 + (size_t)p.ef * 8 + (size_t)HN_FCAP * 16 + (size_t)HN_FMAX * 12;
     if (p.visited_in_smem) b += (size_t)((p.n + 31) / 32) * 4;
     return b;
 }
@@ -523,19 +879,28 @@ int launch_hnsw_search(const HnswSearchParams& p, int grid, cudaStream_t st) {
     return 0;
 }
 
-// ---- traversal copy of the base rows: zero-padded to a multiple of 8 elements, fp32 or bf16 (round to nearest even) ----
-__global__ void make_traversal_rows_kernel(const float* __restrict__ base, int64_t n, int dim, int dpad, int bf16, void* __restrict__ out) {
-    const int64_t total = n * dpad;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t r = i / dpad; const int c = (int)(i % dpad);
-        const float v = c < dim ? base[r * dim + c] : 0.0f;
-        if (bf16) reinterpret_cast<__nv_bfloat16*>(out)[i] = __float2bfloat16_rn(v);
-        else reinterpret_cast<float*>(out)[i] = v;
+// ---- traversal copy of the base rows: zero-padded to a multiple of 8 elements, fp32 or bf16 (round to nearest even);
+//      tnorm[r] = sum of squares of the STORED (rounded) row, sequential fp32 — used by the bf16 sq-L2 form ----
+__global__ void make_traversal_rows_kernel(const float* __restrict__ base, int64_t n, int dim, int dpad, int bf16, void* __restrict__ out,
+                                           float* __restrict__ tnorm) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t r = warp; r < n; r += nwarps) {
+        float a = 0.0f;
+        for (int c = lane; c < dpad; c += 32) {
+            const float v = c < dim ? base[r * dim + c] : 0.0f;
+            float sv = v;
+            if (bf16) { const __nv_bfloat16 h = __float2bfloat16_rn(v); reinterpret_cast<__nv_bfloat16*>(out)[r * dpad + c] = h; sv = __bfloat162float(h); }
+            else reinterpret_cast<float*>(out)[r * dpad + c] = v;
+            a = __fmaf_rn(sv, sv, a);
+        }
+        a = warp_tree_sum(a);
+        if (lane == 0 && tnorm) tnorm[r] = a;
     }
 }
-void launch_make_traversal_rows(const float* d_base, int64_t n, int dim, int dpad, int bf16, void* d_out, cudaStream_t st) {
+void launch_make_traversal_rows(const float* d_base, int64_t n, int dim, int dpad, int bf16, void* d_out, float* d_tnorm, cudaStream_t st) {
     if (n <= 0) return;
-    const int64_t total = n * dpad;
-    int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 16);
-    make_traversal_rows_kernel<<<blocks, 256, 0, st>>>(d_base, n, dim, dpad, bf16, d_out);
+    int blocks = (int)std::min<int64_t>((n + 7) / 8, 148 * 16);
+    make_traversal_rows_kernel<<<blocks, 256, 0, st>>>(d_base, n, dim, dpad, bf16, d_out, d_tnorm);
 }

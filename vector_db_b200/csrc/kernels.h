@@ -23,6 +23,7 @@ void launch_distance(const float* d_a, const float* d_b, int64_t n, int dim, int
 // hnsw_kernels.cu
 struct HnswSearchParams {
     const float* base;        // [n][dim]; normalised rows for cosine (exact re-score, greedy descent)
+    const float* tnorm;       // [n] squared norm of the stored traversal row (bf16 sq-L2 form)
     const void* tbase;        // traversal rows [n][tstride bytes]: fp32 or bf16, zero-padded to a multiple of 8 elements
     const float* norms;       // [n] Java norm of the stored row (cosine), else nullptr
     const int32_t* ids;       // [n] external ids
@@ -32,7 +33,7 @@ struct HnswSearchParams {
     const float* queries;     // [nq][dim]
     int32_t* out_ids;         // [nq][k]
     float* out_dists;         // [nq][k]
-    unsigned long long* counters;  // [2] dist evals, expansions
+    unsigned long long* counters;  // [16]: dist evals, expansions, then 8 phase cycle counters (profile)
     uint32_t* visited_scratch;     // [grid][ceil(n/32)] when the bitset does not fit in shared memory
     int n, dim, deg, max_level, entry;
     int pq_m, trained;
@@ -41,12 +42,13 @@ struct HnswSearchParams {
     int ef, k, nq;
     int tstride, tstore;      // bytes per traversal row (multiple of 16); 0 = fp32, 1 = bf16
     int batch;                // candidates expanded per round (1 = the Java order)
+    int profile;              // accumulate thread-0 cycle counters per phase into counters[2..9]
     int visited_in_smem;
 };
 int launch_hnsw_search(const HnswSearchParams& p, int grid, cudaStream_t st);
 size_t hnsw_search_smem_bytes(const HnswSearchParams& p);
 int hnsw_max_batch(int deg);
-void launch_make_traversal_rows(const float* d_base, int64_t n, int dim, int dpad, int bf16, void* d_out, cudaStream_t st);
+void launch_make_traversal_rows(const float* d_base, int64_t n, int dim, int dpad, int bf16, void* d_out, float* d_tnorm, cudaStream_t st);
 
 // flat_kernels.cu
 void launch_flat_search_exact(const float* d_base, const float* d_norms, const int32_t* d_ids, int id_offset, int64_t n, int dim,

@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <numeric>
 
@@ -80,8 +81,8 @@ extern "C" int vdb_create(const vdb_config* cfg, vdb_index** out) {
     }
     if (cudaStreamCreateWithFlags(&x->stream, cudaStreamNonBlocking) != cudaSuccess) { delete x; FAIL(VDB_ERR_CUDA, "stream create failed"); }
     cudaEventCreate(&x->ev_total0); cudaEventCreate(&x->ev_total1); cudaEventCreate(&x->ev_k0); cudaEventCreate(&x->ev_k1);
-    if (x->d_counters.ensure(2, 0, x->stream) != VDB_OK) { delete x; return VDB_ERR_CUDA; }
-    cudaMemsetAsync(x->d_counters.p, 0, 2 * sizeof(unsigned long long), x->stream);
+    if (x->d_counters.ensure(16, 0, x->stream) != VDB_OK) { delete x; return VDB_ERR_CUDA; }
+    cudaMemsetAsync(x->d_counters.p, 0, 16 * sizeof(unsigned long long), x->stream);
     *out = x;
     return VDB_OK;
 }
@@ -92,7 +93,7 @@ extern "C" int vdb_destroy(vdb_index* x) {
     if (x->stream) cudaStreamSynchronize(x->stream);
     x->d_base.release(); x->d_norms.release(); x->d_cb.release(); x->d_ids.release(); x->d_adj.release(); x->d_codes.release();
     x->d_q.release(); x->d_out_d.release(); x->d_lut.release(); x->d_out_ids.release(); x->d_keys.release(); x->d_keys_tmp.release();
-    x->d_rows.release(); x->d_rows_tmp.release(); x->d_visited.release(); x->d_counters.release(); x->d_trav.release();
+    x->d_rows.release(); x->d_rows_tmp.release(); x->d_visited.release(); x->d_counters.release(); x->d_trav.release(); x->d_tnorm.release();
     x->d_train.release(); x->d_sub.release(); x->d_mind.release(); x->d_asg.release();
     x->p_q.release(); x->p_d.release(); x->p_ids.release();
     if (x->ev_total0) { cudaEventDestroy(x->ev_total0); cudaEventDestroy(x->ev_total1); cudaEventDestroy(x->ev_k0); cudaEventDestroy(x->ev_k1); }
@@ -132,8 +133,10 @@ static int build_traversal_rows(vdb_index* x) {
     if (x->n_trav >= x->n_dev) return VDB_OK;
     const size_t stride = (size_t)trav_stride(x);
     VDB_TRY(x->d_trav.ensure((size_t)x->n_dev * stride, (size_t)x->n_trav * stride, x->stream));
+    VDB_TRY(x->d_tnorm.ensure((size_t)x->n_dev, (size_t)x->n_trav, x->stream));
     launch_make_traversal_rows(x->d_base.p + (size_t)x->n_trav * x->cfg.dim, x->n_dev - x->n_trav, x->cfg.dim, trav_dpad(x),
-                               x->cfg.trav_store == VDB_TRAV_F32 ? 0 : 1, x->d_trav.p + (size_t)x->n_trav * stride, x->stream);
+                               x->cfg.trav_store == VDB_TRAV_F32 ? 0 : 1, x->d_trav.p + (size_t)x->n_trav * stride,
+                               x->d_tnorm.p + x->n_trav, x->stream);
     VDB_CUDA(cudaGetLastError());
     VDB_CUDA(cudaStreamSynchronize(x->stream));
     x->n_trav = x->n_dev;
@@ -421,12 +424,14 @@ static int search_graph(vdb_index* x, const float* d_q, int64_t nq, int k, int32
     } else { p.variant = 2; p.ef = std::max(x->cfg.ef_search, k * 4); }        // HnswIndex.java:347
     p.ef = (int)std::min<int64_t>(p.ef, std::max<int64_t>(x->n, 1));
     p.k = k; p.nq = (int)nq;
-    p.tbase = x->d_trav.p; p.tstride = trav_stride(x); p.tstore = x->cfg.trav_store == VDB_TRAV_F32 ? 0 : 1;
-    p.batch = x->cfg.trav_batch > 0 ? x->cfg.trav_batch : std::max(4, std::min(32, p.ef / 128));
+    p.tbase = x->d_trav.p; p.tnorm = x->d_tnorm.p; p.tstride = trav_stride(x); p.tstore = x->cfg.trav_store == VDB_TRAV_F32 ? 0 : 1;
+    p.batch = x->cfg.trav_batch > 0 ? x->cfg.trav_batch : (p.ef >= 4096 ? 64 : std::max(4, std::min(32, p.ef / 128)));
     p.batch = std::max(1, std::min(p.batch, hnsw_max_batch(p.deg)));
+    p.profile = getenv("VDB_HNSW_PROFILE") ? 1 : 0;
+    if (const char* eb = getenv("VDB_HNSW_BATCH")) p.batch = std::max(1, std::min(atoi(eb), hnsw_max_batch(p.deg)));
     p.visited_in_smem = 1;
     size_t smem = hnsw_search_smem_bytes(p);
-    if (smem > 110 * 1024) { p.visited_in_smem = 0; smem = hnsw_search_smem_bytes(p); }
+    if (smem > 112 * 1024) { p.visited_in_smem = 0; smem = hnsw_search_smem_bytes(p); }
     if (smem > 227 * 1024) FAIL(VDB_ERR_INVALID, "ef too large for the shared-memory pool");
     int per_sm = (int)std::max<size_t>(1, std::min<size_t>(2, (227 * 1024) / (smem + 1024)));
     int grid = (int)std::min<int64_t>(nq, (int64_t)x->num_sms * per_sm);
@@ -567,8 +572,11 @@ extern "C" int vdb_get_stats(vdb_index* x, vdb_stats* out) {
         cudaEventElapsedTime(&x->stats.last_total_ms, x->ev_total0, x->ev_total1);
         if (cudaEventElapsedTime(&x->stats.last_kernel_ms, x->ev_k0, x->ev_k1) != cudaSuccess) { x->stats.last_kernel_ms = 0; cudaGetLastError(); }
     }
-    unsigned long long c[2] = {0, 0};
+    unsigned long long c[16] = {0};
     VDB_CUDA(cudaMemcpy(c, x->d_counters.p, sizeof(c), cudaMemcpyDeviceToHost));
+    if (getenv("VDB_HNSW_PROFILE"))
+        fprintf(stderr, "[vdb hnsw profile] cycles: setup %llu select %llu gather %llu dist %llu sort %llu merge %llu final %llu | rounds %llu\n",
+                c[2], c[3], c[4], c[5], c[6], c[7], c[8], c[9]);
     x->stats.dist_evals = (int64_t)c[0]; x->stats.expansions = (int64_t)c[1];
     *out = x->stats;
     return VDB_OK;

@@ -79,6 +79,7 @@ struct vdb_index {
     DevBuf<uint8_t> d_codes;
     DevBuf<unsigned char> d_trav;   // traversal rows (bf16 or padded fp32), rebuilt when rows are uploaded
     int64_t n_trav = 0;
+    DevBuf<float> d_tnorm;          // squared norms of the traversal rows
     int64_t n_dev = 0;              // rows present in d_base / d_ids
     int64_t n_coded = 0;            // rows with valid codes in d_codes
 
