@@ -31,8 +31,16 @@ def test_library_exports_every_declared_symbol():
 def test_struct_layout_matches_header():
     import ctypes as C
     from vector_db_b200._lib import VdbConfig, VdbStats
-    assert C.sizeof(VdbConfig) == 16 * 4 + 8
-    assert C.sizeof(VdbStats) == 4 * 8 + 2 * 4
+    # ask the C compiler what include/vdb.h lays out, and compare with the ctypes mirror
+    import subprocess, tempfile
+    src = ('#include <stdio.h>\n#include <stddef.h>\n#include "vdb.h"\nint main(){printf("%zu %zu %zu %zu %zu\\n", sizeof(vdb_config), '
+           'offsetof(vdb_config, level_seed), offsetof(vdb_config, trav_store), sizeof(vdb_stats), offsetof(vdb_stats, last_kernel_ms));return 0;}')
+    with tempfile.TemporaryDirectory() as d:
+        open(os.path.join(d, "t.c"), "w").write(src)
+        subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), "-o", os.path.join(d, "t"), os.path.join(d, "t.c")])
+        want = [int(x) for x in subprocess.check_output([os.path.join(d, "t")]).split()]
+    got = [C.sizeof(VdbConfig), VdbConfig.level_seed.offset, VdbConfig.trav_store.offset, C.sizeof(VdbStats), VdbStats.last_kernel_ms.offset]
+    assert got == want, (got, want)
 
 
 def test_no_cpu_fallback_without_gpu():
