@@ -171,6 +171,45 @@ def test_flat_ties_broken_by_id_and_padding(v, po):
     f.close()
 
 
+@pytest.mark.parametrize("n,dim,M,k,rerank", [(20000, 1000, 125, 10, 0), (20000, 1000, 125, 10, 500), (5000, 96, 12, 100, 0),
+                                               (777, 64, 64, 5, 0), (40000, 512, 64, 10, 1000)])
+def test_adc_fast_scan_bit_exact(v, po, n, dim, M, k, rerank):
+    """adc_fast.cu: transposed codes + conflict-free LUT gathers + certified shortlist must return exactly what the
+    reference's sequential scan (PQIndex.cpp:173-205, order R3, (dist,id)) returns — ids AND distance bits — for ragged M
+    (125 = 3 full lane groups + 29), M < 32, n not a multiple of 16, and with the fp32 rerank of C5."""
+    nq = 24
+    X, Q = po.synth(42, n, dim), po.synth(43, nq, dim)
+    p = v.NativePqIndex(dim, n, M=M, rerank=rerank)
+    p.train(X[:1500])
+    p.addBatch(np.arange(n, dtype=np.int32), X)
+    cb = p.codebooks()
+    codes = po.pq_encode(X, cb, po.ARITH_NATIVE_AVX2)
+    assert np.array_equal(p.codes(), codes)
+    ids, d = p.searchBatch(Q, k)
+    oi, od = po.pq_flat_search(Q, cb, codes, k, po.ARITH_NATIVE_AVX2, rerank=rerank, base=X, exact_order=1, nthreads=8)
+    assert np.array_equal(ids, oi)
+    assert np.array_equal(bits(d), bits(od))
+    p.close()
+
+
+def test_adc_fast_scan_tie_fallback(v, po):
+    """100 copies of each of 50 vectors: every ADC distance is a 100-way tie, the fast scan's shortlist cannot be
+    certified and the query is redone by the exact kernel — the answer is still the reference's ((dist,id): lowest ids)."""
+    dim, M, k = 64, 8, 10
+    B = po.synth(5, 50, dim)
+    X = np.repeat(B, 100, axis=0)
+    Q = po.synth(6, 16, dim)
+    p = v.NativePqIndex(dim, len(X), M=M)
+    p.train(po.synth(7, 1000, dim))
+    p.addBatch(np.arange(len(X), dtype=np.int32), X)
+    cb = p.codebooks()
+    codes = po.pq_encode(X, cb, po.ARITH_NATIVE_AVX2)
+    ids, d = p.searchBatch(Q, k)
+    oi, od = po.pq_flat_search(Q, cb, codes, k, po.ARITH_NATIVE_AVX2, nthreads=8)
+    assert np.array_equal(ids, oi) and np.array_equal(bits(d), bits(od))
+    p.close()
+
+
 # ---------------------------------------------------------------- HNSW(+PQ) traversal
 def _load_oracle_state(g, o, codes=None):
     g.set_codebooks(o.codebooks())

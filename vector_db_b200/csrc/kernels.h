@@ -6,7 +6,15 @@
 void launch_pq_lut(const float* d_q, const float* d_cb, int nq, int dim, int M, int arith, float* d_lut, cudaStream_t st);
 void launch_adc_scan_topr(const uint8_t* d_codes, int64_t n, int M, const float* d_luts, int nq, const int32_t* d_ids,
                           int id_offset, int R, int nchunks, uint64_t* d_keys_tmp, uint32_t* d_rows_tmp, uint64_t* d_keys,
-                          uint32_t* d_rows, cudaStream_t st);
+                          uint32_t* d_rows, cudaStream_t st, const int* only_flag = nullptr);
+// adc_fast.cu
+void launch_transpose_codes(const uint8_t* d_codes, int64_t n, int M, int64_t row0, uint8_t* d_codesT, cudaStream_t st);
+void launch_lut_to_gather_layout(const float* d_lut, int nq, int M, float* d_lutg, cudaStream_t st);
+int adc_fast_supported(int M, int R);
+int adc_fast_r2(int R);
+int launch_adc_scan_fast(const uint8_t* d_codesT, const uint8_t* d_codes, int64_t n, int M, const float* d_luts, const float* d_lutg, int nq,
+                         const int32_t* d_ids, int id_offset, int R, int nchunks, uint64_t* d_keys_tmp, uint32_t* d_rows_tmp,
+                         uint64_t* d_keys, uint32_t* d_rows, int* d_flag, cudaStream_t st);
 void launch_merge_keys(const uint64_t* d_in_keys, const uint32_t* d_in_rows, int nq, int nlists, int R, uint64_t* d_keys,
                        uint32_t* d_rows, cudaStream_t st);
 void launch_keys_to_results(const uint64_t* d_keys, int R, int k, int64_t nq, int32_t* d_ids, float* d_dists, cudaStream_t st);

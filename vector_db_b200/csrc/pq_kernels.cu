@@ -36,7 +36,8 @@ template <int NT>
 __global__ void __launch_bounds__(NT)
 adc_scan_topr_kernel(const uint8_t* __restrict__ codes, int64_t n, int M, const float* __restrict__ luts,
                      const int32_t* __restrict__ ids, int id_offset, int R, int cap, int64_t rows_per_chunk,
-                     uint64_t* __restrict__ out_keys, uint32_t* __restrict__ out_rows) {
+                     uint64_t* __restrict__ out_keys, uint32_t* __restrict__ out_rows, const int* __restrict__ only_flag) {
+    if (only_flag && !only_flag[blockIdx.y]) return;      // fallback launch: only queries the fast scan could not certify
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float* lut = reinterpret_cast<float*>(smem_raw);
     uint64_t* bkey = reinterpret_cast<uint64_t*>(lut + (size_t)M * VDB_NCENT);
@@ -119,17 +120,18 @@ void launch_merge_keys(const uint64_t* d_in_keys, const uint32_t* d_in_rows, int
 }
 void launch_adc_scan_topr(const uint8_t* d_codes, int64_t n, int M, const float* d_luts, int nq, const int32_t* d_ids,
                           int id_offset, int R, int nchunks, uint64_t* d_keys_tmp, uint32_t* d_rows_tmp, uint64_t* d_keys,
-                          uint32_t* d_rows, cudaStream_t st) {
+                          uint32_t* d_rows, cudaStream_t st, const int* only_flag) {
     constexpr int NT = 256;
+    if (only_flag) nchunks = 1;
     const int cap = next_pow2(R + NT);
     const size_t smem = (size_t)M * VDB_NCENT * 4 + (size_t)cap * 12;
     cudaFuncSetAttribute(adc_scan_topr_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     const int64_t rpc = (n + nchunks - 1) / nchunks;
     dim3 grid(nchunks, nq);
     if (nchunks == 1) {
-        adc_scan_topr_kernel<NT><<<grid, NT, smem, st>>>(d_codes, n, M, d_luts, d_ids, id_offset, R, cap, rpc, d_keys, d_rows);
+        adc_scan_topr_kernel<NT><<<grid, NT, smem, st>>>(d_codes, n, M, d_luts, d_ids, id_offset, R, cap, rpc, d_keys, d_rows, only_flag);
     } else {
-        adc_scan_topr_kernel<NT><<<grid, NT, smem, st>>>(d_codes, n, M, d_luts, d_ids, id_offset, R, cap, rpc, d_keys_tmp, d_rows_tmp);
+        adc_scan_topr_kernel<NT><<<grid, NT, smem, st>>>(d_codes, n, M, d_luts, d_ids, id_offset, R, cap, rpc, d_keys_tmp, d_rows_tmp, nullptr);
         launch_merge_keys(d_keys_tmp, d_rows_tmp, nq, nchunks, R, d_keys, d_rows, st);
     }
 }

@@ -93,7 +93,7 @@ extern "C" int vdb_destroy(vdb_index* x) {
     if (x->stream) cudaStreamSynchronize(x->stream);
     x->d_base.release(); x->d_norms.release(); x->d_cb.release(); x->d_ids.release(); x->d_adj.release(); x->d_codes.release();
     x->d_q.release(); x->d_out_d.release(); x->d_lut.release(); x->d_out_ids.release(); x->d_keys.release(); x->d_keys_tmp.release();
-    x->d_rows.release(); x->d_rows_tmp.release(); x->d_visited.release(); x->d_counters.release(); x->d_trav.release(); x->d_tnorm.release();
+    x->d_rows.release(); x->d_rows_tmp.release(); x->d_visited.release(); x->d_counters.release(); x->d_trav.release(); x->d_tnorm.release(); x->d_codesT.release(); x->d_lutg.release(); x->d_flag.release();
     x->d_train.release(); x->d_sub.release(); x->d_mind.release(); x->d_asg.release();
     x->p_q.release(); x->p_d.release(); x->p_ids.release();
     if (x->ev_total0) { cudaEventDestroy(x->ev_total0); cudaEventDestroy(x->ev_total1); cudaEventDestroy(x->ev_k0); cudaEventDestroy(x->ev_k1); }
@@ -178,8 +178,19 @@ static int encode_pending(vdb_index* x) {
             FAIL(VDB_ERR_INVALID, "encode launch rejected");
         VDB_CUDA(cudaGetLastError());
     }
-    if (x->codes_overridden && (int64_t)x->h_codes_override.size() == x->n_dev * M)
+    if (x->codes_overridden && (int64_t)x->h_codes_override.size() == x->n_dev * M) {
         VDB_CUDA(cudaMemcpyAsync(x->d_codes.p, x->h_codes_override.data(), x->h_codes_override.size(), cudaMemcpyHostToDevice, x->stream));
+        x->n_codesT = 0;
+    }
+    if (x->cfg.index_type == VDB_INDEX_PQ) {
+        // scan layout: 16-row blocks, subspace-major (adc_fast.cu); blocks that were complete stay, the rest is rewritten
+        if (x->n_codesT > x->n_coded) x->n_codesT = x->n_coded;
+        const int64_t row0 = x->n_codesT & ~(int64_t)15;
+        VDB_TRY(x->d_codesT.ensure((size_t)((x->n_dev + 15) / 16) * M * 16, (size_t)(row0 / 16) * M * 16, x->stream));
+        launch_transpose_codes(x->d_codes.p, x->n_dev, M, row0, x->d_codesT.p, x->stream);
+        VDB_CUDA(cudaGetLastError());
+        x->n_codesT = x->n_dev;
+    }
     VDB_CUDA(cudaStreamSynchronize(x->stream));
     x->n_coded = x->n_dev;
     return VDB_OK;
@@ -463,20 +474,38 @@ static int search_pq(vdb_index* x, const float* d_q, int64_t nq, int k, int32_t*
     const int M = x->pq_m, dim = x->cfg.dim;
     const int R = x->cfg.rerank > 0 ? std::max(x->cfg.rerank, k) : k;
     if (R > 4096) FAIL(VDB_ERR_INVALID, "rerank shortlist > 4096 not supported");
-    const int64_t QB = 1024;   // query sub-batch: bounds the LUT buffer (QB * M * 1 KB)
+    const int64_t QB = 1024;   // query sub-batch: bounds the LUT buffers (QB * M * 1 KB each)
     const int32_t* ids = x->device_only ? nullptr : x->d_ids.p;
+    const bool fast = adc_fast_supported(M, R) && !getenv("VDB_ADC_EXACT_SCAN");
+    const int R2 = fast ? adc_fast_r2(R) : R;
     for (int64_t q0 = 0; q0 < nq; q0 += QB) {
         const int64_t qb = std::min(QB, nq - q0);
-        const int nch = pick_chunks(x, qb, x->n, R);
+        const int nch = pick_chunks(x, qb, x->n, R2);
         VDB_TRY(x->d_lut.ensure((size_t)qb * M * VDB_NCENT, 0, st));
         VDB_TRY(x->d_keys.ensure((size_t)qb * R, 0, st));
         VDB_TRY(x->d_rows.ensure((size_t)qb * R, 0, st));
-        if (nch > 1) { VDB_TRY(x->d_keys_tmp.ensure((size_t)qb * R * nch, 0, st)); VDB_TRY(x->d_rows_tmp.ensure((size_t)qb * R * nch, 0, st)); }
+        VDB_TRY(x->d_keys_tmp.ensure((size_t)qb * R2 * (nch + 1), 0, st));
+        VDB_TRY(x->d_rows_tmp.ensure((size_t)qb * R2 * (nch + 1), 0, st));
         launch_pq_lut(d_q + q0 * dim, x->d_cb.p, (int)qb, dim, M, x->cfg.arith, x->d_lut.p, st);
-        if (x->timed && q0 == 0) cudaEventRecord(x->ev_k0, st);
-        launch_adc_scan_topr(x->d_codes.p, x->n, M, x->d_lut.p, (int)qb, ids, x->cfg.id_offset, R, nch, x->d_keys_tmp.p, x->d_rows_tmp.p,
-                             x->d_keys.p, x->d_rows.p, st);
-        if (x->timed && q0 == 0) cudaEventRecord(x->ev_k1, st);
+        if (fast) {
+            const int groups = (M + 63) / 64;
+            VDB_TRY(x->d_lutg.ensure((size_t)qb * groups * 16384, 0, st));
+            VDB_TRY(x->d_flag.ensure((size_t)qb, 0, st));
+            launch_lut_to_gather_layout(x->d_lut.p, (int)qb, M, x->d_lutg.p, st);
+            if (x->timed && q0 == 0) cudaEventRecord(x->ev_k0, st);
+            if (launch_adc_scan_fast(x->d_codesT.p, x->d_codes.p, x->n, M, x->d_lut.p, x->d_lutg.p, (int)qb, ids, x->cfg.id_offset, R, nch,
+                                     x->d_keys_tmp.p, x->d_rows_tmp.p, x->d_keys.p, x->d_rows.p, x->d_flag.p, st) != 0)
+                FAIL(VDB_ERR_INVALID, "fast ADC scan rejected the launch");
+            if (x->timed && q0 == 0) cudaEventRecord(x->ev_k1, st);
+            // queries whose shortlist could not be certified (massive ties) are redone in the reference's own order
+            launch_adc_scan_topr(x->d_codes.p, x->n, M, x->d_lut.p, (int)qb, ids, x->cfg.id_offset, R, 1, nullptr, nullptr, x->d_keys.p,
+                                 x->d_rows.p, st, x->d_flag.p);
+        } else {
+            if (x->timed && q0 == 0) cudaEventRecord(x->ev_k0, st);
+            launch_adc_scan_topr(x->d_codes.p, x->n, M, x->d_lut.p, (int)qb, ids, x->cfg.id_offset, R, nch, x->d_keys_tmp.p, x->d_rows_tmp.p,
+                                 x->d_keys.p, x->d_rows.p, st);
+            if (x->timed && q0 == 0) cudaEventRecord(x->ev_k1, st);
+        }
         if (x->cfg.rerank > 0)
             launch_rerank(x->d_base.p, ids, x->cfg.id_offset, dim, d_q + q0 * dim, (int)qb, x->d_rows.p, R,
                           x->cfg.arith == VDB_ARITH_NATIVE_AVX2 ? ORDER_R1 : ORDER_SEQ, k, d_ids + q0 * k, d_dists + q0 * k, st);

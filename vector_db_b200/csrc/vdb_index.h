@@ -77,6 +77,8 @@ struct vdb_index {
     DevBuf<float> d_base, d_norms, d_cb;
     DevBuf<int32_t> d_ids, d_adj;
     DevBuf<uint8_t> d_codes;
+    DevBuf<uint8_t> d_codesT;       // PQ index: codes transposed in 16-row blocks [ceil(n/16)][M][16] (adc_fast.cu)
+    int64_t n_codesT = 0;           // rows present in d_codesT
     DevBuf<unsigned char> d_trav;   // traversal rows (bf16 or padded fp32), rebuilt when rows are uploaded
     int64_t n_trav = 0;
     DevBuf<float> d_tnorm;          // squared norms of the traversal rows
@@ -97,7 +99,8 @@ struct vdb_index {
     bool graph_uploaded = false;
 
     // search scratch
-    DevBuf<float> d_q, d_out_d, d_lut;
+    DevBuf<float> d_q, d_out_d, d_lut, d_lutg;
+    DevBuf<int> d_flag;
     DevBuf<int32_t> d_out_ids;
     DevBuf<uint64_t> d_keys, d_keys_tmp;
     DevBuf<uint32_t> d_rows, d_rows_tmp, d_visited;
