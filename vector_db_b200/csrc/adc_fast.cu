@@ -26,15 +26,18 @@
 #define AF_K 8                                  // 16-row blocks per warp between barriers
 #define AF_SPAN (16 * AF_WARPS * AF_K)          // rows per super-iteration (= max insertions between barriers)
 
-// ---- codes [n][M] -> codesT [ceil(n/16)][M][16]; rows past n are code 0 (never reported: row < n is checked) ----
+// ---- codes [n][M] -> codesT [ceil(n/16)][M][16]; rows past n are code 0 (never reported: row < n is checked).
+//      Inside a chunk the 16 rows are stored in the order the reading lane's butterfly wants (see the scan kernel): byte a
+//      = row a ^ p(lane), which removes every select from the transposing reduction. ----
 __global__ void transpose_codes_kernel(const uint8_t* __restrict__ codes, int64_t n, int M, int64_t row0, uint8_t* __restrict__ codesT) {
     // one thread per output byte of blocks covering rows [row0, n)
     const int64_t b0 = row0 >> 4;
     const int64_t total = (((n + 15) >> 4) - b0) * (int64_t)M * 16;
     for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
-        const int r = (int)(t & 15);
         const int64_t bm = t >> 4;
         const int m = (int)(bm % M);
+        const int l = m & 31;             // the lane that reads this 16-byte chunk; byte a holds row a ^ p(l), p = row_of_lane
+        const int r = (int)(t & 15) ^ ((((l >> 4) & 1) << 3) | (((l >> 3) & 1) << 2) | (((l >> 2) & 1) << 1) | ((l >> 1) & 1));
         const int64_t row = ((b0 + bm / M) << 4) + r;
         codesT[(b0 * M << 4) + t] = row < n ? codes[row * M + m] : (uint8_t)0;
     }
@@ -69,14 +72,45 @@ __device__ __forceinline__ uint4 ld_stream(const uint4* p) {     // codes are re
     return r;
 }
 
+// loads are never predicated: a lane past M reads the row's last chunk (its LUT column is all zero, so whatever it gathers
+// adds 0.0), a block past the chunk's end re-reads the last valid block (its rows are not reported)
 template <int NJ>
-__device__ __forceinline__ void load_block(const uint4* __restrict__ codesT, int64_t blk, int64_t blk_end, int M, int lane, uint4 (&v)[NJ]) {
+__device__ __forceinline__ void load_block(const uint4* __restrict__ p, int lastoff, uint4 (&v)[NJ]) {
+#pragma unroll
+    for (int j = 0; j < NJ - 1; j++) v[j] = ld_stream(p + 32 * j);
+    v[NJ - 1] = ld_stream(p + lastoff);
+}
+
+// gather + transposing butterfly for one 16-row block held in v[]; returns this lane's row total (valid on every lane pair)
+template <int NJ>
+__device__ __forceinline__ float block_distance(const uint4 (&v)[NJ], const uint32_t (&lbase)[NJ], const unsigned char* __restrict__ lutb) {
+    float acc[16];
 #pragma unroll
     for (int j = 0; j < NJ; j++) {
-        const int m = lane + 32 * j;
-        v[j] = make_uint4(0u, 0u, 0u, 0u);
-        if (blk < blk_end && m < M) v[j] = ld_stream(codesT + blk * M + m);
+        const uint32_t w[4] = {v[j].x, v[j].y, v[j].z, v[j].w};
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const float v0 = *reinterpret_cast<const float*>(lutb + __byte_perm(w[i], lbase[j], 0x7604));
+            const float v1 = *reinterpret_cast<const float*>(lutb + __byte_perm(w[i], lbase[j], 0x7614));
+            const float v2 = *reinterpret_cast<const float*>(lutb + __byte_perm(w[i], lbase[j], 0x7624));
+            const float v3 = *reinterpret_cast<const float*>(lutb + __byte_perm(w[i], lbase[j], 0x7634));
+            if (j == 0) { acc[4 * i + 0] = v0; acc[4 * i + 1] = v1; acc[4 * i + 2] = v2; acc[4 * i + 3] = v3; }
+            else {
+                acc[4 * i + 0] = __fadd_rn(acc[4 * i + 0], v0); acc[4 * i + 1] = __fadd_rn(acc[4 * i + 1], v1);
+                acc[4 * i + 2] = __fadd_rn(acc[4 * i + 2], v2); acc[4 * i + 3] = __fadd_rn(acc[4 * i + 3], v3);
+            }
+        }
     }
+    // 16 partial sums x 32 lanes -> one total per row (each on two lanes). The chunk's rows were stored pre-permuted by
+    // this lane's bits (transpose_codes_kernel), so every lane keeps acc[r] and sends acc[r + half]: no selects.
+#pragma unroll
+    for (int r = 0; r < 8; r++) acc[r] = __fadd_rn(acc[r], __shfl_xor_sync(0xffffffffu, acc[r + 8], 16));
+#pragma unroll
+    for (int r = 0; r < 4; r++) acc[r] = __fadd_rn(acc[r], __shfl_xor_sync(0xffffffffu, acc[r + 4], 8));
+#pragma unroll
+    for (int r = 0; r < 2; r++) acc[r] = __fadd_rn(acc[r], __shfl_xor_sync(0xffffffffu, acc[r + 2], 4));
+    acc[0] = __fadd_rn(acc[0], __shfl_xor_sync(0xffffffffu, acc[1], 2));
+    return __fadd_rn(acc[0], __shfl_xor_sync(0xffffffffu, acc[0], 1));
 }
 
 // NJ = ceil(M/32) 16-byte loads per lane and block. grid = (chunks, queries).
@@ -108,57 +142,32 @@ adc_scan_fast_kernel(const uint4* __restrict__ codesT, int64_t n, int M, const f
     const unsigned char* lutb = reinterpret_cast<const unsigned char*>(lut);
     const int row_of_lane = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
 
-    uint4 cur[NJ], nxt[NJ];
-    load_block<NJ>(codesT, b0 + warp, b1, M, lane, cur);
-    for (int64_t sb = b0; sb < b1; sb += AF_WARPS * AF_K) {
+    // block indices relative to the chunk start (32-bit); rows of the chunk that exist: nrel
+    const int nb = (int)(b1 - b0);
+    const int nrel = (int)min((int64_t)nb << 4, n - (b0 << 4));
+    const int lastoff = min(lane + 32 * (NJ - 1), M - 1) - lane;
+    const int64_t bstride = (int64_t)AF_WARPS * M;
+    const uint4* bp = codesT + (b0 + min(warp, nb - 1)) * M + lane;     // this lane's chunk of this warp's current block
+    uint4 va[NJ], vb[NJ];
+    load_block<NJ>(bp, lastoff, va);
+    auto advance = [&](int next_blk) { if (next_blk < nb) bp += bstride; };   // clamp: past the end, re-read the last block
+    auto report = [&](float d, int blk) {
+        const int row = (blk << 4) + row_of_lane;
+        if (!(lane & 1) && row < nrel && d < s_tau) {
+            const int slot = atomicAdd(&s_cnt, 1);
+            buf[slot] = ((uint64_t)f2ord(d) << 32) | (uint32_t)((b0 << 4) + row);
+        }
+    };
+    for (int sb = 0; sb < nb; sb += AF_WARPS * AF_K) {
 #pragma unroll 1
-        for (int kk = 0; kk < AF_K; kk++) {
-            const int64_t blk = sb + (int64_t)kk * AF_WARPS + warp;
-            load_block<NJ>(codesT, blk + AF_WARPS, b1, M, lane, nxt);   // this warp's next block (also across the barrier)
-            float acc[16];
-#pragma unroll
-            for (int r = 0; r < 16; r++) acc[r] = 0.0f;
-#pragma unroll
-            for (int j = 0; j < NJ; j++) {
-                if (lane + 32 * j < M) {
-                    const uint32_t w[4] = {cur[j].x, cur[j].y, cur[j].z, cur[j].w};
-#pragma unroll
-                    for (int i = 0; i < 4; i++) {
-                        acc[4 * i + 0] = __fadd_rn(acc[4 * i + 0], *reinterpret_cast<const float*>(lutb + __byte_perm(w[i], lbase[j], 0x7604)));
-                        acc[4 * i + 1] = __fadd_rn(acc[4 * i + 1], *reinterpret_cast<const float*>(lutb + __byte_perm(w[i], lbase[j], 0x7614)));
-                        acc[4 * i + 2] = __fadd_rn(acc[4 * i + 2], *reinterpret_cast<const float*>(lutb + __byte_perm(w[i], lbase[j], 0x7624)));
-                        acc[4 * i + 3] = __fadd_rn(acc[4 * i + 3], *reinterpret_cast<const float*>(lutb + __byte_perm(w[i], lbase[j], 0x7634)));
-                    }
-                }
-            }
-            // transposing butterfly: 16 partial sums x 32 lanes -> one total per row (each on two lanes)
-#pragma unroll
-            for (int r = 0; r < 8; r++) {
-                const float send = (lane & 16) ? acc[r] : acc[r + 8], keep = (lane & 16) ? acc[r + 8] : acc[r];
-                acc[r] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, 16));
-            }
-#pragma unroll
-            for (int r = 0; r < 4; r++) {
-                const float send = (lane & 8) ? acc[r] : acc[r + 4], keep = (lane & 8) ? acc[r + 4] : acc[r];
-                acc[r] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, 8));
-            }
-#pragma unroll
-            for (int r = 0; r < 2; r++) {
-                const float send = (lane & 4) ? acc[r] : acc[r + 2], keep = (lane & 4) ? acc[r + 2] : acc[r];
-                acc[r] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, 4));
-            }
-            {
-                const float send = (lane & 2) ? acc[0] : acc[1], keep = (lane & 2) ? acc[1] : acc[0];
-                acc[0] = __fadd_rn(keep, __shfl_xor_sync(0xffffffffu, send, 2));
-            }
-            const float d = __fadd_rn(acc[0], __shfl_xor_sync(0xffffffffu, acc[0], 1));
-            const int64_t row = (blk << 4) + row_of_lane;
-            if (!(lane & 1) && blk < b1 && row < n && d < s_tau) {
-                const int slot = atomicAdd(&s_cnt, 1);
-                buf[slot] = ((uint64_t)f2ord(d) << 32) | (uint32_t)row;
-            }
-#pragma unroll
-            for (int j = 0; j < NJ; j++) cur[j] = nxt[j];
+        for (int kk = 0; kk < AF_K; kk += 2) {
+            const int blk = sb + kk * AF_WARPS + warp;
+            advance(blk + AF_WARPS);
+            load_block<NJ>(bp, lastoff, vb);                           // next block in flight while this one is gathered
+            report(block_distance<NJ>(va, lbase, lutb), blk);
+            advance(blk + 2 * AF_WARPS);
+            load_block<NJ>(bp, lastoff, va);
+            report(block_distance<NJ>(vb, lbase, lutb), blk + AF_WARPS);
         }
         __syncthreads();
         if (s_cnt > cap - AF_SPAN) {                      // uniform: s_cnt only changes between barriers
