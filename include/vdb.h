@@ -83,6 +83,8 @@ typedef struct vdb_stats {
     int64_t adc_rows;        /* PQ code rows scanned */
     float last_kernel_ms;    /* device time of the dominant kernel of the last search (CUDA events) */
     float last_total_ms;     /* device time of the whole last search */
+    int64_t flat_certified;  /* flat search: queries answered by the tensor-core shortlist and certified exact */
+    int64_t flat_fallback;   /* flat search: queries that failed certification and were re-run by the order-exact scan */
 } vdb_stats;
 
 const char* vdb_last_error(void);

@@ -32,7 +32,7 @@ class VdbConfig(C.Structure):
 
 class VdbStats(C.Structure):
     _fields_ = [("queries", C.c_int64), ("dist_evals", C.c_int64), ("expansions", C.c_int64), ("adc_rows", C.c_int64),
-                ("last_kernel_ms", C.c_float), ("last_total_ms", C.c_float)]
+                ("last_kernel_ms", C.c_float), ("last_total_ms", C.c_float), ("flat_certified", C.c_int64), ("flat_fallback", C.c_int64)]
 
 
 class VdbError(RuntimeError):

@@ -1,0 +1,579 @@
+// flat_gemm.cu — brute-force flat search (a6, a13; SURVEY.md §8 row "Flat search / batched rerank as GEMM") on the
+// 5th-generation tensor cores: a bf16 query x base contraction (tcgen05.mma, operands staged by TMA into 128B-swizzled
+// shared memory, fp32 accumulators in TMEM) whose epilogue never writes the Q x N matrix — it turns each accumulator
+// into an approximate distance, compares it with a per-query threshold and appends the few survivors to a per-query
+// candidate list. The shortlist is then re-scored in fp32 in the reference's own summation order
+// (HnswPqIndex.java:741-750 / DistanceAVX2.cpp:9-33 / HnswIndex.java:126-133) and CERTIFIED: a query's answer is
+// accepted only if the k-th exact distance is strictly below a rigorous lower bound on the exact distance of every row
+// that was not re-scored; otherwise the query is flagged and answered by the order-exact scan in flat_kernels.cu.
+// So ids and distances are bit-identical to the CPU reference while >99% of the arithmetic runs on tensor cores.
+//
+//   pass 0  (once per index change)  bf16 mirror of the base: rows centred on the base mean for sq-L2
+//           (||q-x||^2 is translation invariant; centring shrinks ||q'|| ||x'|| and with it the bf16 error bound),
+//           rows as stored (already normalised, HnswIndex.java:344) for cosine; per-row (a,b) with score = a + b*acc.
+//   pass 1  GEMM over a strided sample of <= 32767 rows, scores stored; per query the s-th smallest -> threshold tau.
+//   pass 2  GEMM over all rows, fused filter epilogue: score < tau -> append (score,row).
+//   pass 3  per query: sort candidates, exact fp32 re-score of the best k2, certify, emit top-k by (dist,id).
+#include "kernels.h"
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+
+namespace {
+
+constexpr int BM = 128;            // queries per tile  (UMMA M, one TMEM lane per query)
+constexpr int BN = 256;            // base rows per tile (UMMA N, one TMEM column per row)
+constexpr int BK = 64;             // bf16 per k-block = 128 bytes = one swizzle-128B row
+constexpr int UK = 16;             // K of one tcgen05.mma kind::f16
+constexpr int STAGES = 4;
+constexpr int A_BYTES = BM * BK * 2;                 // 16 KB
+constexpr int B_BYTES = BN * BK * 2;                 // 32 KB
+constexpr int STAGE_BYTES = A_BYTES + B_BYTES;       // 48 KB
+constexpr int GEMM_THREADS = 192;                    // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2..5 epilogue
+constexpr int TMEM_COLS = 512;                       // two accumulator stages of BN columns
+constexpr int SMEM_AB = 2 * BN * 8;                  // per-stage (a,b) of the tile's base rows
+constexpr int GEMM_SMEM = STAGES * STAGE_BYTES + SMEM_AB + 256 + 1024;   // + barriers + alignment slack
+
+// ---------------------------------------------------------------------------------------------------------------
+// PTX wrappers (sm_100a)
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t smem_dst, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_dst), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, both operands K-major, one thread issues for the CTA
+__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// arrive on an mbarrier once every tcgen05.mma issued so far by this thread has completed
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// 32 consecutive accumulator columns of this thread's TMEM lane
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, "
+        "%19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+          "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
+          "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+          "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// Shared-memory matrix descriptor (cute/arch/mma_sm100_desc.hpp SmemDescriptor layout): K-major tile of 128-byte rows,
+// SWIZZLE_128B (layout type 2), 8-row groups 1024 bytes apart (SBO), LBO unused for swizzled K-major (1), version 1.
+__device__ __forceinline__ uint64_t make_kmajor_sw128_desc(uint32_t saddr) {
+    return (uint64_t)((saddr >> 4) & 0x3fffu) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) |
+           ((uint64_t)2 << 61);
+}
+// Instruction descriptor (InstrDescriptor): D=f32 (bit 4), A=B=bf16 (bits 7,10), both K-major, N>>3 at bit 17, M>>4 at bit 24.
+constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+
+
+// ---------------------------------------------------------------------------------------------------------------
+// The contraction. One persistent CTA per SM walks tiles t = blockIdx.x, +gridDim.x, ...; tile t covers base rows
+// [nt*256, +256) x queries [mt*128, +128) with nt = t / m_tiles, so CTAs running at the same time share base tiles in L2
+// and the base streams from HBM once. Three pipelines: shared-memory stages (TMA -> MMA), two TMEM accumulator stages
+// (MMA -> epilogue), and the tile walk.
+// ---------------------------------------------------------------------------------------------------------------
+struct GemmArgs {
+    int m_tiles, n_tiles, k_blocks;
+    int nq;                    // valid query rows
+    int64_t n_rows;            // valid rows of the B operand (sample rows in pass 1)
+    int64_t row_step;          // B row j is base row j*row_step
+    const float2* ab;          // per base row: score = a + b*acc
+    float* scores;             // STORE: [nq][ld_scores]
+    int64_t ld_scores;
+    const float* tau;          // FILTER: per-query threshold
+    uint32_t* cnt;             // FILTER: per-query candidate count (may run past cap: overflow marker)
+    uint64_t* cand;            // FILTER: [nq][cap] (ordered score << 32 | row)
+    uint32_t cap;
+};
+
+template <bool FILTER>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+flat_gemm_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_b, const GemmArgs g) {
+    extern __shared__ unsigned char smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    const uint32_t sbase = (raw + 1023u) & ~1023u;                    // swizzle-128B tiles need 1024-byte alignment
+    unsigned char* sm = smem_raw + (sbase - raw);
+    float2* s_ab = reinterpret_cast<float2*>(sm + STAGES * STAGE_BYTES);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sm + STAGES * STAGE_BYTES + SMEM_AB);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+    const uint32_t bar0 = smem_u32(bars);
+#define BAR_FULL(s) (bar0 + 8u * (uint32_t)(s))
+#define BAR_EMPTY(s) (bar0 + 8u * (uint32_t)(STAGES + (s)))
+#define BAR_TFULL(a) (bar0 + 8u * (uint32_t)(2 * STAGES + (a)))
+#define BAR_TEMPTY(a) (bar0 + 8u * (uint32_t)(2 * STAGES + 2 + (a)))
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; s++) { mbar_init(BAR_FULL(s), 1); mbar_init(BAR_EMPTY(s), 1); }
+        for (int a = 0; a < 2; a++) { mbar_init(BAR_TFULL(a), 1); mbar_init(BAR_TEMPTY(a), 4); }
+        fence_barrier_init();
+        tma_prefetch_desc(&map_q);
+        tma_prefetch_desc(&map_b);
+    }
+    if (warp == 1) tmem_alloc(smem_u32(tmem_slot), TMEM_COLS);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
+    const int total = g.m_tiles * g.n_tiles;
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        int stage = 0; uint32_t phase = 0;
+        for (int t = blockIdx.x; t < total; t += gridDim.x) {
+            const int nt = t / g.m_tiles, mt = t - nt * g.m_tiles;
+            if (lane == 0) {
+                for (int kb = 0; kb < g.k_blocks; kb++) {
+                    mbar_wait(BAR_EMPTY(stage), phase ^ 1u);
+                    mbar_expect_tx(BAR_FULL(stage), STAGE_BYTES);
+                    tma_load_2d(sbase + stage * STAGE_BYTES, &map_q, BAR_FULL(stage), kb * BK, mt * BM);
+                    tma_load_2d(sbase + stage * STAGE_BYTES + A_BYTES, &map_b, BAR_FULL(stage), kb * BK, nt * BN);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+                }
+            }
+            __syncwarp();
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer (one thread) =====
+        int stage = 0; uint32_t phase = 0; int as = 0; uint32_t aphase = 0;
+        for (int t = blockIdx.x; t < total; t += gridDim.x) {
+            if (lane == 0) {
+                mbar_wait(BAR_TEMPTY(as), aphase ^ 1u);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + (uint32_t)(as * BN);
+                for (int kb = 0; kb < g.k_blocks; kb++) {
+                    mbar_wait(BAR_FULL(stage), phase);
+                    tc_fence_after();
+                    const uint32_t a0 = sbase + stage * STAGE_BYTES;
+                    const uint64_t ad = make_kmajor_sw128_desc(a0), bd = make_kmajor_sw128_desc(a0 + A_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BK / UK; k++)           // +32 bytes along K inside the swizzle atom = +2 in the address field
+                        umma_bf16(d_tmem, ad + (uint64_t)(k * 2), bd + (uint64_t)(k * 2), IDESC, (uint32_t)((kb | k) != 0));
+                    umma_commit(BAR_EMPTY(stage));              // frees the stage once these MMAs have read it
+                    if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+                }
+                umma_commit(BAR_TFULL(as));                     // accumulator complete -> epilogue
+            }
+            __syncwarp();
+            as ^= 1; if (as == 0) aphase ^= 1u;
+        }
+    } else {
+        // ===== epilogue: 4 warps, warp w reads TMEM lanes [32*(w&3), +32) = 32 queries =====
+        const int eq = warp & 3;
+        const int et = threadIdx.x - 64;
+        int as = 0; uint32_t aphase = 0;
+        const float INF = __int_as_float(0x7f800000);
+        for (int t = blockIdx.x; t < total; t += gridDim.x) {
+            const int nt = t / g.m_tiles, mt = t - nt * g.m_tiles;
+            float2* ab = s_ab + as * BN;
+            for (int c = et; c < BN; c += 128) {
+                const int64_t j = (int64_t)nt * BN + c;
+                float2 v = make_float2(INF, 0.0f);
+                if (j < g.n_rows) v = __ldg(g.ab + j * g.row_step);
+                ab[c] = v;
+            }
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            const int q = mt * BM + eq * 32 + lane;
+            const bool qok = q < g.nq;
+            float tau = -INF;
+            if (FILTER && qok) tau = g.tau[q];
+            mbar_wait(BAR_TFULL(as), aphase);
+            tc_fence_after();
+            const uint32_t trow = tmem_base + ((uint32_t)(eq * 32) << 16) + (uint32_t)(as * BN);
+#pragma unroll 1
+            for (int c0 = 0; c0 < BN; c0 += 64) {
+                uint32_t r[2][32];
+                tmem_ld32(trow + c0, r[0]);
+                tmem_ld32(trow + c0 + 32, r[1]);
+                tmem_ld_wait();
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    if (FILTER) {
+#pragma unroll
+                        for (int i = 0; i < 32; i++) {
+                            const float2 v = ab[c0 + h * 32 + i];
+                            const float s = fmaf(v.y, __uint_as_float(r[h][i]), v.x);
+                            if (s < tau) {
+                                const uint32_t pos = atomicAdd(g.cnt + q, 1u);
+                                if (pos < g.cap)
+                                    g.cand[(size_t)q * g.cap + pos] = ((uint64_t)f2ord(s) << 32) | (uint32_t)(nt * BN + c0 + h * 32 + i);
+                            }
+                        }
+                    } else if (qok) {
+                        float4* dst = reinterpret_cast<float4*>(g.scores + (size_t)q * g.ld_scores + (size_t)nt * BN + c0 + h * 32);
+#pragma unroll
+                        for (int i = 0; i < 32; i += 4) {
+                            float4 o;
+                            float2 v = ab[c0 + h * 32 + i];     o.x = fmaf(v.y, __uint_as_float(r[h][i]), v.x);
+                            v = ab[c0 + h * 32 + i + 1];        o.y = fmaf(v.y, __uint_as_float(r[h][i + 1]), v.x);
+                            v = ab[c0 + h * 32 + i + 2];        o.z = fmaf(v.y, __uint_as_float(r[h][i + 2]), v.x);
+                            v = ab[c0 + h * 32 + i + 3];        o.w = fmaf(v.y, __uint_as_float(r[h][i + 3]), v.x);
+                            dst[i >> 2] = o;
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(BAR_TEMPTY(as));
+            as ^= 1; if (as == 0) aphase ^= 1u;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
+#undef BAR_FULL
+#undef BAR_EMPTY
+#undef BAR_TFULL
+#undef BAR_TEMPTY
+}
+
+
+// ---------------------------------------------------------------------------------------------------------------
+// pass 0: bf16 mirrors
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void column_sum_kernel(const float* __restrict__ base, int64_t n, int dim, int64_t rows_per_block, float* __restrict__ sum) {
+    const int64_t r0 = (int64_t)blockIdx.x * rows_per_block, r1 = min(n, r0 + rows_per_block);
+    for (int d = threadIdx.x; d < dim; d += blockDim.x) {
+        float s = 0.0f;
+        for (int64_t r = r0; r < r1; r++) s += base[r * dim + d];
+        atomicAdd(sum + d, s);
+    }
+}
+
+// one warp per row: out[row][0..dpad) = bf16(x - mu) (sq-L2) or bf16(x) (cosine, rows already normalised);
+// ab[row] = (||x-mu||^2, -2) or (0, -1); rows in [n, n_pad) get (+inf, 0) so padded columns never pass the filter.
+__global__ void base_mirror_kernel(const float* __restrict__ base, int64_t n, int64_t n_pad, int dim, int dpad, int metric,
+                                   const float* __restrict__ colsum, float inv_n, __nv_bfloat16* __restrict__ out,
+                                   float2* __restrict__ ab, uint32_t* __restrict__ amax_bits) {
+    const int lane = threadIdx.x & 31;
+    const int64_t w0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, wstep = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t row = w0; row < n_pad; row += wstep) {
+        if (row >= n) { if (lane == 0) ab[row] = make_float2(__int_as_float(0x7f800000), 0.0f); continue; }
+        const float* x = base + row * dim;
+        float acc = 0.0f;
+        for (int c = lane * 2; c < dpad; c += 64) {
+            float v0 = 0.0f, v1 = 0.0f;
+            if (c < dim) v0 = x[c] - (metric == 0 ? colsum[c] * inv_n : 0.0f);
+            if (c + 1 < dim) v1 = x[c + 1] - (metric == 0 ? colsum[c + 1] * inv_n : 0.0f);
+            acc = fmaf(v0, v0, acc); acc = fmaf(v1, v1, acc);
+            *reinterpret_cast<__nv_bfloat162*>(out + row * dpad + c) = __floats2bfloat162_rn(v0, v1);
+        }
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+        if (lane == 0) {
+            ab[row] = metric == 0 ? make_float2(acc, -2.0f) : make_float2(0.0f, -1.0f);
+            atomicMax(amax_bits, __float_as_uint(acc));
+        }
+    }
+}
+
+// one CTA per query. sq-L2: q' = q - mu. cosine: q^ = q / ||q|| the Java way (HnswIndex.java:344, Vector.java:93-116),
+// kept in fp32 for the exact re-score as well. qstat = (||q'||^2, Java norm of q^).
+__global__ void query_mirror_kernel(const float* __restrict__ queries, int dim, int dpad, int metric, const float* __restrict__ colsum,
+                                    float inv_n, __nv_bfloat16* __restrict__ out, float* __restrict__ qf, float2* __restrict__ qstat) {
+    extern __shared__ float sq[];
+    __shared__ float s_nrm, s_red[32];
+    const int q = blockIdx.x;
+    for (int i = threadIdx.x; i < dim; i += blockDim.x) sq[i] = queries[(size_t)q * dim + i];
+    __syncthreads();
+    float qn = 0.0f;
+    if (metric == 1) {
+        if (threadIdx.x == 0) s_nrm = norm_java(sq, dim);
+        __syncthreads();
+        const float nrm = s_nrm;
+        __syncthreads();
+        for (int i = threadIdx.x; i < dim; i += blockDim.x) sq[i] = __fdiv_rn(sq[i], nrm);
+        __syncthreads();
+        if (threadIdx.x == 0) s_nrm = norm_java(sq, dim);
+        __syncthreads();
+        qn = s_nrm;
+        for (int i = threadIdx.x; i < dim; i += blockDim.x) qf[(size_t)q * dim + i] = sq[i];
+    }
+    float acc = 0.0f;
+    for (int c = threadIdx.x; c < dpad; c += blockDim.x) {
+        float v = 0.0f;
+        if (c < dim) v = metric == 0 ? sq[c] - colsum[c] * inv_n : sq[c];
+        acc = fmaf(v, v, acc);
+        out[(size_t)q * dpad + c] = __float2bfloat16_rn(v);
+    }
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+    if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.0f;
+        for (int w = 0; w < (int)(blockDim.x >> 5); w++) t += s_red[w];
+        qstat[q] = make_float2(t, qn);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// pass 1b: per-query threshold = the (s+1)-th smallest sample score (s-th index of the sorted list)
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void block_bitonic_sort_u32(uint32_t* keys, int n) {
+    for (int k = 2; k <= n; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            __syncthreads();
+            for (int i = threadIdx.x; i < (n >> 1); i += blockDim.x) {
+                const int lo = ((i & ~(j - 1)) << 1) | (i & (j - 1)), hi = lo | j;
+                const uint32_t a = keys[lo], b = keys[hi];
+                const bool up = ((lo & k) == 0);
+                if ((a > b) == up) { keys[lo] = b; keys[hi] = a; }
+            }
+        }
+    }
+    __syncthreads();
+}
+__global__ void threshold_select_kernel(const float* __restrict__ scores, int64_t ld, int S, int P, int s, float* __restrict__ tau,
+                                        uint32_t* __restrict__ cnt) {
+    extern __shared__ uint32_t skeys[];
+    const int q = blockIdx.x;
+    for (int i = threadIdx.x; i < P; i += blockDim.x) skeys[i] = i < S ? f2ord(scores[(size_t)q * ld + i]) : 0xffffffffu;
+    block_bitonic_sort_u32(skeys, P);
+    if (threadIdx.x == 0) {
+        tau[q] = s < S ? ord2f(skeys[s]) : __int_as_float(0x7f800000);
+        cnt[q] = 0u;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// pass 3: shortlist, exact re-score in the reference order, certification
+// ---------------------------------------------------------------------------------------------------------------
+struct ShortlistArgs {
+    const uint64_t* cand; const uint32_t* cnt; uint32_t cap; int capP;
+    const float* tau; const float2* qstat; const uint32_t* amax_bits;
+    const float* base; const float* norms; const int32_t* ids; int id_offset; int64_t n; int dim;
+    const float* queries;        // fp32 queries used by the exact distance (normalised copy for cosine)
+    int metric, order, k, k2, k2p;
+    float err_rel;               // bound on |acc - q'.x'| / (||q'|| ||x'||)
+    int32_t* out_ids; float* out_d; int* flag; unsigned long long* stats;   // stats[0] certified, [1] flagged
+};
+__global__ void __launch_bounds__(256)
+flat_shortlist_kernel(const ShortlistArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint64_t* ckey = reinterpret_cast<uint64_t*>(smem_raw);
+    uint64_t* rkey = ckey + a.capP;
+    float* sq = reinterpret_cast<float*>(rkey + a.k2p);
+    const int q = blockIdx.x;
+    const uint32_t cnt = a.cnt[q];
+    const int c = (int)min(cnt, a.cap);
+    for (int i = threadIdx.x; i < a.capP; i += blockDim.x) ckey[i] = i < c ? a.cand[(size_t)q * a.cap + i] : KEY_MAX;
+    for (int i = threadIdx.x; i < a.dim; i += blockDim.x) sq[i] = a.queries[(size_t)q * a.dim + i];
+    block_bitonic_sort<false>(ckey, nullptr, a.capP);
+    const int R = min(c, a.k2);
+    const float qn = a.qstat[q].y;
+    for (int j = threadIdx.x; j < a.k2p; j += blockDim.x) {
+        uint64_t key = KEY_MAX;
+        if (j < R) {
+            const uint32_t row = (uint32_t)ckey[j];
+            const float* x = a.base + (size_t)row * a.dim;
+            float d;
+            if (a.metric == 1) d = cosine_dist_from_dot(dot_seq(x, sq, a.dim), a.norms[row], qn);
+            else d = l2sq_order(sq, x, a.dim, a.order);
+            key = make_key(d, a.ids ? a.ids[row] : (int32_t)(a.id_offset + row));
+        }
+        rkey[j] = key;
+    }
+    block_bitonic_sort<false>(rkey, nullptr, a.k2p);
+    for (int j = threadIdx.x; j < a.k; j += blockDim.x) {
+        const uint64_t key = j < a.k2p ? rkey[j] : KEY_MAX;
+        if (key == KEY_MAX) { a.out_ids[(size_t)q * a.k + j] = -1; a.out_d[(size_t)q * a.k + j] = __int_as_float(0x7f800000); }
+        else { a.out_ids[(size_t)q * a.k + j] = key_id(key); a.out_d[(size_t)q * a.k + j] = key_dist(key); }
+    }
+    if (threadIdx.x == 0) {
+        bool ok;
+        if ((int64_t)cnt == a.n && c <= a.k2 && cnt <= a.cap) {
+            ok = true;                                       // every row was re-scored
+        } else if (cnt > a.cap || R < a.k) {
+            ok = false;                                      // list overflow, or too few survivors to fill k
+        } else {
+            // rows not re-scored have approximate score >= s_cut
+            const double s_cut = c > a.k2 ? (double)ord2f((uint32_t)(ckey[a.k2] >> 32)) : (double)a.tau[q];
+            const double dk = (double)key_dist(rkey[a.k - 1]);
+            const double amax = (double)__uint_as_float(*a.amax_bits), qn2 = (double)a.qstat[q].x;
+            const double gamma = (double)a.dim * 2.384185791015625e-07;          // dim * 2^-22: fp32 summation slack
+            const double ecs = (double)a.err_rel * sqrt(qn2 * amax);               // |acc - q'.x'| for any row
+            if (a.metric == 0) {
+                const double lb = s_cut + qn2 - 2.0 * ecs - (amax + qn2 + fabs(s_cut)) * gamma;
+                ok = lb > 0.0 && dk * (1.0 + gamma) < lb * (1.0 - gamma);
+            } else {
+                const double u = -s_cut + ecs;                                     // upper bound on dot(x, q^) of an outsider
+                const double lb = 1.0 - (u >= 0.0 ? u * (1.0 + 1e-5) : u * (1.0 - 1e-5)) - gamma - 1e-5;
+                ok = dk + gamma + 1e-5 < lb;
+            }
+        }
+        a.flag[q] = ok ? 0 : 1;
+        atomicAdd(a.stats + (ok ? 0 : 1), 1ull);
+    }
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qr) != cudaSuccess || qr != cudaDriverEntryPointSuccess)
+            return nullptr;
+        fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+// 2-D bf16 tensor [rows][dpad], row pitch `pitch_bytes`, box = 64 elements (128 bytes) x box_rows, 128-byte swizzle
+static int make_map(CUtensorMap* m, const void* ptr, uint64_t rows, int dpad, uint64_t pitch_bytes, int box_rows) {
+    EncodeTiledFn fn = encode_tiled_fn();
+    if (!fn) return 1;
+    cuuint64_t dims[2] = {(cuuint64_t)dpad, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)pitch_bytes};
+    cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? 0 : 2;
+}
+
+static int round_up_i(int64_t v, int m) { return (int)(((v + m - 1) / m) * m); }
+
+FlatGemmPlan flat_gemm_plan(int64_t n, int dim, int k) {
+    FlatGemmPlan p;
+    p.dpad = round_up_i(dim, BK);
+    p.n_pad = ((n + BN - 1) / BN) * BN;
+    p.k2 = std::min(2048, round_up_i(std::max(4 * k, k + 128), 128));
+    p.k2p = next_pow2(p.k2);
+    p.step = std::max<int64_t>(1, (n + 16383) / 16384);
+    p.S = (int)((n + p.step - 1) / p.step);
+    p.S_pad = round_up_i(p.S, BN);
+    p.P = next_pow2(p.S);
+    // expected survivors s*step; keep >= 3*k2 so the shortlist is full with overwhelming probability
+    p.s = (int)std::min<int64_t>(p.S, std::max<int64_t>(32, (3 * (int64_t)p.k2 + p.step - 1) / p.step));
+    const int64_t expect = (int64_t)p.s * p.step;
+    p.cap = (uint32_t)std::min<int64_t>(n, (int64_t)round_up_i(3 * expect + 1024, 1024));
+    p.capP = next_pow2((int)p.cap);
+    return p;
+}
+
+// The candidate list of one query must fit one CTA's shared memory (capP * 8 bytes) in pass 3; with a 16 384-row
+// sample that holds up to ~2.6 M rows per index (per GPU shard) at k <= 256. Larger shards use the order-exact scan.
+int flat_gemm_supported(int64_t n, int dim, int k) {
+    if (n < 4096 || n >= ((int64_t)1 << 31) || dim < 16 || dim > 8192 || k < 1 || k > 256) return 0;
+    const FlatGemmPlan p = flat_gemm_plan(n, dim, k);
+    return p.capP <= 16384 && p.k2 <= p.cap;
+}
+
+int launch_flat_mirror(const float* d_base, int64_t n, int dim, int metric, void* d_mirror, float2* d_ab, float* d_colsum, cudaStream_t st) {
+    const FlatGemmPlan p = flat_gemm_plan(n, dim, 1);
+    cudaMemsetAsync(d_colsum, 0, (size_t)(dim + 4) * 4, st);
+    if (metric == 0) {
+        const int64_t rpb = 512;
+        column_sum_kernel<<<(unsigned)((n + rpb - 1) / rpb), 256, 0, st>>>(d_base, n, dim, rpb, d_colsum);
+    }
+    base_mirror_kernel<<<148 * 8, 256, 0, st>>>(d_base, n, p.n_pad, dim, p.dpad, metric, d_colsum, 1.0f / (float)n,
+                                                reinterpret_cast<__nv_bfloat16*>(d_mirror), d_ab, reinterpret_cast<uint32_t*>(d_colsum + dim));
+    return cudaGetLastError() == cudaSuccess ? 0 : 1;
+}
+
+template <bool FILTER>
+static int run_gemm(const CUtensorMap& mq, const CUtensorMap& mb, const GemmArgs& g, cudaStream_t st) {
+    static bool attr_done[2] = {false, false};
+    if (!attr_done[FILTER]) {
+        if (cudaFuncSetAttribute(flat_gemm_kernel<FILTER>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM) != cudaSuccess) return 3;
+        attr_done[FILTER] = true;
+    }
+    const int total = g.m_tiles * g.n_tiles;
+    static int sms = 0;
+    if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); if (sms <= 0) sms = 148; }
+    const int grid = std::min(total, sms);
+    flat_gemm_kernel<FILTER><<<grid, GEMM_THREADS, GEMM_SMEM, st>>>(mq, mb, g);
+    return cudaGetLastError() == cudaSuccess ? 0 : 4;
+}
+
+int launch_flat_gemm_search(const FlatGemmArgs& a, cudaStream_t st) {
+    const FlatGemmPlan p = flat_gemm_plan(a.n, a.dim, a.k);
+    const float inv_n = 1.0f / (float)a.n;
+    __nv_bfloat16* qm = reinterpret_cast<__nv_bfloat16*>(a.d_qmirror);
+    query_mirror_kernel<<<a.nq, 128, (size_t)a.dim * 4, st>>>(a.d_queries, a.dim, p.dpad, a.metric, a.d_colsum, inv_n, qm, a.d_qf, a.d_qstat);
+    CUtensorMap mq, mb_sample, mb_all;
+    if (make_map(&mq, qm, (uint64_t)a.nq, p.dpad, (uint64_t)p.dpad * 2, BM)) return 10;
+    if (make_map(&mb_sample, a.d_mirror, (uint64_t)p.S, p.dpad, (uint64_t)p.dpad * 2 * (uint64_t)p.step, BN)) return 11;
+    if (make_map(&mb_all, a.d_mirror, (uint64_t)a.n, p.dpad, (uint64_t)p.dpad * 2, BN)) return 12;
+    GemmArgs g{};
+    g.m_tiles = (a.nq + BM - 1) / BM; g.k_blocks = p.dpad / BK; g.nq = a.nq; g.ab = a.d_ab;
+    // pass 1: sample scores -> tau
+    g.n_tiles = p.S_pad / BN; g.n_rows = p.S; g.row_step = p.step; g.scores = a.d_scores; g.ld_scores = p.S_pad;
+    int rc = run_gemm<false>(mq, mb_sample, g, st);
+    if (rc) return rc;
+    static size_t tsm_set = 0;
+    if ((size_t)p.P * 4 > tsm_set) {
+        if (cudaFuncSetAttribute(threshold_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.P * 4) != cudaSuccess) return 15;
+        tsm_set = (size_t)p.P * 4;
+    }
+    threshold_select_kernel<<<a.nq, 512, (size_t)p.P * 4, st>>>(a.d_scores, p.S_pad, p.S, p.P, p.s, a.d_tau, a.d_cnt);
+    // pass 2: all rows, filter epilogue
+    g.n_tiles = (int)(p.n_pad / BN); g.n_rows = a.n; g.row_step = 1; g.scores = nullptr;
+    g.tau = a.d_tau; g.cnt = a.d_cnt; g.cand = a.d_cand; g.cap = p.cap;
+    rc = run_gemm<true>(mq, mb_all, g, st);
+    if (rc) return rc;
+    // pass 3
+    ShortlistArgs s{};
+    s.cand = a.d_cand; s.cnt = a.d_cnt; s.cap = p.cap; s.capP = p.capP; s.tau = a.d_tau; s.qstat = a.d_qstat;
+    s.amax_bits = reinterpret_cast<const uint32_t*>(a.d_colsum + a.dim);
+    s.base = a.d_base; s.norms = a.d_norms; s.ids = a.d_ids; s.id_offset = a.id_offset; s.n = a.n; s.dim = a.dim;
+    s.queries = a.metric == 1 ? a.d_qf : a.d_queries;
+    s.metric = a.metric; s.order = a.order; s.k = a.k; s.k2 = p.k2; s.k2p = p.k2p;
+    s.err_rel = (float)((0.00390625 * (1.0 + 0.001953125) + (double)a.dim * 2.384185791015625e-07) * 1.02);
+    s.out_ids = a.d_out_ids; s.out_d = a.d_out_d; s.flag = a.d_flag; s.stats = a.d_stats;
+    const size_t smem = (size_t)p.capP * 8 + (size_t)p.k2p * 8 + (size_t)((a.dim + 3) & ~3) * 4;
+    static size_t smem_set = 0;
+    if (smem > smem_set) {
+        if (cudaFuncSetAttribute(flat_shortlist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 13;
+        smem_set = smem;
+    }
+    flat_shortlist_kernel<<<a.nq, 256, smem, st>>>(s);
+    return cudaGetLastError() == cudaSuccess ? 0 : 14;
+}

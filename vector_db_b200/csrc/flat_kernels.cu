@@ -11,8 +11,10 @@ template <int NT>
 __global__ void __launch_bounds__(NT)
 flat_exact_kernel(const float* __restrict__ base, const float* __restrict__ norms, const int32_t* __restrict__ ids, int id_offset,
                   int64_t n, int dim, const float* __restrict__ queries, int k, int cap, int metric, int order,
-                  int64_t rows_per_chunk, uint64_t* __restrict__ out_keys, uint32_t* __restrict__ out_rows) {
+                  int64_t rows_per_chunk, uint64_t* __restrict__ out_keys, uint32_t* __restrict__ out_rows,
+                  const int* __restrict__ only_flag) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    if (only_flag && !only_flag[blockIdx.y]) return;        // certified by the tensor-core path: nothing to do
     float* sq = reinterpret_cast<float*>(smem_raw);
     uint64_t* bkey = reinterpret_cast<uint64_t*>(sq + ((dim + 3) & ~3));
     uint32_t* brow = reinterpret_cast<uint32_t*>(bkey + cap);
@@ -68,7 +70,7 @@ flat_exact_kernel(const float* __restrict__ base, const float* __restrict__ norm
 
 void launch_flat_search_exact(const float* d_base, const float* d_norms, const int32_t* d_ids, int id_offset, int64_t n, int dim,
                               const float* d_q, int nq, int k, int metric, int order, int nchunks, uint64_t* d_keys_tmp,
-                              uint32_t* d_rows_tmp, uint64_t* d_keys, uint32_t* d_rows, cudaStream_t st) {
+                              uint32_t* d_rows_tmp, uint64_t* d_keys, uint32_t* d_rows, cudaStream_t st, const int* only_flag) {
     constexpr int NT = 128;
     const int cap = next_pow2(k + NT);
     const size_t smem = (size_t)((dim + 3) & ~3) * 4 + (size_t)cap * 12;
@@ -76,10 +78,10 @@ void launch_flat_search_exact(const float* d_base, const float* d_norms, const i
     const int64_t rpc = (n + nchunks - 1) / nchunks;
     dim3 grid(nchunks, nq);
     if (nchunks == 1) {
-        flat_exact_kernel<NT><<<grid, NT, smem, st>>>(d_base, d_norms, d_ids, id_offset, n, dim, d_q, k, cap, metric, order, rpc, d_keys, d_rows);
+        flat_exact_kernel<NT><<<grid, NT, smem, st>>>(d_base, d_norms, d_ids, id_offset, n, dim, d_q, k, cap, metric, order, rpc, d_keys, d_rows, only_flag);
     } else {
-        flat_exact_kernel<NT><<<grid, NT, smem, st>>>(d_base, d_norms, d_ids, id_offset, n, dim, d_q, k, cap, metric, order, rpc, d_keys_tmp, d_rows_tmp);
-        launch_merge_keys(d_keys_tmp, d_rows_tmp, nq, nchunks, k, d_keys, d_rows, st);
+        flat_exact_kernel<NT><<<grid, NT, smem, st>>>(d_base, d_norms, d_ids, id_offset, n, dim, d_q, k, cap, metric, order, rpc, d_keys_tmp, d_rows_tmp, only_flag);
+        launch_merge_keys(d_keys_tmp, d_rows_tmp, nq, nchunks, k, d_keys, d_rows, st, only_flag);
     }
 }
 

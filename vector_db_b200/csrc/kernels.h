@@ -16,8 +16,9 @@ int launch_adc_scan_fast(const uint8_t* d_codesT, const uint8_t* d_codes, int64_
                          const int32_t* d_ids, int id_offset, int R, int nchunks, uint64_t* d_keys_tmp, uint32_t* d_rows_tmp,
                          uint64_t* d_keys, uint32_t* d_rows, int* d_flag, cudaStream_t st);
 void launch_merge_keys(const uint64_t* d_in_keys, const uint32_t* d_in_rows, int nq, int nlists, int R, uint64_t* d_keys,
-                       uint32_t* d_rows, cudaStream_t st);
-void launch_keys_to_results(const uint64_t* d_keys, int R, int k, int64_t nq, int32_t* d_ids, float* d_dists, cudaStream_t st);
+                       uint32_t* d_rows, cudaStream_t st, const int* only_flag = nullptr);
+void launch_keys_to_results(const uint64_t* d_keys, int R, int k, int64_t nq, int32_t* d_ids, float* d_dists, cudaStream_t st,
+                            const int* only_flag = nullptr);
 void launch_adc_scan_plain(const uint8_t* d_codes, int64_t n, int M, const float* d_lut, float* d_out, cudaStream_t st);
 void launch_rerank(const float* d_base, const int32_t* d_ids, int id_offset, int dim, const float* d_q, int nq,
                    const uint32_t* d_rows, int R, int order, int k, int32_t* d_out_ids, float* d_out_d, cudaStream_t st);
@@ -61,6 +62,40 @@ void launch_make_traversal_rows(const float* d_base, int64_t n, int dim, int dpa
 // flat_kernels.cu
 void launch_flat_search_exact(const float* d_base, const float* d_norms, const int32_t* d_ids, int id_offset, int64_t n, int dim,
                               const float* d_q, int nq, int k, int metric, int order, int nchunks, uint64_t* d_keys_tmp,
-                              uint32_t* d_rows_tmp, uint64_t* d_keys, uint32_t* d_rows, cudaStream_t st);
+                              uint32_t* d_rows_tmp, uint64_t* d_keys, uint32_t* d_rows, cudaStream_t st, const int* only_flag = nullptr);
 void launch_merge_topk(const float* d_dists, const int32_t* d_ids, int g, int64_t nq, int k, float* d_out_d, int32_t* d_out_ids,
                        cudaStream_t st);
+
+// flat_gemm.cu — tensor-core flat search (tcgen05 + TMA), certified against the order-exact re-score
+struct FlatGemmPlan {
+    int dpad;            // dim padded to a multiple of 64 (one 128-byte swizzle row of bf16)
+    int64_t n_pad;       // rows padded to a multiple of 256 (length of the (a,b) array)
+    int64_t step;        // sample stride
+    int S, S_pad, P;     // sample rows, padded to 256, next power of two
+    int s;               // threshold rank inside the sample
+    int k2, k2p;         // rows re-scored exactly per query, next power of two
+    uint32_t cap;        // candidate-list capacity per query
+    int capP;
+};
+struct FlatGemmArgs {
+    const float* d_base; const float* d_norms; const int32_t* d_ids; int id_offset; int64_t n; int dim; int metric; int order;
+    const void* d_mirror;        // bf16 [n][dpad]
+    const float2* d_ab;          // [n_pad]
+    const float* d_colsum;       // [dim] column sums, [dim] = max ||row'||^2 bits
+    const float* d_queries; int nq; int k;
+    // scratch
+    void* d_qmirror;             // bf16 [nq][dpad]
+    float* d_qf;                 // [nq][dim] (cosine: normalised queries)
+    float2* d_qstat;             // [nq]
+    float* d_scores;             // [nq][S_pad]
+    float* d_tau;                // [nq]
+    uint32_t* d_cnt;             // [nq]
+    uint64_t* d_cand;            // [nq][cap]
+    int* d_flag;                 // [nq] 1 = not certified, answer with the exact scan
+    unsigned long long* d_stats; // [2] certified, flagged
+    int32_t* d_out_ids; float* d_out_d;
+};
+int flat_gemm_supported(int64_t n, int dim, int k);
+FlatGemmPlan flat_gemm_plan(int64_t n, int dim, int k);
+int launch_flat_mirror(const float* d_base, int64_t n, int dim, int metric, void* d_mirror, float2* d_ab, float* d_colsum, cudaStream_t st);
+int launch_flat_gemm_search(const FlatGemmArgs& a, cudaStream_t st);

@@ -86,11 +86,13 @@ adc_scan_topr_kernel(const uint8_t* __restrict__ codes, int64_t n, int M, const 
 
 // merge `nlists` sorted-or-not lists of R (key,row) per query into the R best; one CTA per query.
 __global__ void merge_keys_kernel(const uint64_t* __restrict__ in_keys, const uint32_t* __restrict__ in_rows, int nlists,
-                                  int R, int cap, uint64_t* __restrict__ out_keys, uint32_t* __restrict__ out_rows) {
+                                  int R, int cap, uint64_t* __restrict__ out_keys, uint32_t* __restrict__ out_rows,
+                                  const int* __restrict__ only_flag) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint64_t* bkey = reinterpret_cast<uint64_t*>(smem_raw);
     uint32_t* brow = reinterpret_cast<uint32_t*>(bkey + cap);
     const int q = blockIdx.x;
+    if (only_flag && !only_flag[q]) return;
     const int total = nlists * R;
     for (int i = threadIdx.x; i < cap; i += blockDim.x) {
         bkey[i] = i < total ? in_keys[(size_t)q * total + i] : KEY_MAX;
@@ -102,21 +104,22 @@ __global__ void merge_keys_kernel(const uint64_t* __restrict__ in_keys, const ui
 
 // keys -> (ids, dists), first k of each query's R
 __global__ void keys_to_results_kernel(const uint64_t* __restrict__ keys, int R, int k, int64_t nq, int32_t* __restrict__ out_ids,
-                                       float* __restrict__ out_d) {
+                                       float* __restrict__ out_d, const int* __restrict__ only_flag) {
     int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= nq * k) return;
     int64_t q = t / k; int j = (int)(t % k);
+    if (only_flag && !only_flag[q]) return;
     uint64_t key = j < R ? keys[q * R + j] : KEY_MAX;
     if (key == KEY_MAX) { out_ids[t] = -1; out_d[t] = __int_as_float(0x7f800000); }
     else { out_ids[t] = key_id(key); out_d[t] = key_dist(key); }
 }
 
 void launch_merge_keys(const uint64_t* d_in_keys, const uint32_t* d_in_rows, int nq, int nlists, int R, uint64_t* d_keys,
-                       uint32_t* d_rows, cudaStream_t st) {
+                       uint32_t* d_rows, cudaStream_t st, const int* only_flag) {
     const int mcap = next_pow2(nlists * R);
     const size_t msmem = (size_t)mcap * 12;
     cudaFuncSetAttribute(merge_keys_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem);
-    merge_keys_kernel<<<nq, 256, msmem, st>>>(d_in_keys, d_in_rows, nlists, R, mcap, d_keys, d_rows);
+    merge_keys_kernel<<<nq, 256, msmem, st>>>(d_in_keys, d_in_rows, nlists, R, mcap, d_keys, d_rows, only_flag);
 }
 void launch_adc_scan_topr(const uint8_t* d_codes, int64_t n, int M, const float* d_luts, int nq, const int32_t* d_ids,
                           int id_offset, int R, int nchunks, uint64_t* d_keys_tmp, uint32_t* d_rows_tmp, uint64_t* d_keys,
@@ -135,10 +138,11 @@ void launch_adc_scan_topr(const uint8_t* d_codes, int64_t n, int M, const float*
         launch_merge_keys(d_keys_tmp, d_rows_tmp, nq, nchunks, R, d_keys, d_rows, st);
     }
 }
-void launch_keys_to_results(const uint64_t* d_keys, int R, int k, int64_t nq, int32_t* d_ids, float* d_dists, cudaStream_t st) {
+void launch_keys_to_results(const uint64_t* d_keys, int R, int k, int64_t nq, int32_t* d_ids, float* d_dists, cudaStream_t st,
+                            const int* only_flag) {
     int64_t tot = nq * k;
     if (tot <= 0) return;
-    keys_to_results_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(d_keys, R, k, nq, d_ids, d_dists);
+    keys_to_results_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(d_keys, R, k, nq, d_ids, d_dists, only_flag);
 }
 
 // plain ADC distances for one LUT (test hook; order R3)

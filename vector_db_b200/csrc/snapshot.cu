@@ -75,7 +75,7 @@ extern "C" int vdb_load(vdb_index* x, const char* path) {
     x->h_ids.resize(n); x->h_vecs.resize((size_t)n * c.dim);
     bool ok = fh.r(x->h_ids.data(), (size_t)n * 4) && fh.r(x->h_vecs.data(), (size_t)n * c.dim * 4);
     if (x->cfg.metric == VDB_METRIC_COSINE) { x->h_norms.resize(n); ok = ok && fh.r(x->h_norms.data(), (size_t)n * 4); }
-    x->n = n; x->n_dev = 0; x->n_trav = 0; x->n_coded = 0; x->raw_rows = raw_rows;
+    x->n = n; x->n_dev = 0; x->n_trav = 0; x->n_fmirror = 0; x->n_coded = 0; x->raw_rows = raw_rows;
     if (ok && trained && x->pq_m > 0) {
         std::vector<float> cb((size_t)x->pq_m * VDB_NCENT * x->sd);
         int64_t nc = 0;

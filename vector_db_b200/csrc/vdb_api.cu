@@ -94,6 +94,8 @@ extern "C" int vdb_destroy(vdb_index* x) {
     x->d_base.release(); x->d_norms.release(); x->d_cb.release(); x->d_ids.release(); x->d_adj.release(); x->d_codes.release();
     x->d_q.release(); x->d_out_d.release(); x->d_lut.release(); x->d_out_ids.release(); x->d_keys.release(); x->d_keys_tmp.release();
     x->d_rows.release(); x->d_rows_tmp.release(); x->d_visited.release(); x->d_counters.release(); x->d_trav.release(); x->d_tnorm.release(); x->d_codesT.release(); x->d_lutg.release(); x->d_flag.release();
+    x->d_fmirror.release(); x->d_fab.release(); x->d_fcolsum.release(); x->d_fq.release(); x->d_fqf.release(); x->d_fscores.release(); x->d_ftau.release();
+    x->d_fqstat.release(); x->d_fcnt.release(); x->d_fcand.release();
     x->d_train.release(); x->d_sub.release(); x->d_mind.release(); x->d_asg.release();
     x->p_q.release(); x->p_d.release(); x->p_ids.release();
     if (x->ev_total0) { cudaEventDestroy(x->ev_total0); cudaEventDestroy(x->ev_total1); cudaEventDestroy(x->ev_k0); cudaEventDestroy(x->ev_k1); }
@@ -385,7 +387,7 @@ extern "C" int vdb_build(vdb_index* x) {
         x->h_vecs.swap(nv); x->h_ids.swap(ni); x->h_norms.swap(nn);
     }
     x->g.clear();
-    x->n_indexed = 0; x->n_dev = 0; x->n_trav = 0; x->n_coded = 0; x->raw_rows = 0; x->codes_overridden = false;
+    x->n_indexed = 0; x->n_dev = 0; x->n_trav = 0; x->n_fmirror = 0; x->n_coded = 0; x->raw_rows = 0; x->codes_overridden = false;
     return sync_index(x);
 }
 
@@ -517,22 +519,63 @@ static int search_pq(vdb_index* x, const float* d_q, int64_t nq, int k, int32_t*
     return VDB_OK;
 }
 
+// bf16 mirror for the tensor-core flat search; rebuilt whenever rows were added (the centring mean changes with them)
+static int build_flat_mirror(vdb_index* x, cudaStream_t st) {
+    if (x->n_fmirror == x->n) return VDB_OK;
+    const FlatGemmPlan p = flat_gemm_plan(x->n, x->cfg.dim, 1);
+    VDB_TRY(x->d_fmirror.ensure((size_t)x->n * p.dpad, 0, st));
+    VDB_TRY(x->d_fab.ensure((size_t)p.n_pad, 0, st));
+    VDB_TRY(x->d_fcolsum.ensure((size_t)x->cfg.dim + 4, 0, st));
+    if (launch_flat_mirror(x->d_base.p, x->n, x->cfg.dim, x->cfg.metric, x->d_fmirror.p, x->d_fab.p, x->d_fcolsum.p, st))
+        FAIL(VDB_ERR_CUDA, "flat mirror launch failed");
+    x->n_fmirror = x->n;
+    return VDB_OK;
+}
+
 static int search_flat(vdb_index* x, const float* d_q, int64_t nq, int k, int32_t* d_ids, float* d_dists, cudaStream_t st) {
     if (k > 2048) FAIL(VDB_ERR_INVALID, "k > 2048 not supported");
     const int32_t* ids = x->device_only ? nullptr : x->d_ids.p;
-    const int64_t QB = 16384;
+    const int order = x->cfg.arith == VDB_ARITH_NATIVE_AVX2 ? ORDER_R1 : ORDER_SEQ;
+    // tensor-core path (flat_gemm.cu): bf16 GEMM shortlist + exact re-score + certification; VDB_FLAT_EXACT_SCAN=1 forces
+    // the order-exact scan (tests compare the two)
+    const bool gemm = flat_gemm_supported(x->n, x->cfg.dim, k) && !getenv("VDB_FLAT_EXACT_SCAN");
+    if (gemm) VDB_TRY(build_flat_mirror(x, st));
+    const int64_t QB = gemm ? 4096 : 16384;
     for (int64_t q0 = 0; q0 < nq; q0 += QB) {
         const int64_t qb = std::min(QB, nq - q0);
         const int nch = pick_chunks(x, qb, x->n, k);
         VDB_TRY(x->d_keys.ensure((size_t)qb * k, 0, st));
         VDB_TRY(x->d_rows.ensure((size_t)qb * k, 0, st));
         if (nch > 1) { VDB_TRY(x->d_keys_tmp.ensure((size_t)qb * k * nch, 0, st)); VDB_TRY(x->d_rows_tmp.ensure((size_t)qb * k * nch, 0, st)); }
-        if (x->timed && q0 == 0) cudaEventRecord(x->ev_k0, st);
+        const int* only = nullptr;
+        if (gemm) {
+            const FlatGemmPlan p = flat_gemm_plan(x->n, x->cfg.dim, k);
+            VDB_TRY(x->d_fq.ensure((size_t)qb * p.dpad, 0, st));
+            if (x->cfg.metric == 1) VDB_TRY(x->d_fqf.ensure((size_t)qb * x->cfg.dim, 0, st));
+            VDB_TRY(x->d_fqstat.ensure((size_t)qb, 0, st));
+            VDB_TRY(x->d_fscores.ensure((size_t)qb * p.S_pad, 0, st));
+            VDB_TRY(x->d_ftau.ensure((size_t)qb, 0, st));
+            VDB_TRY(x->d_fcnt.ensure((size_t)qb, 0, st));
+            VDB_TRY(x->d_fcand.ensure((size_t)qb * p.cap, 0, st));
+            VDB_TRY(x->d_flag.ensure((size_t)qb, 0, st));
+            FlatGemmArgs a{};
+            a.d_base = x->d_base.p; a.d_norms = x->d_norms.p; a.d_ids = ids; a.id_offset = x->cfg.id_offset; a.n = x->n; a.dim = x->cfg.dim;
+            a.metric = x->cfg.metric; a.order = order; a.d_mirror = x->d_fmirror.p; a.d_ab = x->d_fab.p; a.d_colsum = x->d_fcolsum.p;
+            a.d_queries = d_q + q0 * x->cfg.dim; a.nq = (int)qb; a.k = k;
+            a.d_qmirror = x->d_fq.p; a.d_qf = x->d_fqf.p; a.d_qstat = x->d_fqstat.p; a.d_scores = x->d_fscores.p; a.d_tau = x->d_ftau.p;
+            a.d_cnt = x->d_fcnt.p; a.d_cand = x->d_fcand.p; a.d_flag = x->d_flag.p; a.d_stats = x->d_counters.p + 10;
+            a.d_out_ids = d_ids + q0 * k; a.d_out_d = d_dists + q0 * k;
+            if (x->timed && q0 == 0) cudaEventRecord(x->ev_k0, st);
+            const int rc = launch_flat_gemm_search(a, st);
+            if (rc) { char msg[64]; snprintf(msg, sizeof msg, "flat GEMM launch failed (%d)", rc); FAIL(VDB_ERR_CUDA, msg); }
+            if (x->timed && q0 == 0) cudaEventRecord(x->ev_k1, st);
+            only = x->d_flag.p;                      // uncertified queries fall through to the order-exact scan below
+        }
+        if (!gemm && x->timed && q0 == 0) cudaEventRecord(x->ev_k0, st);
         launch_flat_search_exact(x->d_base.p, x->d_norms.p, ids, x->cfg.id_offset, x->n, x->cfg.dim, d_q + q0 * x->cfg.dim, (int)qb, k,
-                                 x->cfg.metric, x->cfg.arith == VDB_ARITH_NATIVE_AVX2 ? ORDER_R1 : ORDER_SEQ, nch, x->d_keys_tmp.p,
-                                 x->d_rows_tmp.p, x->d_keys.p, x->d_rows.p, st);
-        if (x->timed && q0 == 0) cudaEventRecord(x->ev_k1, st);
-        launch_keys_to_results(x->d_keys.p, k, k, qb, d_ids + q0 * k, d_dists + q0 * k, st);
+                                 x->cfg.metric, order, nch, x->d_keys_tmp.p, x->d_rows_tmp.p, x->d_keys.p, x->d_rows.p, st, only);
+        if (!gemm && x->timed && q0 == 0) cudaEventRecord(x->ev_k1, st);
+        launch_keys_to_results(x->d_keys.p, k, k, qb, d_ids + q0 * k, d_dists + q0 * k, st, only);
         VDB_CUDA(cudaGetLastError());
     }
     return VDB_OK;
@@ -607,6 +650,7 @@ extern "C" int vdb_get_stats(vdb_index* x, vdb_stats* out) {
         fprintf(stderr, "[vdb hnsw profile] cycles: setup %llu select %llu gather %llu dist %llu sort %llu merge %llu final %llu | rounds %llu\n",
                 c[2], c[3], c[4], c[5], c[6], c[7], c[8], c[9]);
     x->stats.dist_evals = (int64_t)c[0]; x->stats.expansions = (int64_t)c[1];
+    x->stats.flat_certified = (int64_t)c[10]; x->stats.flat_fallback = (int64_t)c[11];
     *out = x->stats;
     return VDB_OK;
 }

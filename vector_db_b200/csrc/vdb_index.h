@@ -82,6 +82,10 @@ struct vdb_index {
     DevBuf<unsigned char> d_trav;   // traversal rows (bf16 or padded fp32), rebuilt when rows are uploaded
     int64_t n_trav = 0;
     DevBuf<float> d_tnorm;          // squared norms of the traversal rows
+    DevBuf<uint16_t> d_fmirror;     // flat index: bf16 mirror [n][dpad] for the tensor-core search (flat_gemm.cu)
+    DevBuf<float2> d_fab;           // per-row (a,b): approximate score = a + b * (q' . x')
+    DevBuf<float> d_fcolsum;        // [dim] column sums, [dim] max squared row norm
+    int64_t n_fmirror = 0;          // rows the mirror was built for (rebuilt whenever it differs from n)
     int64_t n_dev = 0;              // rows present in d_base / d_ids
     int64_t n_coded = 0;            // rows with valid codes in d_codes
 
@@ -105,6 +109,11 @@ struct vdb_index {
     DevBuf<uint64_t> d_keys, d_keys_tmp;
     DevBuf<uint32_t> d_rows, d_rows_tmp, d_visited;
     DevBuf<unsigned long long> d_counters;
+    DevBuf<uint16_t> d_fq;          // flat GEMM scratch: bf16 query mirror, normalised queries, scores, thresholds, candidates
+    DevBuf<float> d_fqf, d_fscores, d_ftau;
+    DevBuf<float2> d_fqstat;
+    DevBuf<uint32_t> d_fcnt;
+    DevBuf<uint64_t> d_fcand;
     PinnedBuf<float> p_q, p_d;
     PinnedBuf<int32_t> p_ids;
     // training scratch
