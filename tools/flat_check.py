@@ -14,13 +14,14 @@ def main():
     ap.add_argument("--nq", type=int, default=200)
     ap.add_argument("--k", type=int, default=100)
     ap.add_argument("--metric", type=int, default=0)
+    ap.add_argument("--arith", type=int, default=0)
     ap.add_argument("--big", type=int, default=0, help="also time N=big rows generated on the device (no oracle)")
     a = ap.parse_args()
     import torch
     from oracle import pyoracle as po
     import vector_db_b200 as v
     X, Q = po.synth(42, a.n, a.dim), po.synth(43, a.nq, a.dim)
-    f = v.NativeFlatIndex(a.dim, a.n, metric=a.metric)
+    f = v.NativeFlatIndex(a.dim, a.n, metric=a.metric, arith=a.arith)
     f.addBatch(np.arange(a.n, dtype=np.int32), X)
     t0 = time.time()
     ids, d = f.searchBatch(Q, a.k)
@@ -29,10 +30,10 @@ def main():
     if a.metric == 1:
         oi, od = po.flat_search(po.java_normalize(X), po.java_normalize(Q), a.k, metric=1, nthreads=16)
     else:
-        oi, od = po.flat_search(X, Q, a.k, metric=0, order=0, nthreads=16)
+        oi, od = po.flat_search(X, Q, a.k, metric=0, order=a.arith, nthreads=16)
     same_ids = float((ids == oi).mean())
     same_d = float((d.view(np.uint32) == od.view(np.uint32)).mean())
-    out = dict(n=a.n, dim=a.dim, nq=a.nq, k=a.k, metric=a.metric, ids_equal=same_ids, dist_bits_equal=same_d, certified=st["flat_certified"],
+    out = dict(arith=a.arith, n=a.n, dim=a.dim, nq=a.nq, k=a.k, metric=a.metric, ids_equal=same_ids, dist_bits_equal=same_d, certified=st["flat_certified"],
                fallback=st["flat_fallback"], kernel_ms=st["last_kernel_ms"], total_ms=st["last_total_ms"], wall_s=t1 - t0)
     if same_ids < 1.0:
         bad = np.argwhere(ids != oi)[:5]

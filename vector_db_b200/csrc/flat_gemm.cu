@@ -31,9 +31,9 @@ constexpr int STAGES = 4;
 constexpr int A_BYTES = BM * BK * 2;                 // 16 KB
 constexpr int B_BYTES = BN * BK * 2;                 // 32 KB
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES;       // 48 KB
-constexpr int GEMM_THREADS = 192;                    // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2..5 epilogue
+constexpr int GEMM_THREADS = 320;                    // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2..9 epilogue (two per SM sub-partition)
 constexpr int TMEM_COLS = 512;                       // two accumulator stages of BN columns
-constexpr int SMEM_AB = 2 * BN * 8;                  // per-stage (a,b) of the tile's base rows
+constexpr int SMEM_AB = 2 * BN * 4;                  // per accumulator stage: the additive term a[] of the tile's base rows
 constexpr int GEMM_SMEM = STAGES * STAGE_BYTES + SMEM_AB + 256 + 1024;   // + barriers + alignment slack
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -116,7 +116,8 @@ struct GemmArgs {
     int nq;                    // valid query rows
     int64_t n_rows;            // valid rows of the B operand (sample rows in pass 1)
     int64_t row_step;          // B row j is base row j*row_step
-    const float2* ab;          // per base row: score = a + b*acc
+    const float* arow;         // per base row: score = arow[row] + bconst * acc
+    float bconst;
     float* scores;             // STORE: [nq][ld_scores]
     int64_t ld_scores;
     const float* tau;          // FILTER: per-query threshold
@@ -132,7 +133,7 @@ flat_gemm_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
     const uint32_t raw = smem_u32(smem_raw);
     const uint32_t sbase = (raw + 1023u) & ~1023u;                    // swizzle-128B tiles need 1024-byte alignment
     unsigned char* sm = smem_raw + (sbase - raw);
-    float2* s_ab = reinterpret_cast<float2*>(sm + STAGES * STAGE_BYTES);
+    float* s_a = reinterpret_cast<float*>(sm + STAGES * STAGE_BYTES);
     uint64_t* bars = reinterpret_cast<uint64_t*>(sm + STAGES * STAGE_BYTES + SMEM_AB);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
     const uint32_t bar0 = smem_u32(bars);
@@ -143,7 +144,7 @@ flat_gemm_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES; s++) { mbar_init(BAR_FULL(s), 1); mbar_init(BAR_EMPTY(s), 1); }
-        for (int a = 0; a < 2; a++) { mbar_init(BAR_TFULL(a), 1); mbar_init(BAR_TEMPTY(a), 4); }
+        for (int a = 0; a < 2; a++) { mbar_init(BAR_TFULL(a), 1); mbar_init(BAR_TEMPTY(a), 8); }
         fence_barrier_init();
         tma_prefetch_desc(&map_q);
         tma_prefetch_desc(&map_b);
@@ -196,56 +197,85 @@ flat_gemm_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
             as ^= 1; if (as == 0) aphase ^= 1u;
         }
     } else {
-        // ===== epilogue: 4 warps, warp w reads TMEM lanes [32*(w&3), +32) = 32 queries =====
+        // ===== epilogue: 8 warps; warp w may read TMEM lanes [32*(w&3), +32) = 32 queries, and takes one half of the columns.
+        // Two warps per scheduler hide each other's latencies; the filter is branch-free in the common case (a running
+        // minimum over 32 scores, one compare), and the next tile's a[] / tau are prefetched while this one is processed.
         const int eq = warp & 3;
+        const int half = (warp - 2) >> 2;
         const int et = threadIdx.x - 64;
         int as = 0; uint32_t aphase = 0;
         const float INF = __int_as_float(0x7f800000);
+        const float bc = g.bconst;
+        float a_next = INF, tau_next = -INF;
+        if ((int)blockIdx.x < total) {
+            const int nt = blockIdx.x / g.m_tiles, mt = blockIdx.x - nt * g.m_tiles;
+            const int64_t j = (int64_t)nt * BN + et;
+            if (j < g.n_rows) a_next = __ldg(g.arow + j * g.row_step);
+            const int q = mt * BM + eq * 32 + lane;
+            if (FILTER && q < g.nq) tau_next = g.tau[q];
+        }
         for (int t = blockIdx.x; t < total; t += gridDim.x) {
             const int nt = t / g.m_tiles, mt = t - nt * g.m_tiles;
-            float2* ab = s_ab + as * BN;
-            for (int c = et; c < BN; c += 128) {
-                const int64_t j = (int64_t)nt * BN + c;
-                float2 v = make_float2(INF, 0.0f);
-                if (j < g.n_rows) v = __ldg(g.ab + j * g.row_step);
-                ab[c] = v;
+            float* sa = s_a + as * BN;
+            sa[et] = a_next;
+            const float tau = tau_next;
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            {
+                const int tn = t + gridDim.x;
+                a_next = INF; tau_next = -INF;
+                if (tn < total) {
+                    const int nt2 = tn / g.m_tiles, mt2 = tn - nt2 * g.m_tiles;
+                    const int64_t j = (int64_t)nt2 * BN + et;
+                    if (j < g.n_rows) a_next = __ldg(g.arow + j * g.row_step);
+                    const int q2 = mt2 * BM + eq * 32 + lane;
+                    if (FILTER && q2 < g.nq) tau_next = g.tau[q2];
+                }
             }
-            asm volatile("bar.sync 1, 128;" ::: "memory");
             const int q = mt * BM + eq * 32 + lane;
             const bool qok = q < g.nq;
-            float tau = -INF;
-            if (FILTER && qok) tau = g.tau[q];
             mbar_wait(BAR_TFULL(as), aphase);
             tc_fence_after();
-            const uint32_t trow = tmem_base + ((uint32_t)(eq * 32) << 16) + (uint32_t)(as * BN);
+            const uint32_t trow = tmem_base + ((uint32_t)(eq * 32) << 16) + (uint32_t)(as * BN + half * 128);
 #pragma unroll 1
-            for (int c0 = 0; c0 < BN; c0 += 64) {
+            for (int c0 = 0; c0 < 128; c0 += 64) {
                 uint32_t r[2][32];
                 tmem_ld32(trow + c0, r[0]);
                 tmem_ld32(trow + c0 + 32, r[1]);
                 tmem_ld_wait();
 #pragma unroll
                 for (int h = 0; h < 2; h++) {
+                    const int cb = half * 128 + c0 + h * 32;           // first column of this group inside the tile
+                    const float4* sa4 = reinterpret_cast<const float4*>(sa + cb);
                     if (FILTER) {
+                        float m0 = INF, m1 = INF, m2 = INF, m3 = INF;
 #pragma unroll
-                        for (int i = 0; i < 32; i++) {
-                            const float2 v = ab[c0 + h * 32 + i];
-                            const float s = fmaf(v.y, __uint_as_float(r[h][i]), v.x);
-                            if (s < tau) {
-                                const uint32_t pos = atomicAdd(g.cnt + q, 1u);
-                                if (pos < g.cap)
-                                    g.cand[(size_t)q * g.cap + pos] = ((uint64_t)f2ord(s) << 32) | (uint32_t)(nt * BN + c0 + h * 32 + i);
+                        for (int i = 0; i < 32; i += 4) {
+                            const float4 av = sa4[i >> 2];
+                            m0 = fminf(m0, fmaf(bc, __uint_as_float(r[h][i]), av.x));
+                            m1 = fminf(m1, fmaf(bc, __uint_as_float(r[h][i + 1]), av.y));
+                            m2 = fminf(m2, fmaf(bc, __uint_as_float(r[h][i + 2]), av.z));
+                            m3 = fminf(m3, fmaf(bc, __uint_as_float(r[h][i + 3]), av.w));
+                        }
+                        if (fminf(fminf(m0, m1), fminf(m2, m3)) < tau) {       // rare: some column of this group survives
+#pragma unroll
+                            for (int i = 0; i < 32; i++) {
+                                const float sc = fmaf(bc, __uint_as_float(r[h][i]), sa[cb + i]);
+                                if (sc < tau) {
+                                    const uint32_t pos = atomicAdd(g.cnt + q, 1u);
+                                    if (pos < g.cap) g.cand[(size_t)q * g.cap + pos] = ((uint64_t)f2ord(sc) << 32) | (uint32_t)(nt * BN + cb + i);
+                                }
                             }
                         }
                     } else if (qok) {
-                        float4* dst = reinterpret_cast<float4*>(g.scores + (size_t)q * g.ld_scores + (size_t)nt * BN + c0 + h * 32);
+                        float4* dst = reinterpret_cast<float4*>(g.scores + (size_t)q * g.ld_scores + (size_t)nt * BN + cb);
 #pragma unroll
                         for (int i = 0; i < 32; i += 4) {
+                            const float4 av = sa4[i >> 2];
                             float4 o;
-                            float2 v = ab[c0 + h * 32 + i];     o.x = fmaf(v.y, __uint_as_float(r[h][i]), v.x);
-                            v = ab[c0 + h * 32 + i + 1];        o.y = fmaf(v.y, __uint_as_float(r[h][i + 1]), v.x);
-                            v = ab[c0 + h * 32 + i + 2];        o.z = fmaf(v.y, __uint_as_float(r[h][i + 2]), v.x);
-                            v = ab[c0 + h * 32 + i + 3];        o.w = fmaf(v.y, __uint_as_float(r[h][i + 3]), v.x);
+                            o.x = fmaf(bc, __uint_as_float(r[h][i]), av.x);
+                            o.y = fmaf(bc, __uint_as_float(r[h][i + 1]), av.y);
+                            o.z = fmaf(bc, __uint_as_float(r[h][i + 2]), av.z);
+                            o.w = fmaf(bc, __uint_as_float(r[h][i + 3]), av.w);
                             dst[i >> 2] = o;
                         }
                     }
@@ -280,14 +310,14 @@ __global__ void column_sum_kernel(const float* __restrict__ base, int64_t n, int
 }
 
 // one warp per row: out[row][0..dpad) = bf16(x - mu) (sq-L2) or bf16(x) (cosine, rows already normalised);
-// ab[row] = (||x-mu||^2, -2) or (0, -1); rows in [n, n_pad) get (+inf, 0) so padded columns never pass the filter.
+// arow[row] = ||x-mu||^2 or 0 (score = arow + b*acc with b = -2 / -1); rows in [n, n_pad) get +inf so padded columns never pass.
 __global__ void base_mirror_kernel(const float* __restrict__ base, int64_t n, int64_t n_pad, int dim, int dpad, int metric,
                                    const float* __restrict__ colsum, float inv_n, __nv_bfloat16* __restrict__ out,
-                                   float2* __restrict__ ab, uint32_t* __restrict__ amax_bits) {
+                                   float* __restrict__ arow, uint32_t* __restrict__ amax_bits) {
     const int lane = threadIdx.x & 31;
     const int64_t w0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, wstep = ((int64_t)gridDim.x * blockDim.x) >> 5;
     for (int64_t row = w0; row < n_pad; row += wstep) {
-        if (row >= n) { if (lane == 0) ab[row] = make_float2(__int_as_float(0x7f800000), 0.0f); continue; }
+        if (row >= n) { if (lane == 0) arow[row] = __int_as_float(0x7f800000); continue; }
         const float* x = base + row * dim;
         float acc = 0.0f;
         for (int c = lane * 2; c < dpad; c += 64) {
@@ -300,7 +330,7 @@ __global__ void base_mirror_kernel(const float* __restrict__ base, int64_t n, in
 #pragma unroll
         for (int off = 16; off >= 1; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
         if (lane == 0) {
-            ab[row] = metric == 0 ? make_float2(acc, -2.0f) : make_float2(0.0f, -1.0f);
+            arow[row] = metric == 0 ? acc : 0.0f;
             atomicMax(amax_bits, __float_as_uint(acc));
         }
     }
@@ -363,16 +393,56 @@ __device__ __forceinline__ void block_bitonic_sort_u32(uint32_t* keys, int n) {
     }
     __syncthreads();
 }
-__global__ void threshold_select_kernel(const float* __restrict__ scores, int64_t ld, int S, int P, int s, float* __restrict__ tau,
-                                        uint32_t* __restrict__ cnt) {
+constexpr int RS_TILE = 32 * 33 + 32;      // per-warp transpose tile + row numbers (floats)
+constexpr int TS_NT = 512, TS_PER = 32, TS_LCAP = 2048;
+// Fast path (s < 511): the s+1 smallest per-thread minima are s+1 distinct sample scores, so the (s+1)-th smallest score
+// overall is <= their largest ("pivot"); only the few scores <= pivot are collected and sorted. Otherwise: full sort.
+__global__ void __launch_bounds__(TS_NT)
+threshold_select_kernel(const float* __restrict__ scores, int64_t ld, int S, int P, int s, float* __restrict__ tau,
+                        uint32_t* __restrict__ cnt) {
     extern __shared__ uint32_t skeys[];
+    __shared__ uint32_t s_mins[TS_NT];
+    __shared__ uint32_t s_n;
     const int q = blockIdx.x;
-    for (int i = threadIdx.x; i < P; i += blockDim.x) skeys[i] = i < S ? f2ord(scores[(size_t)q * ld + i]) : 0xffffffffu;
-    block_bitonic_sort_u32(skeys, P);
-    if (threadIdx.x == 0) {
-        tau[q] = s < S ? ord2f(skeys[s]) : __int_as_float(0x7f800000);
-        cnt[q] = 0u;
+    if (threadIdx.x == 0) { cnt[q] = 0u; s_n = 0u; }
+    if (s >= S) { if (threadIdx.x == 0) tau[q] = __int_as_float(0x7f800000); return; }
+    uint32_t key[TS_PER];
+    uint32_t mn = 0xffffffffu;
+#pragma unroll
+    for (int j = 0; j < TS_PER; j++) {
+        const int i = threadIdx.x + j * TS_NT;
+        key[j] = i < S ? f2ord(__ldg(scores + (size_t)q * ld + i)) : 0xffffffffu;
+        mn = min(mn, key[j]);
     }
+    if (s < TS_NT - 1) {
+        s_mins[threadIdx.x] = mn;
+        block_bitonic_sort_u32(s_mins, TS_NT);
+        const uint32_t pivot = s_mins[s];
+#pragma unroll
+        for (int j = 0; j < TS_PER; j++)
+            if (key[j] <= pivot) {
+                const uint32_t pos = atomicAdd(&s_n, 1u);
+                if (pos < TS_LCAP) skeys[pos] = key[j];
+            }
+        __syncthreads();
+        const int n = (int)s_n;
+        if (n <= TS_LCAP) {
+            int Pn = 2;
+            while (Pn < n) Pn <<= 1;
+            for (int i = n + threadIdx.x; i < Pn; i += TS_NT) skeys[i] = 0xffffffffu;
+            block_bitonic_sort_u32(skeys, Pn);
+            if (threadIdx.x == 0) tau[q] = ord2f(skeys[s]);
+            return;
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int j = 0; j < TS_PER; j++) {
+        const int i = threadIdx.x + j * TS_NT;
+        if (i < P) skeys[i] = key[j];
+    }
+    block_bitonic_sort_u32(skeys, P);
+    if (threadIdx.x == 0) tau[q] = ord2f(skeys[s]);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -384,34 +454,90 @@ struct ShortlistArgs {
     const float* base; const float* norms; const int32_t* ids; int id_offset; int64_t n; int dim;
     const float* queries;        // fp32 queries used by the exact distance (normalised copy for cosine)
     int metric, order, k, k2, k2p;
+    int tile_off;                // byte offset of the per-warp transpose tiles inside the candidate region
     float err_rel;               // bound on |acc - q'.x'| / (||q'|| ||x'||)
     int32_t* out_ids; float* out_d; int* flag; unsigned long long* stats;   // stats[0] certified, [1] flagged
 };
-__global__ void __launch_bounds__(256)
+
+// Exact distances of 32 rows by one warp, in the reference's summation order, with coalesced row reads: lane l loads
+// element (32c + l) of every row, the per-element terms go through a padded shared-memory tile, and lane l then sums row
+// l's 32 terms in index order. MODE 0: R6 sum += (q-x)^2 (HnswPqIndex.java:741-750). MODE 1: R1 eight fma lanes + pairwise
+// combine + scalar tail (DistanceAVX2.cpp:9-33). MODE 2: dot, sum += x*q (HnswIndex.java:126-133).
+template <int MODE>
+__device__ __forceinline__ float rescore32(const float* __restrict__ base, int dim, const float* __restrict__ sq, uint32_t myrow,
+                                           float* __restrict__ tile, int lane) {
+    volatile uint32_t* rows = reinterpret_cast<volatile uint32_t*>(tile + 32 * 33);     // the warp's 32 row numbers, read back as broadcasts
+    __syncwarp();
+    rows[lane] = myrow;
+    __syncwarp();
+    float acc = 0.0f, l[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) l[j] = 0.0f;
+    const int d8 = dim & ~7;
+    const int nchunk = (dim + 31) >> 5;
+    for (int c = 0; c < nchunk; c++) {
+        const int col = c * 32 + lane;
+        const bool cok = col < dim;
+        const float qv = cok ? sq[col] : 0.0f;
+        __syncwarp();
+#pragma unroll
+        for (int r0 = 0; r0 < 32; r0 += 16) {
+            float v[16];
+#pragma unroll
+            for (int r = 0; r < 16; r++) v[r] = cok ? __ldg(base + (size_t)rows[r0 + r] * dim + col) : 0.0f;
+#pragma unroll
+            for (int r = 0; r < 16; r++) tile[(r0 + r) * 33 + lane] = MODE == 2 ? __fmul_rn(v[r], qv) : __fsub_rn(qv, v[r]);
+        }
+        __syncwarp();
+        const int lim = min(32, (MODE == 1 ? d8 : dim) - c * 32);
+#pragma unroll
+        for (int i = 0; i < 32; i++) {
+            if (i < lim) {
+                const float x = tile[lane * 33 + i];
+                if (MODE == 0) acc = __fadd_rn(acc, __fmul_rn(x, x));
+                else if (MODE == 1) l[i & 7] = __fmaf_rn(x, x, l[i & 7]);
+                else acc = __fadd_rn(acc, x);
+            }
+        }
+    }
+    if (MODE == 1) {
+        const float s0 = __fadd_rn(l[0], l[4]), s1 = __fadd_rn(l[1], l[5]), s2 = __fadd_rn(l[2], l[6]), s3 = __fadd_rn(l[3], l[7]);
+        acc = __fadd_rn(__fadd_rn(s0, s1), __fadd_rn(s2, s3));
+        const int c0 = (nchunk - 1) * 32;                    // the tail [d8, dim) lies inside the last chunk, still in the tile
+        for (int gi = d8; gi < dim; gi++) { const float x = tile[lane * 33 + (gi - c0)]; acc = __fadd_rn(acc, __fmul_rn(x, x)); }
+    }
+    return acc;
+}
+
+__global__ void __launch_bounds__(256, 2)
 flat_shortlist_kernel(const ShortlistArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint64_t* ckey = reinterpret_cast<uint64_t*>(smem_raw);
-    uint64_t* rkey = ckey + a.capP;
+    float* tiles = reinterpret_cast<float*>(smem_raw + a.tile_off);
+    const size_t region = max((size_t)a.capP * 8, (size_t)a.tile_off + 8 * RS_TILE * 4);
+    uint64_t* rkey = reinterpret_cast<uint64_t*>(smem_raw + region);
     float* sq = reinterpret_cast<float*>(rkey + a.k2p);
-    const int q = blockIdx.x;
+    const int q = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t cnt = a.cnt[q];
     const int c = (int)min(cnt, a.cap);
-    for (int i = threadIdx.x; i < a.capP; i += blockDim.x) ckey[i] = i < c ? a.cand[(size_t)q * a.cap + i] : KEY_MAX;
+    int Pc = 2;
+    while (Pc < max(c, a.k2 + 1)) Pc <<= 1;
+    for (int i = threadIdx.x; i < Pc; i += blockDim.x) ckey[i] = i < c ? a.cand[(size_t)q * a.cap + i] : KEY_MAX;
     for (int i = threadIdx.x; i < a.dim; i += blockDim.x) sq[i] = a.queries[(size_t)q * a.dim + i];
-    block_bitonic_sort<false>(ckey, nullptr, a.capP);
+    block_bitonic_sort<false>(ckey, nullptr, Pc);
     const int R = min(c, a.k2);
     const float qn = a.qstat[q].y;
-    for (int j = threadIdx.x; j < a.k2p; j += blockDim.x) {
-        uint64_t key = KEY_MAX;
-        if (j < R) {
-            const uint32_t row = (uint32_t)ckey[j];
-            const float* x = a.base + (size_t)row * a.dim;
-            float d;
-            if (a.metric == 1) d = cosine_dist_from_dot(dot_seq(x, sq, a.dim), a.norms[row], qn);
-            else d = l2sq_order(sq, x, a.dim, a.order);
-            key = make_key(d, a.ids ? a.ids[row] : (int32_t)(a.id_offset + row));
-        }
-        rkey[j] = key;
+    const uint64_t cut_key = ckey[a.k2];                      // (k2+1)-th best approximate score: bound for the rows left out
+    float* tile = tiles + warp * RS_TILE;
+    for (int g = warp; g * 32 < a.k2p; g += 8) {
+        const int j = g * 32 + lane;
+        if (g * 32 >= R) { rkey[j] = KEY_MAX; continue; }
+        const uint32_t row = j < R ? (uint32_t)ckey[j] : (uint32_t)ckey[0];
+        float d;
+        if (a.metric == 1) d = cosine_dist_from_dot(rescore32<2>(a.base, a.dim, sq, row, tile, lane), a.norms[row], qn);
+        else if (a.order == ORDER_R1) d = rescore32<1>(a.base, a.dim, sq, row, tile, lane);
+        else d = rescore32<0>(a.base, a.dim, sq, row, tile, lane);
+        rkey[j] = j < R ? make_key(d, a.ids ? a.ids[row] : (int32_t)(a.id_offset + row)) : KEY_MAX;
     }
     block_bitonic_sort<false>(rkey, nullptr, a.k2p);
     for (int j = threadIdx.x; j < a.k; j += blockDim.x) {
@@ -427,7 +553,7 @@ flat_shortlist_kernel(const ShortlistArgs a) {
             ok = false;                                      // list overflow, or too few survivors to fill k
         } else {
             // rows not re-scored have approximate score >= s_cut
-            const double s_cut = c > a.k2 ? (double)ord2f((uint32_t)(ckey[a.k2] >> 32)) : (double)a.tau[q];
+            const double s_cut = c > a.k2 ? (double)ord2f((uint32_t)(cut_key >> 32)) : (double)a.tau[q];
             const double dk = (double)key_dist(rkey[a.k - 1]);
             const double amax = (double)__uint_as_float(*a.amax_bits), qn2 = (double)a.qstat[q].x;
             const double gamma = (double)a.dim * 2.384185791015625e-07;          // dim * 2^-22: fp32 summation slack
@@ -506,7 +632,7 @@ int flat_gemm_supported(int64_t n, int dim, int k) {
     return p.capP <= 16384 && p.k2 <= p.cap;
 }
 
-int launch_flat_mirror(const float* d_base, int64_t n, int dim, int metric, void* d_mirror, float2* d_ab, float* d_colsum, cudaStream_t st) {
+int launch_flat_mirror(const float* d_base, int64_t n, int dim, int metric, void* d_mirror, float* d_arow, float* d_colsum, cudaStream_t st) {
     const FlatGemmPlan p = flat_gemm_plan(n, dim, 1);
     cudaMemsetAsync(d_colsum, 0, (size_t)(dim + 4) * 4, st);
     if (metric == 0) {
@@ -514,7 +640,7 @@ int launch_flat_mirror(const float* d_base, int64_t n, int dim, int metric, void
         column_sum_kernel<<<(unsigned)((n + rpb - 1) / rpb), 256, 0, st>>>(d_base, n, dim, rpb, d_colsum);
     }
     base_mirror_kernel<<<148 * 8, 256, 0, st>>>(d_base, n, p.n_pad, dim, p.dpad, metric, d_colsum, 1.0f / (float)n,
-                                                reinterpret_cast<__nv_bfloat16*>(d_mirror), d_ab, reinterpret_cast<uint32_t*>(d_colsum + dim));
+                                                reinterpret_cast<__nv_bfloat16*>(d_mirror), d_arow, reinterpret_cast<uint32_t*>(d_colsum + dim));
     return cudaGetLastError() == cudaSuccess ? 0 : 1;
 }
 
@@ -543,17 +669,18 @@ int launch_flat_gemm_search(const FlatGemmArgs& a, cudaStream_t st) {
     if (make_map(&mb_sample, a.d_mirror, (uint64_t)p.S, p.dpad, (uint64_t)p.dpad * 2 * (uint64_t)p.step, BN)) return 11;
     if (make_map(&mb_all, a.d_mirror, (uint64_t)a.n, p.dpad, (uint64_t)p.dpad * 2, BN)) return 12;
     GemmArgs g{};
-    g.m_tiles = (a.nq + BM - 1) / BM; g.k_blocks = p.dpad / BK; g.nq = a.nq; g.ab = a.d_ab;
+    g.m_tiles = (a.nq + BM - 1) / BM; g.k_blocks = p.dpad / BK; g.nq = a.nq; g.arow = a.d_arow; g.bconst = a.metric == 0 ? -2.0f : -1.0f;
     // pass 1: sample scores -> tau
     g.n_tiles = p.S_pad / BN; g.n_rows = p.S; g.row_step = p.step; g.scores = a.d_scores; g.ld_scores = p.S_pad;
     int rc = run_gemm<false>(mq, mb_sample, g, st);
     if (rc) return rc;
     static size_t tsm_set = 0;
-    if ((size_t)p.P * 4 > tsm_set) {
-        if (cudaFuncSetAttribute(threshold_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p.P * 4) != cudaSuccess) return 15;
-        tsm_set = (size_t)p.P * 4;
+    const size_t tsm = (size_t)std::max(p.P, TS_LCAP) * 4;
+    if (tsm > tsm_set) {
+        if (cudaFuncSetAttribute(threshold_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm) != cudaSuccess) return 15;
+        tsm_set = tsm;
     }
-    threshold_select_kernel<<<a.nq, 512, (size_t)p.P * 4, st>>>(a.d_scores, p.S_pad, p.S, p.P, p.s, a.d_tau, a.d_cnt);
+    threshold_select_kernel<<<a.nq, TS_NT, tsm, st>>>(a.d_scores, p.S_pad, p.S, p.P, p.s, a.d_tau, a.d_cnt);
     // pass 2: all rows, filter epilogue
     g.n_tiles = (int)(p.n_pad / BN); g.n_rows = a.n; g.row_step = 1; g.scores = nullptr;
     g.tau = a.d_tau; g.cnt = a.d_cnt; g.cand = a.d_cand; g.cap = p.cap;
@@ -568,7 +695,9 @@ int launch_flat_gemm_search(const FlatGemmArgs& a, cudaStream_t st) {
     s.metric = a.metric; s.order = a.order; s.k = a.k; s.k2 = p.k2; s.k2p = p.k2p;
     s.err_rel = (float)((0.00390625 * (1.0 + 0.001953125) + (double)a.dim * 2.384185791015625e-07) * 1.02);
     s.out_ids = a.d_out_ids; s.out_d = a.d_out_d; s.flag = a.d_flag; s.stats = a.d_stats;
-    const size_t smem = (size_t)p.capP * 8 + (size_t)p.k2p * 8 + (size_t)((a.dim + 3) & ~3) * 4;
+    s.tile_off = (p.k2 + 2) * 8;
+    const size_t region = std::max((size_t)p.capP * 8, (size_t)s.tile_off + 8 * RS_TILE * 4);
+    const size_t smem = region + (size_t)p.k2p * 8 + (size_t)((a.dim + 3) & ~3) * 4;
     static size_t smem_set = 0;
     if (smem > smem_set) {
         if (cudaFuncSetAttribute(flat_shortlist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 13;

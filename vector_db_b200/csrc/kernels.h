@@ -80,7 +80,7 @@ struct FlatGemmPlan {
 struct FlatGemmArgs {
     const float* d_base; const float* d_norms; const int32_t* d_ids; int id_offset; int64_t n; int dim; int metric; int order;
     const void* d_mirror;        // bf16 [n][dpad]
-    const float2* d_ab;          // [n_pad]
+    const float* d_arow;         // [n_pad] additive term of the approximate score
     const float* d_colsum;       // [dim] column sums, [dim] = max ||row'||^2 bits
     const float* d_queries; int nq; int k;
     // scratch
@@ -97,5 +97,5 @@ struct FlatGemmArgs {
 };
 int flat_gemm_supported(int64_t n, int dim, int k);
 FlatGemmPlan flat_gemm_plan(int64_t n, int dim, int k);
-int launch_flat_mirror(const float* d_base, int64_t n, int dim, int metric, void* d_mirror, float2* d_ab, float* d_colsum, cudaStream_t st);
+int launch_flat_mirror(const float* d_base, int64_t n, int dim, int metric, void* d_mirror, float* d_arow, float* d_colsum, cudaStream_t st);
 int launch_flat_gemm_search(const FlatGemmArgs& a, cudaStream_t st);

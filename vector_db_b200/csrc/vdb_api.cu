@@ -560,7 +560,7 @@ static int search_flat(vdb_index* x, const float* d_q, int64_t nq, int k, int32_
             VDB_TRY(x->d_flag.ensure((size_t)qb, 0, st));
             FlatGemmArgs a{};
             a.d_base = x->d_base.p; a.d_norms = x->d_norms.p; a.d_ids = ids; a.id_offset = x->cfg.id_offset; a.n = x->n; a.dim = x->cfg.dim;
-            a.metric = x->cfg.metric; a.order = order; a.d_mirror = x->d_fmirror.p; a.d_ab = x->d_fab.p; a.d_colsum = x->d_fcolsum.p;
+            a.metric = x->cfg.metric; a.order = order; a.d_mirror = x->d_fmirror.p; a.d_arow = x->d_fab.p; a.d_colsum = x->d_fcolsum.p;
             a.d_queries = d_q + q0 * x->cfg.dim; a.nq = (int)qb; a.k = k;
             a.d_qmirror = x->d_fq.p; a.d_qf = x->d_fqf.p; a.d_qstat = x->d_fqstat.p; a.d_scores = x->d_fscores.p; a.d_tau = x->d_ftau.p;
             a.d_cnt = x->d_fcnt.p; a.d_cand = x->d_fcand.p; a.d_flag = x->d_flag.p; a.d_stats = x->d_counters.p + 10;

@@ -83,7 +83,7 @@ struct vdb_index {
     int64_t n_trav = 0;
     DevBuf<float> d_tnorm;          // squared norms of the traversal rows
     DevBuf<uint16_t> d_fmirror;     // flat index: bf16 mirror [n][dpad] for the tensor-core search (flat_gemm.cu)
-    DevBuf<float2> d_fab;           // per-row (a,b): approximate score = a + b * (q' . x')
+    DevBuf<float> d_fab;            // per-row additive term a: approximate score = a + b * (q' . x')
     DevBuf<float> d_fcolsum;        // [dim] column sums, [dim] max squared row norm
     int64_t n_fmirror = 0;          // rows the mirror was built for (rebuilt whenever it differs from n)
     int64_t n_dev = 0;              // rows present in d_base / d_ids
