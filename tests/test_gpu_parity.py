@@ -159,6 +159,53 @@ def test_flat_exact_search_bit_exact(v, po, metric, arith):
     f.close()
 
 
+@pytest.mark.parametrize("n,dim,nq,k,metric,arith", [(50000, 768, 200, 100, 0, 0), (50000, 768, 130, 100, 1, 0), (20000, 100, 24, 10, 0, 1),
+                                                     (9000, 100, 130, 7, 1, 0), (4096, 64, 5, 256, 0, 0), (33000, 40, 300, 1, 0, 1)])
+def test_flat_gemm_search_bit_exact(v, po, n, dim, nq, k, metric, arith):
+    """flat_gemm.cu: the tcgen05 bf16 GEMM + threshold filter + certified fp32 re-score must return exactly what the fp32
+    brute force returns (RecallOptimizationTest.java:151-164 order R6, DistanceAVX2.cpp:9-33 order R1, cosine
+    HnswIndex.java:126-133) — ids and distance bits — for ragged dims (100, 40: K padding, R1 scalar tail), partial query
+    tiles, k from 1 to 256, and every query must have been certified (no silent use of the exact-scan fallback)."""
+    X, Q = po.synth(42, n, dim), po.synth(43, nq, dim)
+    ids_ext = (np.arange(n, dtype=np.int32) * 7 + 3) % 1000003
+    f = v.NativeFlatIndex(dim, n, metric=metric, arith=arith)
+    f.addBatch(ids_ext, X)
+    ids, d = f.searchBatch(Q, k)
+    st = f.stats()
+    if metric == 1:
+        oi, od = po.flat_search(po.java_normalize(X), po.java_normalize(Q), k, metric=1, ids=ids_ext, nthreads=8)
+    else:
+        oi, od = po.flat_search(X, Q, k, metric=0, order=arith, ids=ids_ext, nthreads=8)
+    assert np.array_equal(ids, oi)
+    assert np.array_equal(bits(d), bits(od))
+    assert st["flat_certified"] == nq and st["flat_fallback"] == 0
+    f.close()
+
+
+def test_flat_gemm_certification_fallback_and_growth(v, po):
+    """Rows that tie exactly (duplicates) cannot be separated by the bf16 shortlist bound: those queries must fail
+    certification, be answered by the order-exact scan, and still match the oracle bit for bit with (dist,id) tie order.
+    Adding rows afterwards must rebuild the bf16 mirror (the centring mean changes)."""
+    n, dim, nq, k = 12000, 64, 16, 20
+    X = po.synth(42, n, dim)
+    X[1000:9000] = X[0]                      # 8001 identical rows: any query's top-k is inside one giant tie
+    Q = po.synth(43, nq, dim)
+    Q[:4] = X[0] + 0.001
+    f = v.NativeFlatIndex(dim, 2 * n)
+    f.addBatch(np.arange(n, dtype=np.int32), X)
+    ids, d = f.searchBatch(Q, k)
+    oi, od = po.flat_search(X, Q, k, nthreads=8)
+    assert np.array_equal(ids, oi) and np.array_equal(bits(d), bits(od))
+    st = f.stats()
+    assert st["flat_fallback"] >= 4 and st["flat_certified"] + st["flat_fallback"] == nq
+    X2 = po.synth(44, 5000, dim) + 3.0
+    f.addBatch(np.arange(n, n + 5000, dtype=np.int32), X2)
+    ids, d = f.searchBatch(Q[4:], k)
+    oi, od = po.flat_search(np.concatenate([X, X2]), Q[4:], k, nthreads=8)
+    assert np.array_equal(ids, oi) and np.array_equal(bits(d), bits(od))
+    f.close()
+
+
 def test_flat_ties_broken_by_id_and_padding(v, po):
     dim = 16
     base = np.zeros((6, dim), dtype=np.float32)

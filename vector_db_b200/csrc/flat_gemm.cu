@@ -34,7 +34,9 @@ constexpr int STAGE_BYTES = A_BYTES + B_BYTES;       // 48 KB
 constexpr int GEMM_THREADS = 320;                    // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2..9 epilogue (two per SM sub-partition)
 constexpr int TMEM_COLS = 512;                       // two accumulator stages of BN columns
 constexpr int SMEM_AB = 2 * BN * 4;                  // per accumulator stage: the additive term a[] of the tile's base rows
-constexpr int GEMM_SMEM = STAGES * STAGE_BYTES + SMEM_AB + 256 + 1024;   // + barriers + alignment slack
+constexpr int WBUF = 64;                             // per-epilogue-warp staging buffer for survivors (entries)
+constexpr int SMEM_WB = 8 * WBUF * 8 + 64;           // 8 warps x WBUF x (ordered score, lane<<8 | column) + counters
+constexpr int GEMM_SMEM = STAGES * STAGE_BYTES + SMEM_AB + SMEM_WB + 256 + 1024;   // + barriers + alignment slack
 
 // ---------------------------------------------------------------------------------------------------------------
 // PTX wrappers (sm_100a)
@@ -134,7 +136,9 @@ flat_gemm_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
     const uint32_t sbase = (raw + 1023u) & ~1023u;                    // swizzle-128B tiles need 1024-byte alignment
     unsigned char* sm = smem_raw + (sbase - raw);
     float* s_a = reinterpret_cast<float*>(sm + STAGES * STAGE_BYTES);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sm + STAGES * STAGE_BYTES + SMEM_AB);
+    uint2* s_wbuf = reinterpret_cast<uint2*>(sm + STAGES * STAGE_BYTES + SMEM_AB);
+    uint32_t* s_wcnt = reinterpret_cast<uint32_t*>(sm + STAGES * STAGE_BYTES + SMEM_AB + 8 * WBUF * 8);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sm + STAGES * STAGE_BYTES + SMEM_AB + SMEM_WB);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
     const uint32_t bar0 = smem_u32(bars);
 #define BAR_FULL(s) (bar0 + 8u * (uint32_t)(s))
@@ -206,6 +210,11 @@ flat_gemm_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
         int as = 0; uint32_t aphase = 0;
         const float INF = __int_as_float(0x7f800000);
         const float bc = g.bconst;
+        uint2* wbuf = s_wbuf + (warp - 2) * WBUF;
+        volatile uint32_t* wcntv = s_wcnt + (warp - 2);
+        uint32_t* wcnt = const_cast<uint32_t*>(wcntv);
+        if (lane == 0) *wcnt = 0u;
+        __syncwarp();
         float a_next = INF, tau_next = -INF;
         if ((int)blockIdx.x < total) {
             const int nt = blockIdx.x / g.m_tiles, mt = blockIdx.x - nt * g.m_tiles;
@@ -247,22 +256,31 @@ flat_gemm_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
                     const int cb = half * 128 + c0 + h * 32;           // first column of this group inside the tile
                     const float4* sa4 = reinterpret_cast<const float4*>(sa + cb);
                     if (FILTER) {
-                        float m0 = INF, m1 = INF, m2 = INF, m3 = INF;
+                        float sc[32], m[4] = {INF, INF, INF, INF};
 #pragma unroll
                         for (int i = 0; i < 32; i += 4) {
                             const float4 av = sa4[i >> 2];
-                            m0 = fminf(m0, fmaf(bc, __uint_as_float(r[h][i]), av.x));
-                            m1 = fminf(m1, fmaf(bc, __uint_as_float(r[h][i + 1]), av.y));
-                            m2 = fminf(m2, fmaf(bc, __uint_as_float(r[h][i + 2]), av.z));
-                            m3 = fminf(m3, fmaf(bc, __uint_as_float(r[h][i + 3]), av.w));
+                            sc[i] = fmaf(bc, __uint_as_float(r[h][i]), av.x);         m[0] = fminf(m[0], sc[i]);
+                            sc[i + 1] = fmaf(bc, __uint_as_float(r[h][i + 1]), av.y); m[1] = fminf(m[1], sc[i + 1]);
+                            sc[i + 2] = fmaf(bc, __uint_as_float(r[h][i + 2]), av.z); m[2] = fminf(m[2], sc[i + 2]);
+                            sc[i + 3] = fmaf(bc, __uint_as_float(r[h][i + 3]), av.w); m[3] = fminf(m[3], sc[i + 3]);
                         }
-                        if (fminf(fminf(m0, m1), fminf(m2, m3)) < tau) {       // rare: some column of this group survives
+                        if (fminf(fminf(m[0], m[1]), fminf(m[2], m[3])) < tau) {   // some column of this group survives (for some lane)
 #pragma unroll
-                            for (int i = 0; i < 32; i++) {
-                                const float sc = fmaf(bc, __uint_as_float(r[h][i]), sa[cb + i]);
-                                if (sc < tau) {
-                                    const uint32_t pos = atomicAdd(g.cnt + q, 1u);
-                                    if (pos < g.cap) g.cand[(size_t)q * g.cap + pos] = ((uint64_t)f2ord(sc) << 32) | (uint32_t)(nt * BN + cb + i);
+                            for (int g4 = 0; g4 < 4; g4++) {
+                                if (m[g4] < tau) {
+#pragma unroll
+                                    for (int i = g4; i < 32; i += 4) {
+                                        if (sc[i] < tau) {
+                                            // stage in the warp's shared buffer; flushed with all global atomics in flight at once
+                                            const uint32_t pos = atomicAdd(wcnt, 1u);
+                                            if (pos < WBUF) wbuf[pos] = make_uint2(f2ord(sc[i]), ((uint32_t)lane << 8) | (uint32_t)(cb + i));
+                                            else {
+                                                const uint32_t gp = atomicAdd(g.cnt + q, 1u);
+                                                if (gp < g.cap) g.cand[(size_t)q * g.cap + gp] = ((uint64_t)f2ord(sc[i]) << 32) | (uint32_t)(nt * BN + cb + i);
+                                            }
+                                        }
+                                    }
                                 }
                             }
                         }
@@ -283,7 +301,19 @@ flat_gemm_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(BAR_TEMPTY(as));
+            if (lane == 0) mbar_arrive(BAR_TEMPTY(as));      // TMEM stage drained: the MMA warp may overwrite it
+            if (FILTER) {
+                const uint32_t nb = min(*wcnt, (uint32_t)WBUF);
+                for (uint32_t e = lane; e < nb; e += 32) {
+                    const uint2 w = wbuf[e];
+                    const int qq = mt * BM + eq * 32 + (int)(w.y >> 8);
+                    const uint32_t gp = atomicAdd(g.cnt + qq, 1u);
+                    if (gp < g.cap) g.cand[(size_t)qq * g.cap + gp] = ((uint64_t)w.x << 32) | (uint32_t)(nt * BN + (int)(w.y & 255u));
+                }
+                __syncwarp();
+                if (lane == 0) *wcnt = 0u;
+                __syncwarp();
+            }
             as ^= 1; if (as == 0) aphase ^= 1u;
         }
     }
