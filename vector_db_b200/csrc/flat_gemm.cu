@@ -27,16 +27,22 @@ constexpr int BM = 128;            // queries per tile  (UMMA M, one TMEM lane p
 constexpr int BN = 256;            // base rows per tile (UMMA N, one TMEM column per row)
 constexpr int BK = 64;             // bf16 per k-block = 128 bytes = one swizzle-128B row
 constexpr int UK = 16;             // K of one tcgen05.mma kind::f16
-constexpr int STAGES = 4;
 constexpr int A_BYTES = BM * BK * 2;                 // 16 KB
-constexpr int B_BYTES = BN * BK * 2;                 // 32 KB
-constexpr int STAGE_BYTES = A_BYTES + B_BYTES;       // 48 KB
+// CG = 1: one CTA per tile (128 queries x 256 rows), B tile 32 KB, 4 stages.
+// CG = 2: a CTA pair per tile (256 queries x 256 rows, tcgen05 cta_group::2): each CTA stages its 128 queries and HALF of
+//         the base rows (16 KB), the pair's tensor cores read both halves -> 32 KB per k-block per SM instead of 48, 6 stages.
+template <int CG> struct Cfg {
+    static constexpr int B_BYTES = (BN / CG) * BK * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int STAGES = CG == 2 ? 6 : 4;
+    static constexpr int PIPE_BYTES = STAGES * STAGE_BYTES;
+};
 constexpr int GEMM_THREADS = 320;                    // warp 0 TMA, warp 1 MMA + TMEM alloc, warps 2..9 epilogue (two per SM sub-partition)
 constexpr int TMEM_COLS = 512;                       // two accumulator stages of BN columns
 constexpr int SMEM_AB = 2 * BN * 4;                  // per accumulator stage: the additive term a[] of the tile's base rows
 constexpr int WBUF = 64;                             // per-epilogue-warp staging buffer for survivors (entries)
 constexpr int SMEM_WB = 8 * WBUF * 8 + 64;           // 8 warps x WBUF x (ordered score, lane<<8 | column) + counters
-constexpr int GEMM_SMEM = STAGES * STAGE_BYTES + SMEM_AB + SMEM_WB + 256 + 1024;   // + barriers + alignment slack
+constexpr int GEMM_SMEM = 4 * (A_BYTES + BN * BK * 2) + SMEM_AB + SMEM_WB + 256 + 1024;   // 192 KB pipeline (both configs) + barriers + alignment slack
 
 // ---------------------------------------------------------------------------------------------------------------
 // PTX wrappers (sm_100a)
@@ -97,6 +103,40 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+// ---- cta_group::2 forms (a CTA pair = one 2-CTA cluster; the even CTA issues the MMAs for both) ----
+__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_sync() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t saddr, uint32_t rank) {
+    uint32_t r; asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank)); return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// TMA load whose completion bytes are credited to the barrier at the same offset in the pair's EVEN CTA (peer bit cleared)
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar & 0xFEFFFFFFu), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t smem_dst, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_dst), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t addr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void umma_bf16_pair(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// arrive (once these MMAs are done) on the barrier at this offset in BOTH CTAs of the pair
+__device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(bar), "h"((uint16_t)3) : "memory");
+}
+
 // Shared-memory matrix descriptor (cute/arch/mma_sm100_desc.hpp SmemDescriptor layout): K-major tile of 128-byte rows,
 // SWIZZLE_128B (layout type 2), 8-row groups 1024 bytes apart (SBO), LBO unused for swizzled K-major (1), version 1.
 __device__ __forceinline__ uint64_t make_kmajor_sw128_desc(uint32_t saddr) {
@@ -104,8 +144,23 @@ __device__ __forceinline__ uint64_t make_kmajor_sw128_desc(uint32_t saddr) {
            ((uint64_t)2 << 61);
 }
 // Instruction descriptor (InstrDescriptor): D=f32 (bit 4), A=B=bf16 (bits 7,10), both K-major, N>>3 at bit 17, M>>4 at bit 24.
-constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+template <int CG> struct IDesc {                      // CG = 2: M = 256 across the pair
+    static constexpr uint32_t value = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((BM * CG) >> 4) << 24);
+};
 
+
+// v[i] for a run-time i without dynamic register indexing: five levels of selects
+__device__ __forceinline__ float pick32(const float (&v)[32], int i) {
+    float a[16], b[8], c[4];
+#pragma unroll
+    for (int j = 0; j < 16; j++) a[j] = (i & 1) ? v[2 * j + 1] : v[2 * j];
+#pragma unroll
+    for (int j = 0; j < 8; j++) b[j] = (i & 2) ? a[2 * j + 1] : a[2 * j];
+#pragma unroll
+    for (int j = 0; j < 4; j++) c[j] = (i & 4) ? b[2 * j + 1] : b[2 * j];
+    const float d0 = (i & 8) ? c[1] : c[0], d1 = (i & 8) ? c[3] : c[2];
+    return (i & 16) ? d1 : d0;
+}
 
 // ---------------------------------------------------------------------------------------------------------------
 // The contraction. One persistent CTA per SM walks tiles t = blockIdx.x, +gridDim.x, ...; tile t covers base rows
@@ -126,19 +181,23 @@ struct GemmArgs {
     uint32_t* cnt;             // FILTER: per-query candidate count (may run past cap: overflow marker)
     uint64_t* cand;            // FILTER: [nq][cap] (ordered score << 32 | row)
     uint32_t cap;
+    int debug;                 // timing experiments only (VDB_FLAT_DBG): 1 = nothing survives, 2 = epilogue skips the TMEM read-out
 };
 
-template <bool FILTER>
+template <bool FILTER, int CG>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 flat_gemm_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_b, const GemmArgs g) {
+    constexpr int STAGES = Cfg<CG>::STAGES, STAGE_BYTES = Cfg<CG>::STAGE_BYTES;
+    const uint32_t rank = CG == 2 ? cluster_ctarank() : 0u;     // position inside the CTA pair
+    const int unit = CG == 2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x, nunits = (int)gridDim.x / CG;
     extern __shared__ unsigned char smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
     const uint32_t sbase = (raw + 1023u) & ~1023u;                    // swizzle-128B tiles need 1024-byte alignment
     unsigned char* sm = smem_raw + (sbase - raw);
-    float* s_a = reinterpret_cast<float*>(sm + STAGES * STAGE_BYTES);
-    uint2* s_wbuf = reinterpret_cast<uint2*>(sm + STAGES * STAGE_BYTES + SMEM_AB);
-    uint32_t* s_wcnt = reinterpret_cast<uint32_t*>(sm + STAGES * STAGE_BYTES + SMEM_AB + 8 * WBUF * 8);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sm + STAGES * STAGE_BYTES + SMEM_AB + SMEM_WB);
+    float* s_a = reinterpret_cast<float*>(sm + Cfg<CG>::PIPE_BYTES);
+    uint2* s_wbuf = reinterpret_cast<uint2*>(sm + Cfg<CG>::PIPE_BYTES + SMEM_AB);
+    uint32_t* s_wcnt = reinterpret_cast<uint32_t*>(sm + Cfg<CG>::PIPE_BYTES + SMEM_AB + 8 * WBUF * 8);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sm + Cfg<CG>::PIPE_BYTES + SMEM_AB + SMEM_WB);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
     const uint32_t bar0 = smem_u32(bars);
 #define BAR_FULL(s) (bar0 + 8u * (uint32_t)(s))
@@ -147,15 +206,15 @@ flat_gemm_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
 #define BAR_TEMPTY(a) (bar0 + 8u * (uint32_t)(2 * STAGES + 2 + (a)))
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
-        for (int s = 0; s < STAGES; s++) { mbar_init(BAR_FULL(s), 1); mbar_init(BAR_EMPTY(s), 1); }
-        for (int a = 0; a < 2; a++) { mbar_init(BAR_TFULL(a), 1); mbar_init(BAR_TEMPTY(a), 8); }
+        for (int s = 0; s < STAGES; s++) { mbar_init(BAR_FULL(s), CG); mbar_init(BAR_EMPTY(s), 1); }
+        for (int a = 0; a < 2; a++) { mbar_init(BAR_TFULL(a), 1); mbar_init(BAR_TEMPTY(a), 8 * CG); }
         fence_barrier_init();
         tma_prefetch_desc(&map_q);
         tma_prefetch_desc(&map_b);
     }
-    if (warp == 1) tmem_alloc(smem_u32(tmem_slot), TMEM_COLS);
+    if (warp == 1) { if (CG == 2) tmem_alloc_pair(smem_u32(tmem_slot), TMEM_COLS); else tmem_alloc(smem_u32(tmem_slot), TMEM_COLS); }
     tc_fence_before();
-    __syncthreads();
+    if (CG == 2) cluster_sync(); else __syncthreads();      // barriers initialised in both CTAs before anyone signals them
     tc_fence_after();
     const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
     const int total = g.m_tiles * g.n_tiles;
@@ -163,14 +222,22 @@ flat_gemm_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
     if (warp == 0) {
         // ===== TMA producer =====
         int stage = 0; uint32_t phase = 0;
-        for (int t = blockIdx.x; t < total; t += gridDim.x) {
+        for (int t = unit; t < total; t += nunits) {
             const int nt = t / g.m_tiles, mt = t - nt * g.m_tiles;
             if (lane == 0) {
                 for (int kb = 0; kb < g.k_blocks; kb++) {
                     mbar_wait(BAR_EMPTY(stage), phase ^ 1u);
-                    mbar_expect_tx(BAR_FULL(stage), STAGE_BYTES);
-                    tma_load_2d(sbase + stage * STAGE_BYTES, &map_q, BAR_FULL(stage), kb * BK, mt * BM);
-                    tma_load_2d(sbase + stage * STAGE_BYTES + A_BYTES, &map_b, BAR_FULL(stage), kb * BK, nt * BN);
+                    if (CG == 1) {
+                        mbar_expect_tx(BAR_FULL(stage), STAGE_BYTES);
+                        tma_load_2d(sbase + stage * STAGE_BYTES, &map_q, BAR_FULL(stage), kb * BK, mt * BM);
+                        tma_load_2d(sbase + stage * STAGE_BYTES + A_BYTES, &map_b, BAR_FULL(stage), kb * BK, nt * BN);
+                    } else {
+                        // the even CTA's barrier collects both CTAs' bytes: it expects 2 x STAGE_BYTES, the odd CTA just arrives
+                        if (rank == 0) mbar_expect_tx(BAR_FULL(stage), 2 * STAGE_BYTES);
+                        else mbar_arrive_cluster(map_to_cta(BAR_FULL(stage), 0));
+                        tma_load_2d_pair(sbase + stage * STAGE_BYTES, &map_q, BAR_FULL(stage), kb * BK, (mt * 2 + (int)rank) * BM);
+                        tma_load_2d_pair(sbase + stage * STAGE_BYTES + A_BYTES, &map_b, BAR_FULL(stage), kb * BK, nt * BN + (int)rank * (BN / 2));
+                    }
                     if (++stage == STAGES) { stage = 0; phase ^= 1u; }
                 }
             }
@@ -179,8 +246,8 @@ flat_gemm_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
     } else if (warp == 1) {
         // ===== MMA issuer (one thread) =====
         int stage = 0; uint32_t phase = 0; int as = 0; uint32_t aphase = 0;
-        for (int t = blockIdx.x; t < total; t += gridDim.x) {
-            if (lane == 0) {
+        for (int t = unit; t < total; t += nunits) {
+            if (lane == 0 && rank == 0) {
                 mbar_wait(BAR_TEMPTY(as), aphase ^ 1u);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + (uint32_t)(as * BN);
@@ -190,12 +257,15 @@ flat_gemm_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
                     const uint32_t a0 = sbase + stage * STAGE_BYTES;
                     const uint64_t ad = make_kmajor_sw128_desc(a0), bd = make_kmajor_sw128_desc(a0 + A_BYTES);
 #pragma unroll
-                    for (int k = 0; k < BK / UK; k++)           // +32 bytes along K inside the swizzle atom = +2 in the address field
-                        umma_bf16(d_tmem, ad + (uint64_t)(k * 2), bd + (uint64_t)(k * 2), IDESC, (uint32_t)((kb | k) != 0));
-                    umma_commit(BAR_EMPTY(stage));              // frees the stage once these MMAs have read it
+                    for (int k = 0; k < BK / UK; k++) {         // +32 bytes along K inside the swizzle atom = +2 in the address field
+                        if (CG == 2) umma_bf16_pair(d_tmem, ad + (uint64_t)(k * 2), bd + (uint64_t)(k * 2), IDesc<2>::value, (uint32_t)((kb | k) != 0));
+                        else umma_bf16(d_tmem, ad + (uint64_t)(k * 2), bd + (uint64_t)(k * 2), IDesc<1>::value, (uint32_t)((kb | k) != 0));
+                    }
+                    // frees the stage (in both CTAs of a pair) once these MMAs have read it
+                    if (CG == 2) umma_commit_pair(BAR_EMPTY(stage)); else umma_commit(BAR_EMPTY(stage));
                     if (++stage == STAGES) { stage = 0; phase ^= 1u; }
                 }
-                umma_commit(BAR_TFULL(as));                     // accumulator complete -> epilogue
+                if (CG == 2) umma_commit_pair(BAR_TFULL(as)); else umma_commit(BAR_TFULL(as));    // accumulator complete -> epilogue
             }
             __syncwarp();
             as ^= 1; if (as == 0) aphase ^= 1u;
@@ -216,37 +286,39 @@ flat_gemm_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
         if (lane == 0) *wcnt = 0u;
         __syncwarp();
         float a_next = INF, tau_next = -INF;
-        if ((int)blockIdx.x < total) {
-            const int nt = blockIdx.x / g.m_tiles, mt = blockIdx.x - nt * g.m_tiles;
+        const uint32_t tempty_remote0 = CG == 2 ? map_to_cta(BAR_TEMPTY(0), 0) : 0u, tempty_remote1 = CG == 2 ? map_to_cta(BAR_TEMPTY(1), 0) : 0u;
+        if (unit < total) {
+            const int nt = unit / g.m_tiles, mt = unit - nt * g.m_tiles;
             const int64_t j = (int64_t)nt * BN + et;
             if (j < g.n_rows) a_next = __ldg(g.arow + j * g.row_step);
-            const int q = mt * BM + eq * 32 + lane;
+            const int q = (mt * CG + (int)rank) * BM + eq * 32 + lane;
             if (FILTER && q < g.nq) tau_next = g.tau[q];
         }
-        for (int t = blockIdx.x; t < total; t += gridDim.x) {
+        for (int t = unit; t < total; t += nunits) {
             const int nt = t / g.m_tiles, mt = t - nt * g.m_tiles;
+            const int qbase = (mt * CG + (int)rank) * BM + eq * 32;     // first query of this warp's 32 TMEM lanes
             float* sa = s_a + as * BN;
             sa[et] = a_next;
-            const float tau = tau_next;
+            const float tau = (g.debug & 1) ? -INF : tau_next;
             asm volatile("bar.sync 1, 256;" ::: "memory");
             {
-                const int tn = t + gridDim.x;
+                const int tn = t + nunits;
                 a_next = INF; tau_next = -INF;
                 if (tn < total) {
                     const int nt2 = tn / g.m_tiles, mt2 = tn - nt2 * g.m_tiles;
                     const int64_t j = (int64_t)nt2 * BN + et;
                     if (j < g.n_rows) a_next = __ldg(g.arow + j * g.row_step);
-                    const int q2 = mt2 * BM + eq * 32 + lane;
+                    const int q2 = (mt2 * CG + (int)rank) * BM + eq * 32 + lane;
                     if (FILTER && q2 < g.nq) tau_next = g.tau[q2];
                 }
             }
-            const int q = mt * BM + eq * 32 + lane;
+            const int q = qbase + lane;
             const bool qok = q < g.nq;
             mbar_wait(BAR_TFULL(as), aphase);
             tc_fence_after();
             const uint32_t trow = tmem_base + ((uint32_t)(eq * 32) << 16) + (uint32_t)(as * BN + half * 128);
 #pragma unroll 1
-            for (int c0 = 0; c0 < 128; c0 += 64) {
+            for (int c0 = (g.debug & 2) ? 128 : 0; c0 < 128; c0 += 64) {
                 uint32_t r[2][32];
                 tmem_ld32(trow + c0, r[0]);
                 tmem_ld32(trow + c0 + 32, r[1]);
@@ -256,32 +328,29 @@ flat_gemm_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
                     const int cb = half * 128 + c0 + h * 32;           // first column of this group inside the tile
                     const float4* sa4 = reinterpret_cast<const float4*>(sa + cb);
                     if (FILTER) {
-                        float sc[32], m[4] = {INF, INF, INF, INF};
+                        // survivors are rare per thread but not per warp: keep the common path branch-free. Each score's
+                        // "below tau" sign bit is funnel-shifted into a per-thread mask (column i -> bit i); the rare set
+                        // bits are then extracted with a select tree (registers cannot be indexed dynamically).
+                        float sc[32];
+                        uint32_t mask = 0u;
 #pragma unroll
-                        for (int i = 0; i < 32; i += 4) {
-                            const float4 av = sa4[i >> 2];
-                            sc[i] = fmaf(bc, __uint_as_float(r[h][i]), av.x);         m[0] = fminf(m[0], sc[i]);
-                            sc[i + 1] = fmaf(bc, __uint_as_float(r[h][i + 1]), av.y); m[1] = fminf(m[1], sc[i + 1]);
-                            sc[i + 2] = fmaf(bc, __uint_as_float(r[h][i + 2]), av.z); m[2] = fminf(m[2], sc[i + 2]);
-                            sc[i + 3] = fmaf(bc, __uint_as_float(r[h][i + 3]), av.w); m[3] = fminf(m[3], sc[i + 3]);
+                        for (int i4 = 28; i4 >= 0; i4 -= 4) {
+                            const float4 av = sa4[i4 >> 2];
+                            sc[i4 + 3] = fmaf(bc, __uint_as_float(r[h][i4 + 3]), av.w); mask = __funnelshift_l(__float_as_uint(sc[i4 + 3] - tau), mask, 1);
+                            sc[i4 + 2] = fmaf(bc, __uint_as_float(r[h][i4 + 2]), av.z); mask = __funnelshift_l(__float_as_uint(sc[i4 + 2] - tau), mask, 1);
+                            sc[i4 + 1] = fmaf(bc, __uint_as_float(r[h][i4 + 1]), av.y); mask = __funnelshift_l(__float_as_uint(sc[i4 + 1] - tau), mask, 1);
+                            sc[i4] = fmaf(bc, __uint_as_float(r[h][i4]), av.x);         mask = __funnelshift_l(__float_as_uint(sc[i4] - tau), mask, 1);
                         }
-                        if (fminf(fminf(m[0], m[1]), fminf(m[2], m[3])) < tau) {   // some column of this group survives (for some lane)
-#pragma unroll
-                            for (int g4 = 0; g4 < 4; g4++) {
-                                if (m[g4] < tau) {
-#pragma unroll
-                                    for (int i = g4; i < 32; i += 4) {
-                                        if (sc[i] < tau) {
-                                            // stage in the warp's shared buffer; flushed with all global atomics in flight at once
-                                            const uint32_t pos = atomicAdd(wcnt, 1u);
-                                            if (pos < WBUF) wbuf[pos] = make_uint2(f2ord(sc[i]), ((uint32_t)lane << 8) | (uint32_t)(cb + i));
-                                            else {
-                                                const uint32_t gp = atomicAdd(g.cnt + q, 1u);
-                                                if (gp < g.cap) g.cand[(size_t)q * g.cap + gp] = ((uint64_t)f2ord(sc[i]) << 32) | (uint32_t)(nt * BN + cb + i);
-                                            }
-                                        }
-                                    }
-                                }
+                        while (mask) {
+                            const int i = 31 - __clz(mask);
+                            mask &= ~(1u << i);
+                            const float v = pick32(sc, i);
+                            // stage in the warp's shared buffer; flushed with all global atomics in flight at once
+                            const uint32_t pos = atomicAdd(wcnt, 1u);
+                            if (pos < WBUF) wbuf[pos] = make_uint2(f2ord(v), ((uint32_t)lane << 8) | (uint32_t)(cb + i));
+                            else {
+                                const uint32_t gp = atomicAdd(g.cnt + q, 1u);
+                                if (gp < g.cap) g.cand[(size_t)q * g.cap + gp] = ((uint64_t)f2ord(v) << 32) | (uint32_t)(nt * BN + cb + i);
                             }
                         }
                     } else if (qok) {
@@ -301,12 +370,14 @@ flat_gemm_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(BAR_TEMPTY(as));      // TMEM stage drained: the MMA warp may overwrite it
+            if (lane == 0) {                                 // TMEM stage drained: the MMA warp (of the pair's even CTA) may overwrite it
+                if (CG == 2) mbar_arrive_cluster(as ? tempty_remote1 : tempty_remote0); else mbar_arrive(BAR_TEMPTY(as));
+            }
             if (FILTER) {
                 const uint32_t nb = min(*wcnt, (uint32_t)WBUF);
                 for (uint32_t e = lane; e < nb; e += 32) {
                     const uint2 w = wbuf[e];
-                    const int qq = mt * BM + eq * 32 + (int)(w.y >> 8);
+                    const int qq = qbase + (int)(w.y >> 8);
                     const uint32_t gp = atomicAdd(g.cnt + qq, 1u);
                     if (gp < g.cap) g.cand[(size_t)qq * g.cap + gp] = ((uint64_t)w.x << 32) | (uint32_t)(nt * BN + (int)(w.y & 255u));
                 }
@@ -318,8 +389,8 @@ flat_gemm_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
         }
     }
     tc_fence_before();
-    __syncthreads();
-    if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
+    if (CG == 2) cluster_sync(); else __syncthreads();      // nobody leaves while the peer may still signal its barriers
+    if (warp == 1) { if (CG == 2) tmem_dealloc_pair(tmem_base, TMEM_COLS); else tmem_dealloc(tmem_base, TMEM_COLS); }
 #undef BAR_FULL
 #undef BAR_EMPTY
 #undef BAR_TFULL
@@ -674,19 +745,26 @@ int launch_flat_mirror(const float* d_base, int64_t n, int dim, int metric, void
     return cudaGetLastError() == cudaSuccess ? 0 : 1;
 }
 
-template <bool FILTER>
+template <bool FILTER, int CG>
 static int run_gemm(const CUtensorMap& mq, const CUtensorMap& mb, const GemmArgs& g, cudaStream_t st) {
-    static bool attr_done[2] = {false, false};
-    if (!attr_done[FILTER]) {
-        if (cudaFuncSetAttribute(flat_gemm_kernel<FILTER>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM) != cudaSuccess) return 3;
-        attr_done[FILTER] = true;
+    static bool attr_done = false;
+    if (!attr_done) {
+        if (cudaFuncSetAttribute(flat_gemm_kernel<FILTER, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM) != cudaSuccess) return 3;
+        attr_done = true;
     }
-    const int total = g.m_tiles * g.n_tiles;
     static int sms = 0;
     if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); if (sms <= 0) sms = 148; }
-    const int grid = std::min(total, sms);
-    flat_gemm_kernel<FILTER><<<grid, GEMM_THREADS, GEMM_SMEM, st>>>(mq, mb, g);
-    return cudaGetLastError() == cudaSuccess ? 0 : 4;
+    const int total = g.m_tiles * g.n_tiles;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(CG * std::min(total, sms / CG)));
+    cfg.blockDim = dim3(GEMM_THREADS);
+    cfg.dynamicSmemBytes = GEMM_SMEM;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CG; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, flat_gemm_kernel<FILTER, CG>, mq, mb, g) == cudaSuccess ? 0 : 4;
 }
 
 int launch_flat_gemm_search(const FlatGemmArgs& a, cudaStream_t st) {
@@ -694,15 +772,19 @@ int launch_flat_gemm_search(const FlatGemmArgs& a, cudaStream_t st) {
     const float inv_n = 1.0f / (float)a.n;
     __nv_bfloat16* qm = reinterpret_cast<__nv_bfloat16*>(a.d_qmirror);
     query_mirror_kernel<<<a.nq, 128, (size_t)a.dim * 4, st>>>(a.d_queries, a.dim, p.dpad, a.metric, a.d_colsum, inv_n, qm, a.d_qf, a.d_qstat);
+    // CTA pairs (cta_group::2) whenever there is more than one 128-query tile; VDB_FLAT_CG=1 forces single-CTA tiles
+    const char* cg_env = getenv("VDB_FLAT_CG");
+    const int CG = (a.nq > BM && !(cg_env && cg_env[0] == '1')) ? 2 : 1;
     CUtensorMap mq, mb_sample, mb_all;
     if (make_map(&mq, qm, (uint64_t)a.nq, p.dpad, (uint64_t)p.dpad * 2, BM)) return 10;
-    if (make_map(&mb_sample, a.d_mirror, (uint64_t)p.S, p.dpad, (uint64_t)p.dpad * 2 * (uint64_t)p.step, BN)) return 11;
-    if (make_map(&mb_all, a.d_mirror, (uint64_t)a.n, p.dpad, (uint64_t)p.dpad * 2, BN)) return 12;
+    if (make_map(&mb_sample, a.d_mirror, (uint64_t)p.S, p.dpad, (uint64_t)p.dpad * 2 * (uint64_t)p.step, BN / CG)) return 11;
+    if (make_map(&mb_all, a.d_mirror, (uint64_t)a.n, p.dpad, (uint64_t)p.dpad * 2, BN / CG)) return 12;
     GemmArgs g{};
-    g.m_tiles = (a.nq + BM - 1) / BM; g.k_blocks = p.dpad / BK; g.nq = a.nq; g.arow = a.d_arow; g.bconst = a.metric == 0 ? -2.0f : -1.0f;
+    { const char* dbg = getenv("VDB_FLAT_DBG"); g.debug = dbg ? atoi(dbg) : 0; }
+    g.m_tiles = (a.nq + BM * CG - 1) / (BM * CG); g.k_blocks = p.dpad / BK; g.nq = a.nq; g.arow = a.d_arow; g.bconst = a.metric == 0 ? -2.0f : -1.0f;
     // pass 1: sample scores -> tau
     g.n_tiles = p.S_pad / BN; g.n_rows = p.S; g.row_step = p.step; g.scores = a.d_scores; g.ld_scores = p.S_pad;
-    int rc = run_gemm<false>(mq, mb_sample, g, st);
+    int rc = CG == 2 ? run_gemm<false, 2>(mq, mb_sample, g, st) : run_gemm<false, 1>(mq, mb_sample, g, st);
     if (rc) return rc;
     static size_t tsm_set = 0;
     const size_t tsm = (size_t)std::max(p.P, TS_LCAP) * 4;
@@ -714,7 +796,7 @@ int launch_flat_gemm_search(const FlatGemmArgs& a, cudaStream_t st) {
     // pass 2: all rows, filter epilogue
     g.n_tiles = (int)(p.n_pad / BN); g.n_rows = a.n; g.row_step = 1; g.scores = nullptr;
     g.tau = a.d_tau; g.cnt = a.d_cnt; g.cand = a.d_cand; g.cap = p.cap;
-    rc = run_gemm<true>(mq, mb_all, g, st);
+    rc = CG == 2 ? run_gemm<true, 2>(mq, mb_all, g, st) : run_gemm<true, 1>(mq, mb_all, g, st);
     if (rc) return rc;
     // pass 3
     ShortlistArgs s{};
