@@ -555,7 +555,7 @@ struct ShortlistArgs {
     const float* base; const float* norms; const int32_t* ids; int id_offset; int64_t n; int dim;
     const float* queries;        // fp32 queries used by the exact distance (normalised copy for cosine)
     int metric, order, k, k2, k2p;
-    int tile_off;                // byte offset of the per-warp transpose tiles inside the candidate region
+    int tile_off;                // byte offset of sel[] (after the survivor arrays / transpose tiles, which share space)
     float err_rel;               // bound on |acc - q'.x'| / (||q'|| ||x'||)
     int32_t* out_ids; float* out_d; int* flag; unsigned long long* stats;   // stats[0] certified, [1] flagged
 };
@@ -613,27 +613,69 @@ __device__ __forceinline__ float rescore32(const float* __restrict__ base, int d
 __global__ void __launch_bounds__(256, 2)
 flat_shortlist_kernel(const ShortlistArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    uint64_t* ckey = reinterpret_cast<uint64_t*>(smem_raw);
-    float* tiles = reinterpret_cast<float*>(smem_raw + a.tile_off);
-    const size_t region = max((size_t)a.capP * 8, (size_t)a.tile_off + 8 * RS_TILE * 4);
-    uint64_t* rkey = reinterpret_cast<uint64_t*>(smem_raw + region);
+    // [hk | rw] survivor scores / rows (dead after the selection, then reused for the per-warp transpose tiles),
+    // sel[k2] selected rows, rkey[k2p] exact keys, sq[dim] the query
+    uint32_t* hk = reinterpret_cast<uint32_t*>(smem_raw);
+    uint32_t* rw = hk + a.cap;
+    float* tiles = reinterpret_cast<float*>(smem_raw);
+    uint32_t* sel = reinterpret_cast<uint32_t*>(smem_raw + a.tile_off);
+    uint64_t* rkey = reinterpret_cast<uint64_t*>(sel + a.k2);
     float* sq = reinterpret_cast<float*>(rkey + a.k2p);
+    __shared__ uint32_t s_cnt0[32], s_nsel, s_ntie;
     const int q = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t cnt = a.cnt[q];
     const int c = (int)min(cnt, a.cap);
-    int Pc = 2;
-    while (Pc < max(c, a.k2 + 1)) Pc <<= 1;
-    for (int i = threadIdx.x; i < Pc; i += blockDim.x) ckey[i] = i < c ? a.cand[(size_t)q * a.cap + i] : KEY_MAX;
+    for (int i = threadIdx.x; i < c; i += blockDim.x) {
+        const uint64_t key = a.cand[(size_t)q * a.cap + i];
+        hk[i] = (uint32_t)(key >> 32); rw[i] = (uint32_t)key;
+    }
     for (int i = threadIdx.x; i < a.dim; i += blockDim.x) sq[i] = a.queries[(size_t)q * a.dim + i];
-    block_bitonic_sort<false>(ckey, nullptr, Pc);
+    if (threadIdx.x < 32) s_cnt0[threadIdx.x] = 0u;
+    if (threadIdx.x == 0) { s_nsel = 0u; s_ntie = 0u; }
+    __syncthreads();
     const int R = min(c, a.k2);
+    // ---- the k2 best survivors by approximate score: radix bisection for the (k2+1)-th smallest ordered score T (its
+    //      value is also the bound s_cut for every row left out), then one compaction pass. No sort of the ~2 000 survivors.
+    uint32_t T = 0xffffffffu;
+    int need_ties = 0;
+    if (c > a.k2) {
+        uint32_t prefix = 0u;
+        int r = a.k2;                                           // 0-based rank looked for
+        for (int b = 31; b >= 0; b--) {
+            uint32_t local = 0u;
+            for (int i = threadIdx.x; i < c; i += blockDim.x) local += (((hk[i] ^ prefix) >> b) == 0u) ? 1u : 0u;
+            local = __reduce_add_sync(0xffffffffu, local);
+            if (lane == 0 && local) atomicAdd(&s_cnt0[b], local);
+            __syncthreads();
+            const int cnt0 = (int)s_cnt0[b];                    // elements matching the prefix with bit b clear
+            if (r >= cnt0) { prefix |= 1u << b; r -= cnt0; }
+        }
+        T = prefix;
+        need_ties = r;                                          // how many survivors equal to T still belong to the best k2
+        for (int i0 = 0; i0 < c; i0 += blockDim.x) {
+            const int i = i0 + threadIdx.x;
+            const uint32_t h = i < c ? hk[i] : 0xffffffffu;
+            const bool lt = i < c && h < T;
+            const uint32_t bal = __ballot_sync(0xffffffffu, lt);
+            uint32_t base = 0u;
+            if (lane == 0 && bal) base = atomicAdd(&s_nsel, (uint32_t)__popc(bal));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (lt) sel[base + __popc(bal & ((1u << lane) - 1u))] = rw[i];
+            else if (i < c && h == T) {
+                const uint32_t p = atomicAdd(&s_ntie, 1u);
+                if ((int)p < need_ties) sel[a.k2 - 1 - (int)p] = rw[i];
+            }
+        }
+    } else {
+        for (int i = threadIdx.x; i < c; i += blockDim.x) sel[i] = rw[i];
+    }
+    __syncthreads();                                            // hk / rw are dead from here on: the tiles reuse their space
     const float qn = a.qstat[q].y;
-    const uint64_t cut_key = ckey[a.k2];                      // (k2+1)-th best approximate score: bound for the rows left out
     float* tile = tiles + warp * RS_TILE;
     for (int g = warp; g * 32 < a.k2p; g += 8) {
         const int j = g * 32 + lane;
         if (g * 32 >= R) { rkey[j] = KEY_MAX; continue; }
-        const uint32_t row = j < R ? (uint32_t)ckey[j] : (uint32_t)ckey[0];
+        const uint32_t row = j < R ? sel[j] : sel[0];
         float d;
         if (a.metric == 1) d = cosine_dist_from_dot(rescore32<2>(a.base, a.dim, sq, row, tile, lane), a.norms[row], qn);
         else if (a.order == ORDER_R1) d = rescore32<1>(a.base, a.dim, sq, row, tile, lane);
@@ -654,7 +696,7 @@ flat_shortlist_kernel(const ShortlistArgs a) {
             ok = false;                                      // list overflow, or too few survivors to fill k
         } else {
             // rows not re-scored have approximate score >= s_cut
-            const double s_cut = c > a.k2 ? (double)ord2f((uint32_t)(cut_key >> 32)) : (double)a.tau[q];
+            const double s_cut = c > a.k2 ? (double)ord2f(T) : (double)a.tau[q];
             const double dk = (double)key_dist(rkey[a.k - 1]);
             const double amax = (double)__uint_as_float(*a.amax_bits), qn2 = (double)a.qstat[q].x;
             const double gamma = (double)a.dim * 2.384185791015625e-07;          // dim * 2^-22: fp32 summation slack
@@ -807,9 +849,9 @@ int launch_flat_gemm_search(const FlatGemmArgs& a, cudaStream_t st) {
     s.metric = a.metric; s.order = a.order; s.k = a.k; s.k2 = p.k2; s.k2p = p.k2p;
     s.err_rel = (float)((0.00390625 * (1.0 + 0.001953125) + (double)a.dim * 2.384185791015625e-07) * 1.02);
     s.out_ids = a.d_out_ids; s.out_d = a.d_out_d; s.flag = a.d_flag; s.stats = a.d_stats;
-    s.tile_off = (p.k2 + 2) * 8;
-    const size_t region = std::max((size_t)p.capP * 8, (size_t)s.tile_off + 8 * RS_TILE * 4);
-    const size_t smem = region + (size_t)p.k2p * 8 + (size_t)((a.dim + 3) & ~3) * 4;
+    const size_t region = std::max((size_t)p.cap * 8, (size_t)8 * RS_TILE * 4);
+    s.tile_off = (int)((region + 15) & ~(size_t)15);              // byte offset of sel[] (tiles alias the survivor arrays)
+    const size_t smem = (size_t)s.tile_off + (size_t)p.k2 * 4 + (size_t)p.k2p * 8 + (size_t)((a.dim + 3) & ~3) * 4 + 16;
     static size_t smem_set = 0;
     if (smem > smem_set) {
         if (cudaFuncSetAttribute(flat_shortlist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 13;
