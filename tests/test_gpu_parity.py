@@ -182,6 +182,28 @@ def test_flat_gemm_search_bit_exact(v, po, n, dim, nq, k, metric, arith):
     f.close()
 
 
+@pytest.mark.parametrize("metric", [0, 1])
+def test_flat_gemm_slabs_merge_bit_exact(v, po, monkeypatch, metric):
+    """Indexes beyond the per-CTA survivor-list window are searched slab by slab and merged by (dist,id); forced here with
+    small slabs (VDB_FLAT_SLAB_ROWS) so that 5 slabs with a ragged last one are exercised. Must equal the brute force."""
+    monkeypatch.setenv("VDB_FLAT_SLAB_ROWS", "8192")
+    n, dim, nq, k = 33000, 72, 150, 20
+    X, Q = po.synth(42, n, dim), po.synth(43, nq, dim)
+    ids_ext = (np.arange(n, dtype=np.int32) * 11 + 1) % 1000003
+    f = v.NativeFlatIndex(dim, n, metric=metric)
+    f.addBatch(ids_ext, X)
+    ids, d = f.searchBatch(Q, k)
+    st = f.stats()
+    if metric == 1:
+        oi, od = po.flat_search(po.java_normalize(X), po.java_normalize(Q), k, metric=1, ids=ids_ext, nthreads=8)
+    else:
+        oi, od = po.flat_search(X, Q, k, metric=0, ids=ids_ext, nthreads=8)
+    assert np.array_equal(ids, oi)
+    assert np.array_equal(bits(d), bits(od))
+    assert st["flat_certified"] + st["flat_fallback"] == nq and st["flat_fallback"] <= nq // 10
+    f.close()
+
+
 def test_flat_gemm_certification_fallback_and_growth(v, po):
     """Rows that tie exactly (duplicates) cannot be separated by the bf16 shortlist bound: those queries must fail
     certification, be answered by the order-exact scan, and still match the oracle bit for bit with (dist,id) tie order.

@@ -558,6 +558,7 @@ struct ShortlistArgs {
     int tile_off;                // byte offset of sel[] (after the survivor arrays / transpose tiles, which share space)
     float err_rel;               // bound on |acc - q'.x'| / (||q'|| ||x'||)
     int32_t* out_ids; float* out_d; int* flag; unsigned long long* stats;   // stats[0] certified, [1] flagged
+    int flag_or;                 // later slabs: OR into flag[] and leave the per-query statistics to the first slab
 };
 
 // Exact distances of 32 rows by one warp, in the reference's summation order, with coalesced row reads: lane l loads
@@ -710,8 +711,12 @@ flat_shortlist_kernel(const ShortlistArgs a) {
                 ok = dk + gamma + 1e-5 < lb;
             }
         }
-        a.flag[q] = ok ? 0 : 1;
-        atomicAdd(a.stats + (ok ? 0 : 1), 1ull);
+        if (a.flag_or) {
+            if (!ok && !a.flag[q]) { a.flag[q] = 1; atomicAdd(a.stats + 1, 1ull); atomicAdd(a.stats, ~0ull); }   // certified -> fallback
+        } else {
+            a.flag[q] = ok ? 0 : 1;
+            atomicAdd(a.stats + (ok ? 0 : 1), 1ull);
+        }
     }
 }
 
@@ -767,12 +772,25 @@ FlatGemmPlan flat_gemm_plan(int64_t n, int dim, int k) {
     return p;
 }
 
-// The candidate list of one query must fit one CTA's shared memory (capP * 8 bytes) in pass 3; with a 16 384-row
-// sample that holds up to ~2.6 M rows per index (per GPU shard) at k <= 256. Larger shards use the order-exact scan.
-int flat_gemm_supported(int64_t n, int dim, int k) {
-    if (n < 4096 || n >= ((int64_t)1 << 31) || dim < 16 || dim > 8192 || k < 1 || k > 256) return 0;
+// The survivor list of one query must fit one CTA's shared memory in pass 3; with a 16 384-row sample that holds up to
+// ~2.6 M rows at k <= 256. Larger indexes are searched slab by slab (each slab its own thresholds, shortlist and certificate)
+// and the per-slab top-k lists are merged by (dist,id).
+static bool plan_fits(int64_t n, int dim, int k) {
     const FlatGemmPlan p = flat_gemm_plan(n, dim, k);
-    return p.capP <= 16384 && p.k2 <= p.cap;
+    return p.capP <= 16384 && p.k2 <= (int)p.cap;
+}
+int flat_gemm_supported(int64_t n, int dim, int k) {
+    return n >= 4096 && n < ((int64_t)1 << 31) && dim >= 16 && dim <= 8192 && k >= 1 && k <= 256;
+}
+int64_t flat_gemm_slab_rows(int64_t n, int dim, int k) {
+    int64_t limit = 2000000;
+    if (const char* e = getenv("VDB_FLAT_SLAB_ROWS")) limit = std::max<int64_t>(4096, atoll(e));     // tests: force several slabs
+    if (n <= limit && plan_fits(n, dim, k)) return n;
+    int64_t slabs = (n + limit - 1) / limit;
+    for (;; slabs++) {
+        const int64_t rows = (((n + slabs - 1) / slabs) + 255) / 256 * 256;
+        if (rows <= 4096 || plan_fits(rows, dim, k)) return rows;
+    }
 }
 
 int launch_flat_mirror(const float* d_base, int64_t n, int dim, int metric, void* d_mirror, float* d_arow, float* d_colsum, cudaStream_t st) {
@@ -811,7 +829,7 @@ static int run_gemm(const CUtensorMap& mq, const CUtensorMap& mb, const GemmArgs
 
 int launch_flat_gemm_search(const FlatGemmArgs& a, cudaStream_t st) {
     const FlatGemmPlan p = flat_gemm_plan(a.n, a.dim, a.k);
-    const float inv_n = 1.0f / (float)a.n;
+    const float inv_n = 1.0f / (float)(a.n_total > 0 ? a.n_total : a.n);     // the centring mean is over the whole index
     __nv_bfloat16* qm = reinterpret_cast<__nv_bfloat16*>(a.d_qmirror);
     query_mirror_kernel<<<a.nq, 128, (size_t)a.dim * 4, st>>>(a.d_queries, a.dim, p.dpad, a.metric, a.d_colsum, inv_n, qm, a.d_qf, a.d_qstat);
     // CTA pairs (cta_group::2) whenever there is more than one 128-query tile; VDB_FLAT_CG=1 forces single-CTA tiles
@@ -848,7 +866,7 @@ int launch_flat_gemm_search(const FlatGemmArgs& a, cudaStream_t st) {
     s.queries = a.metric == 1 ? a.d_qf : a.d_queries;
     s.metric = a.metric; s.order = a.order; s.k = a.k; s.k2 = p.k2; s.k2p = p.k2p;
     s.err_rel = (float)((0.00390625 * (1.0 + 0.001953125) + (double)a.dim * 2.384185791015625e-07) * 1.02);
-    s.out_ids = a.d_out_ids; s.out_d = a.d_out_d; s.flag = a.d_flag; s.stats = a.d_stats;
+    s.out_ids = a.d_out_ids; s.out_d = a.d_out_d; s.flag = a.d_flag; s.stats = a.d_stats; s.flag_or = a.flag_or;
     const size_t region = std::max((size_t)p.cap * 8, (size_t)8 * RS_TILE * 4);
     s.tile_off = (int)((region + 15) & ~(size_t)15);              // byte offset of sel[] (tiles alias the survivor arrays)
     const size_t smem = (size_t)s.tile_off + (size_t)p.k2 * 4 + (size_t)p.k2p * 8 + (size_t)((a.dim + 3) & ~3) * 4 + 16;

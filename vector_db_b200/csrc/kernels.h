@@ -79,6 +79,8 @@ struct FlatGemmPlan {
 };
 struct FlatGemmArgs {
     const float* d_base; const float* d_norms; const int32_t* d_ids; int id_offset; int64_t n; int dim; int metric; int order;
+    int64_t n_total;             // rows of the whole index (n = rows of this slab; all row pointers are the slab's)
+    int flag_or;                 // 1 for slabs after the first: OR the certificate flags
     const void* d_mirror;        // bf16 [n][dpad]
     const float* d_arow;         // [n_pad] additive term of the approximate score
     const float* d_colsum;       // [dim] column sums, [dim] = max ||row'||^2 bits
@@ -96,6 +98,7 @@ struct FlatGemmArgs {
     int32_t* d_out_ids; float* d_out_d;
 };
 int flat_gemm_supported(int64_t n, int dim, int k);
+int64_t flat_gemm_slab_rows(int64_t n, int dim, int k);
 FlatGemmPlan flat_gemm_plan(int64_t n, int dim, int k);
 int launch_flat_mirror(const float* d_base, int64_t n, int dim, int metric, void* d_mirror, float* d_arow, float* d_colsum, cudaStream_t st);
 int launch_flat_gemm_search(const FlatGemmArgs& a, cudaStream_t st);

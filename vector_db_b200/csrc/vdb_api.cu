@@ -95,7 +95,7 @@ extern "C" int vdb_destroy(vdb_index* x) {
     x->d_q.release(); x->d_out_d.release(); x->d_lut.release(); x->d_out_ids.release(); x->d_keys.release(); x->d_keys_tmp.release();
     x->d_rows.release(); x->d_rows_tmp.release(); x->d_visited.release(); x->d_counters.release(); x->d_trav.release(); x->d_tnorm.release(); x->d_codesT.release(); x->d_lutg.release(); x->d_flag.release();
     x->d_fmirror.release(); x->d_fab.release(); x->d_fcolsum.release(); x->d_fq.release(); x->d_fqf.release(); x->d_fscores.release(); x->d_ftau.release();
-    x->d_fqstat.release(); x->d_fcnt.release(); x->d_fcand.release();
+    x->d_fqstat.release(); x->d_fcnt.release(); x->d_fcand.release(); x->d_fslab_d.release(); x->d_fslab_i.release();
     x->d_train.release(); x->d_sub.release(); x->d_mind.release(); x->d_asg.release();
     x->p_q.release(); x->p_d.release(); x->p_ids.release();
     if (x->ev_total0) { cudaEventDestroy(x->ev_total0); cudaEventDestroy(x->ev_total1); cudaEventDestroy(x->ev_k0); cudaEventDestroy(x->ev_k1); }
@@ -549,25 +549,40 @@ static int search_flat(vdb_index* x, const float* d_q, int64_t nq, int k, int32_
         if (nch > 1) { VDB_TRY(x->d_keys_tmp.ensure((size_t)qb * k * nch, 0, st)); VDB_TRY(x->d_rows_tmp.ensure((size_t)qb * k * nch, 0, st)); }
         const int* only = nullptr;
         if (gemm) {
-            const FlatGemmPlan p = flat_gemm_plan(x->n, x->cfg.dim, k);
+            const int dim = x->cfg.dim;
+            const int64_t slab = flat_gemm_slab_rows(x->n, dim, k);
+            const int nslabs = (int)((x->n + slab - 1) / slab);
+            if ((int64_t)nslabs * k > 8192) FAIL(VDB_ERR_INVALID, "flat search: too many slabs for this k");
+            const FlatGemmPlan p = flat_gemm_plan(std::min(slab, x->n), dim, k);
             VDB_TRY(x->d_fq.ensure((size_t)qb * p.dpad, 0, st));
-            if (x->cfg.metric == 1) VDB_TRY(x->d_fqf.ensure((size_t)qb * x->cfg.dim, 0, st));
+            if (x->cfg.metric == 1) VDB_TRY(x->d_fqf.ensure((size_t)qb * dim, 0, st));
             VDB_TRY(x->d_fqstat.ensure((size_t)qb, 0, st));
             VDB_TRY(x->d_fscores.ensure((size_t)qb * p.S_pad, 0, st));
             VDB_TRY(x->d_ftau.ensure((size_t)qb, 0, st));
             VDB_TRY(x->d_fcnt.ensure((size_t)qb, 0, st));
             VDB_TRY(x->d_fcand.ensure((size_t)qb * p.cap, 0, st));
             VDB_TRY(x->d_flag.ensure((size_t)qb, 0, st));
-            FlatGemmArgs a{};
-            a.d_base = x->d_base.p; a.d_norms = x->d_norms.p; a.d_ids = ids; a.id_offset = x->cfg.id_offset; a.n = x->n; a.dim = x->cfg.dim;
-            a.metric = x->cfg.metric; a.order = order; a.d_mirror = x->d_fmirror.p; a.d_arow = x->d_fab.p; a.d_colsum = x->d_fcolsum.p;
-            a.d_queries = d_q + q0 * x->cfg.dim; a.nq = (int)qb; a.k = k;
-            a.d_qmirror = x->d_fq.p; a.d_qf = x->d_fqf.p; a.d_qstat = x->d_fqstat.p; a.d_scores = x->d_fscores.p; a.d_tau = x->d_ftau.p;
-            a.d_cnt = x->d_fcnt.p; a.d_cand = x->d_fcand.p; a.d_flag = x->d_flag.p; a.d_stats = x->d_counters.p + 10;
-            a.d_out_ids = d_ids + q0 * k; a.d_out_d = d_dists + q0 * k;
+            if (nslabs > 1) {
+                VDB_TRY(x->d_fslab_d.ensure((size_t)nslabs * qb * k, 0, st));
+                VDB_TRY(x->d_fslab_i.ensure((size_t)nslabs * qb * k, 0, st));
+            }
             if (x->timed && q0 == 0) cudaEventRecord(x->ev_k0, st);
-            const int rc = launch_flat_gemm_search(a, st);
-            if (rc) { char msg[64]; snprintf(msg, sizeof msg, "flat GEMM launch failed (%d)", rc); FAIL(VDB_ERR_CUDA, msg); }
+            for (int sl = 0; sl < nslabs; sl++) {
+                const int64_t r0 = (int64_t)sl * slab, rows = std::min(slab, x->n - r0);
+                FlatGemmArgs a{};
+                a.d_base = x->d_base.p + (size_t)r0 * dim; a.d_norms = x->d_norms.p ? x->d_norms.p + r0 : nullptr; a.d_ids = ids ? ids + r0 : nullptr;
+                a.id_offset = x->cfg.id_offset + (int)r0; a.n = rows; a.n_total = x->n; a.flag_or = sl > 0; a.dim = dim;
+                a.metric = x->cfg.metric; a.order = order; a.d_mirror = x->d_fmirror.p + (size_t)r0 * p.dpad; a.d_arow = x->d_fab.p + r0;
+                a.d_colsum = x->d_fcolsum.p;
+                a.d_queries = d_q + q0 * dim; a.nq = (int)qb; a.k = k;
+                a.d_qmirror = x->d_fq.p; a.d_qf = x->d_fqf.p; a.d_qstat = x->d_fqstat.p; a.d_scores = x->d_fscores.p; a.d_tau = x->d_ftau.p;
+                a.d_cnt = x->d_fcnt.p; a.d_cand = x->d_fcand.p; a.d_flag = x->d_flag.p; a.d_stats = x->d_counters.p + 10;
+                a.d_out_ids = nslabs > 1 ? x->d_fslab_i.p + (size_t)sl * qb * k : d_ids + q0 * k;
+                a.d_out_d = nslabs > 1 ? x->d_fslab_d.p + (size_t)sl * qb * k : d_dists + q0 * k;
+                const int rc = launch_flat_gemm_search(a, st);
+                if (rc) { char msg[64]; snprintf(msg, sizeof msg, "flat GEMM launch failed (%d)", rc); FAIL(VDB_ERR_CUDA, msg); }
+            }
+            if (nslabs > 1) launch_merge_topk(x->d_fslab_d.p, x->d_fslab_i.p, nslabs, qb, k, d_dists + q0 * k, d_ids + q0 * k, st);
             if (x->timed && q0 == 0) cudaEventRecord(x->ev_k1, st);
             only = x->d_flag.p;                      // uncertified queries fall through to the order-exact scan below
         }

@@ -110,7 +110,8 @@ struct vdb_index {
     DevBuf<uint32_t> d_rows, d_rows_tmp, d_visited;
     DevBuf<unsigned long long> d_counters;
     DevBuf<uint16_t> d_fq;          // flat GEMM scratch: bf16 query mirror, normalised queries, scores, thresholds, candidates
-    DevBuf<float> d_fqf, d_fscores, d_ftau;
+    DevBuf<float> d_fqf, d_fscores, d_ftau, d_fslab_d;
+    DevBuf<int32_t> d_fslab_i;
     DevBuf<float2> d_fqstat;
     DevBuf<uint32_t> d_fcnt;
     DevBuf<uint64_t> d_fcand;
