@@ -434,6 +434,8 @@ __device__ __forceinline__ void mma_bf16_16816(float (&c)[4], uint32_t a0, uint3
                  : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 // sqh: the query rounded to bf16, zero padded, in shared memory ([tstride/2] elements). All threads of the CTA call.
+// FULL: the row is a whole number of 16-block stages (tstride % 256 == 0, e.g. 512-d bf16): no per-load bound checks
+template <bool FULL>
 __device__ __forceinline__ void fresh_distances_mma(const HnswSearchParams& p, const uint4* __restrict__ sqh, float qnorm, float qq,
                                                     const int* __restrict__ fnode, int nf, const FreshOut& o) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -452,16 +454,16 @@ __device__ __forceinline__ void fresh_distances_mma(const HnswSearchParams& p, c
         uint4 A0[4], A1[4], N0[4], N1[4];
         const uint4 z = make_uint4(0u, 0u, 0u, 0u);
 #pragma unroll
-        for (int i = 0; i < 4; i++) { const int cb = c + 4 * i; A0[i] = cb < nblk ? __ldg(r0 + cb) : z; A1[i] = cb < nblk ? __ldg(r1 + cb) : z; }
+        for (int i = 0; i < 4; i++) { const int cb = c + 4 * i; A0[i] = (FULL || cb < nblk) ? __ldg(r0 + cb) : z; A1[i] = (FULL || cb < nblk) ? __ldg(r1 + cb) : z; }
         for (int st = 0; st < nst; st++) {
             if (st + 1 < nst) {
 #pragma unroll
-                for (int i = 0; i < 4; i++) { const int cb = c + 4 * (4 * (st + 1) + i); N0[i] = cb < nblk ? __ldg(r0 + cb) : z; N1[i] = cb < nblk ? __ldg(r1 + cb) : z; }
+                for (int i = 0; i < 4; i++) { const int cb = c + 4 * (4 * (st + 1) + i); N0[i] = (FULL || cb < nblk) ? __ldg(r0 + cb) : z; N1[i] = (FULL || cb < nblk) ? __ldg(r1 + cb) : z; }
             }
 #pragma unroll
             for (int i = 0; i < 4; i++) {
                 const int cb = c + 4 * (4 * st + i);
-                const uint4 qv = cb < nblk ? sqh[cb] : z;
+                const uint4 qv = (FULL || cb < nblk) ? sqh[cb] : z;
                 mma_bf16_16816(acc0, A0[i].x, A1[i].x, A0[i].y, A1[i].y, qv.x, qv.y);
                 mma_bf16_16816(acc1, A0[i].z, A1[i].z, A0[i].w, A1[i].w, qv.z, qv.w);
             }
@@ -484,7 +486,7 @@ struct HnswShared {
     int candP[HN_MAXB], candF[HN_MAXB];   // indices of the first unexpanded entries of the main array / side buffer
     int sel[HN_MAXB];
     int wsum[HN_WARPS];
-    int nfresh, nacc;
+    int nfresh, nacc, takenP;
     int countP, countF;   // entries in the main array (<= ef) / side buffer
     int frontP, frontF;   // every entry below these indices carries the expanded bit
     int whichF;           // which of the two side-buffer halves is current
@@ -582,7 +584,8 @@ __device__ __forceinline__ void fold_side_buffer(uint64_t* P, const uint64_t* F0
     __syncthreads();
 }
 
-template <bool BF16>
+// FULL (bf16 rows only): rows are a whole number of 256-byte MMA stages, the distance loop needs no bound checks
+template <bool BF16, bool FULL>
 __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int qpad = (p.dim + 7) & ~7;
@@ -647,14 +650,14 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
         __syncthreads();
         {
             FreshOut o{fkey, &S.nacc, false, 0.0f};
-            if (BF16) fresh_distances_mma(p, sqh, qnorm, qq, fnode, 1, o);
+            if (BF16) fresh_distances_mma<FULL>(p, sqh, qnorm, qq, fnode, 1, o);
             else fresh_dispatch<false>(p, sq, qnorm, qq, fnode, 1, o);
         }
         __syncthreads();
         if (tid == 0) {
             P[0] = fkey[0];
             S.dentry = pool_dist(fkey[0]);
-            S.countP = 1; S.countF = 0; S.frontP = 0; S.frontF = 0; S.whichF = 0; S.evicted = 0; S.nfresh = 0; S.nacc = 0;
+            S.countP = 1; S.countF = 0; S.frontP = 0; S.frontF = 0; S.whichF = 0; S.evicted = 0; S.nfresh = 0; S.nacc = 0; S.takenP = 0;
             evals++;
         }
         __syncthreads();
@@ -697,15 +700,14 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
                 else { for (int t = 0; t < a; t++) r += ((P[S.candP[t]] & ~EXP_BIT) < key) ? 1 : 0; }
                 if (r < B) {
                     S.sel[r] = (int)(key & 0x7fffffffull);
-                    if (fromP) P[idx] |= EXP_BIT; else Fc_w[idx] |= EXP_BIT;
+                    if (fromP) { P[idx] |= EXP_BIT; atomicAdd(&S.takenP, 1); } else Fc_w[idx] |= EXP_BIT;
                 }
             }
             __syncthreads();
             // new fronts: the first candidate that was NOT taken, else where the scan stopped
             int newfrontP, newfrontF;
             {
-                int takenP = 0;
-                for (int t = 0; t < a; t++) takenP += (P[S.candP[t]] & EXP_BIT) ? 1 : 0;      // taken ones form a prefix
+                const int takenP = S.takenP;                        // taken ones form a prefix of each candidate list
                 const int takenF = nsel - takenP;
                 newfrontP = takenP < a ? S.candP[takenP] : (fndP > B ? S.candP[B - 1] + 1 : toP);
                 newfrontF = takenF < b ? S.candF[takenF] : (fndF > B ? S.candF[B - 1] + 1 : toF);
@@ -722,7 +724,7 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
                         const int it = it0 + t * HN_WARPS;
                         nb[t] = -1;
                         if (it < nitems) {
-                            const int s = it / nj, j = (it - s * nj) * 32 + lane;
+                            const int s = nj == 1 ? it : it / nj, j = (it - s * nj) * 32 + lane;
                             if (j < p.deg) nb[t] = __ldg(p.adj + (size_t)S.sel[s] * p.deg + j);
                         }
                     }
@@ -749,9 +751,10 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
             // of stalling each stage of the distance loop in turn
             {
                 const int lines = (p.tstride + 127) >> 7;
+                const int lsh = (lines & (lines - 1)) == 0 ? 31 - __clz(lines) : -1;      // power of two: shift instead of divide
                 const unsigned char* tb = reinterpret_cast<const unsigned char*>(p.tbase);
                 for (int t = tid; t < nf * lines; t += HN_NT) {
-                    const int r = t / lines, l = t - r * lines;
+                    const int r = lsh >= 0 ? (t >> lsh) : t / lines, l = t - r * lines;
                     asm volatile("prefetch.global.L2 [%0];" ::"l"(tb + (size_t)fnode[r] * p.tstride + ((size_t)l << 7)));
                 }
             }
@@ -764,7 +767,7 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
                 float bound = 0.0f;
                 if (full) bound = (variant == 0 || evicted) ? pool_dist(P[ef - 1]) : S.dentry;
                 FreshOut o{fkey, &S.nacc, full, bound};
-                if (BF16) fresh_distances_mma(p, sqh, qnorm, qq, fnode, nf, o);
+                if (BF16) fresh_distances_mma<FULL>(p, sqh, qnorm, qq, fnode, nf, o);
                 else fresh_dispatch<false>(p, sq, qnorm, qq, fnode, nf, o);
             }
             __syncthreads();
@@ -812,7 +815,7 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
                 if (nacc > 0) { S.countF = countF + nacc; S.whichF ^= 1; }
                 S.frontP = newfrontP;
                 S.frontF = min(newfrontF, r0);
-                S.nfresh = 0; S.nacc = 0;
+                S.nfresh = 0; S.nacc = 0; S.takenP = 0;
             }
             __syncthreads();
             HN_MARK(5);
@@ -869,12 +872,15 @@ int launch_hnsw_search(const HnswSearchParams& p, int grid, cudaStream_t st) {
     if (p.k + 22 > HN_FMAX || p.deg > 64 || p.batch < 1 || p.batch * p.deg > HN_FMAX || p.batch > HN_MAXB) return 1;
     if ((p.tstride & 15) != 0) return 1;
     const size_t smem = hnsw_search_smem_bytes(p);
-    if (p.tstore == 1) {
-        if (cudaFuncSetAttribute(hnsw_search_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 2;
-        hnsw_search_kernel<true><<<grid, HN_NT, smem, st>>>(p);
+    if (p.tstore == 1 && (p.tstride & 255) == 0) {
+        if (cudaFuncSetAttribute(hnsw_search_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 2;
+        hnsw_search_kernel<true, true><<<grid, HN_NT, smem, st>>>(p);
+    } else if (p.tstore == 1) {
+        if (cudaFuncSetAttribute(hnsw_search_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 2;
+        hnsw_search_kernel<true, false><<<grid, HN_NT, smem, st>>>(p);
     } else {
-        if (cudaFuncSetAttribute(hnsw_search_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 2;
-        hnsw_search_kernel<false><<<grid, HN_NT, smem, st>>>(p);
+        if (cudaFuncSetAttribute(hnsw_search_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 2;
+        hnsw_search_kernel<false, false><<<grid, HN_NT, smem, st>>>(p);
     }
     return 0;
 }
