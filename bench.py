@@ -434,6 +434,15 @@ def run_b200(args, rank, world):
         e2e_s = float(t.item())
     e2e = world * nq * args.steps / e2e_s
 
+    # ---- id-range-sharded C5 / C4 lines: every rank takes part (collectives inside), so this runs before rank 0 goes off to
+    #      the CPU baseline and the other ranks leave ----
+    sharded = None
+    if args.shard_rows > 0:
+        try:
+            sharded = sharded_aux(v, po, torch, dist, rank, world, local, args.shard_rows, args.flat_rows)
+        except Exception as e:
+            sharded = {"error": str(e)}
+
     if rank != 0:
         if world > 1:
             dist.barrier()
@@ -493,12 +502,6 @@ def run_b200(args, rank, world):
             flat = flat_gemm_aux(v, po, torch, args.flat_rows, pk)
         except Exception as e:
             flat = {"error": str(e)}
-    sharded = None
-    if args.shard_rows > 0:
-        try:                                    # every rank takes part (collectives inside)
-            sharded = sharded_aux(v, po, torch, dist, rank, world, local, args.shard_rows, args.flat_rows)
-        except Exception as e:
-            sharded = {"error": str(e)}
     gate = gate_c2 = None
     if world == 1 and not args.no_cpu_baseline:
         try:
