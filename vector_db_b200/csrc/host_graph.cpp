@@ -40,13 +40,14 @@ void HostGraph::init(int dim_, int M_, int max_elements, int metric_, uint64_t s
     // maxLevel = (int)(ln(maxElements)/ln(m)) + 1   (HnswPqIndex.java:89, HnswIndex.java:49)
     max_level = (int)(std::log((double)max_elements) / std::log((double)M)) + 1;
     if (max_level < 1) max_level = 1;
-    adj.assign(max_level, {}); deg.assign(max_level, {});
+    adj.assign(max_level, {}); deg.assign(max_level, {}); adjd.assign(max_level, {});
     clear();
 }
 void HostGraph::clear() {
     level.clear(); entry = -1; level_ctr = 0;
     for (auto& a : adj) a.clear();
     for (auto& d : deg) d.clear();
+    for (auto& d : adjd) d.clear();
 }
 // seeded stand-in for ThreadLocalRandom (HnswPqIndex.java:752-759): P(level >= l) = e^-l, capped at max_level-1
 int HostGraph::draw_level() {
@@ -65,6 +66,7 @@ void HostGraph::import_graph(const int32_t* levels, const int32_t* adj_in, int n
     for (int l = 0; l < max_level; l++) {
         adj[l].assign(adj_in + (size_t)l * n * M, adj_in + (size_t)(l + 1) * n * M);
         deg[l].resize(n);
+        adjd[l].assign((size_t)n * M, -1.0f);
         for (int i = 0; i < n; i++) {
             int c = 0;
             while (c < M && adj[l][(size_t)i * M + c] >= 0) c++;
@@ -82,7 +84,7 @@ void HostGraph::insert(int index, int ef, int variant) {
     };
     const int lv = draw_level();
     level.push_back(lv);
-    for (int l = 0; l < max_level; l++) { adj[l].resize((size_t)(index + 1) * M, -1); deg[l].push_back(0); }
+    for (int l = 0; l < max_level; l++) { adj[l].resize((size_t)(index + 1) * M, -1); adjd[l].resize((size_t)(index + 1) * M, -1.0f); deg[l].push_back(0); }
     if ((int)visit.size() <= index) visit.resize(std::max<size_t>(1024, (size_t)(index + 1) * 2), 0);
     if (entry < 0) { entry = index; return; }
 
@@ -117,6 +119,14 @@ void HostGraph::insert(int index, int ef, int variant) {
             if (variant == 2) { if (c.d > furthest) break; }
             else if (c.d > furthest && (int)results.size() >= ef) break;   // `continue` in Java; equivalent (min-heap)
             const int cn = deg[l][c.idx];
+            // pull the unvisited neighbours' rows towards the core before the distance loop walks them one by one
+            for (int j = 0; j < cn; j++) {
+                const int nb = adj[l][(size_t)c.idx * M + j];
+                if (visit[nb] != epoch) {
+                    const char* row = reinterpret_cast<const char*>(vecs + (size_t)nb * dim);
+                    __builtin_prefetch(row); __builtin_prefetch(row + 64); __builtin_prefetch(row + 128); __builtin_prefetch(row + 192);
+                }
+            }
             for (int j = 0; j < cn; j++) {
                 int nb = adj[l][(size_t)c.idx * M + j];
                 if (visit[nb] == epoch) continue;
@@ -133,17 +143,24 @@ void HostGraph::insert(int index, int ef, int variant) {
         // selectNeighbors: the M nearest (HnswPqIndex.java:1043-1064); `found` is already ascending
         sel.clear();
         for (int i = 0; i < (int)found.size() && i < M; i++) sel.push_back(found[i].idx);
-        for (int j = 0; j < (int)sel.size(); j++) adj[l][(size_t)index * M + j] = sel[j];
+        for (int j = 0; j < (int)sel.size(); j++) { adj[l][(size_t)index * M + j] = sel[j]; adjd[l][(size_t)index * M + j] = found[j].d; }
         deg[l][index] = (uint8_t)sel.size();
-        for (int nb : sel) {
+        for (int j = 0; j < (int)sel.size(); j++) {
+            const int nb = sel[j];
+            const float dnew = found[j].d;                      // dist(nb, index) == dist(index, nb) bit for bit
             int c = deg[l][nb];
-            if (c < M) { adj[l][(size_t)nb * M + c] = index; deg[l][nb] = (uint8_t)(c + 1); continue; }
+            if (c < M) { adj[l][(size_t)nb * M + c] = index; adjd[l][(size_t)nb * M + c] = dnew; deg[l][nb] = (uint8_t)(c + 1); continue; }
             // M+1 connections: keep the M nearest to nb, stable in list order (HnswPqIndex.java:512-523)
             tmp.clear();
-            for (int t = 0; t < c; t++) { int nn = adj[l][(size_t)nb * M + t]; tmp.push_back({dist(nb, nn), nn}); }
-            tmp.push_back({dist(nb, index), index});
+            for (int t = 0; t < c; t++) {
+                const int nn = adj[l][(size_t)nb * M + t];
+                float dd = adjd[l][(size_t)nb * M + t];
+                if (dd < 0.0f) dd = dist(nb, nn);               // imported graph: edge distance not cached yet
+                tmp.push_back({dd, nn});
+            }
+            tmp.push_back({dnew, index});
             std::stable_sort(tmp.begin(), tmp.end(), [](const Nb& a, const Nb& b) { return a.d < b.d; });
-            for (int t = 0; t < M; t++) adj[l][(size_t)nb * M + t] = tmp[t].idx;
+            for (int t = 0; t < M; t++) { adj[l][(size_t)nb * M + t] = tmp[t].idx; adjd[l][(size_t)nb * M + t] = tmp[t].d; }
         }
         cur = sel.empty() ? index : sel[0];
     }

@@ -14,6 +14,8 @@ struct HostGraph {
     std::vector<int32_t> level;      // [n]
     std::vector<std::vector<int32_t>> adj;   // [max_level] flat [n][M], -1 padded
     std::vector<std::vector<uint8_t>> deg;   // [max_level][n]
+    std::vector<std::vector<float>> adjd;    // [max_level] flat [n][M]: distance of each stored edge (< 0 = not known yet);
+                                             // distances are symmetric bit for bit, so back-link pruning re-uses them
     // scratch
     std::vector<uint32_t> visit; uint32_t epoch = 0;
 
