@@ -181,7 +181,6 @@ struct GemmArgs {
     uint32_t* cnt;             // FILTER: per-query candidate count (may run past cap: overflow marker)
     uint64_t* cand;            // FILTER: [nq][cap] (ordered score << 32 | row)
     uint32_t cap;
-    int debug;                 // timing experiments only (VDB_FLAT_DBG): 1 = nothing survives, 2 = epilogue skips the TMEM read-out
 };
 
 template <bool FILTER, int CG>
@@ -299,7 +298,7 @@ flat_gemm_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
             const int qbase = (mt * CG + (int)rank) * BM + eq * 32;     // first query of this warp's 32 TMEM lanes
             float* sa = s_a + as * BN;
             sa[et] = a_next;
-            const float tau = (g.debug & 1) ? -INF : tau_next;
+            const float tau = tau_next;
             asm volatile("bar.sync 1, 256;" ::: "memory");
             {
                 const int tn = t + nunits;
@@ -318,7 +317,7 @@ flat_gemm_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
             tc_fence_after();
             const uint32_t trow = tmem_base + ((uint32_t)(eq * 32) << 16) + (uint32_t)(as * BN + half * 128);
 #pragma unroll 1
-            for (int c0 = (g.debug & 2) ? 128 : 0; c0 < 128; c0 += 64) {
+            for (int c0 = 0; c0 < 128; c0 += 64) {
                 uint32_t r[2][32];
                 tmem_ld32(trow + c0, r[0]);
                 tmem_ld32(trow + c0 + 32, r[1]);
@@ -341,6 +340,7 @@ flat_gemm_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constan
                             sc[i4 + 1] = fmaf(bc, __uint_as_float(r[h][i4 + 1]), av.y); mask = __funnelshift_l(__float_as_uint(sc[i4 + 1] - tau), mask, 1);
                             sc[i4] = fmaf(bc, __uint_as_float(r[h][i4]), av.x);         mask = __funnelshift_l(__float_as_uint(sc[i4] - tau), mask, 1);
                         }
+                        if (!qok) mask = 0u;                    // padded query rows never append (NaN scores included)
                         while (mask) {
                             const int i = 31 - __clz(mask);
                             mask &= ~(1u << i);
@@ -807,13 +807,11 @@ int launch_flat_mirror(const float* d_base, int64_t n, int dim, int metric, void
 
 template <bool FILTER, int CG>
 static int run_gemm(const CUtensorMap& mq, const CUtensorMap& mb, const GemmArgs& g, cudaStream_t st) {
-    static bool attr_done = false;
-    if (!attr_done) {
-        if (cudaFuncSetAttribute(flat_gemm_kernel<FILTER, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM) != cudaSuccess) return 3;
-        attr_done = true;
-    }
-    static int sms = 0;
-    if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); if (sms <= 0) sms = 148; }
+    // per launch: the attribute is per device and one process may drive several
+    if (cudaFuncSetAttribute(flat_gemm_kernel<FILTER, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM) != cudaSuccess) return 3;
+    int sms = 0, dev = 0;
+    cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (sms <= 0) sms = 148;
     const int total = g.m_tiles * g.n_tiles;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(CG * std::min(total, sms / CG)));
@@ -840,18 +838,13 @@ int launch_flat_gemm_search(const FlatGemmArgs& a, cudaStream_t st) {
     if (make_map(&mb_sample, a.d_mirror, (uint64_t)p.S, p.dpad, (uint64_t)p.dpad * 2 * (uint64_t)p.step, BN / CG)) return 11;
     if (make_map(&mb_all, a.d_mirror, (uint64_t)a.n, p.dpad, (uint64_t)p.dpad * 2, BN / CG)) return 12;
     GemmArgs g{};
-    { const char* dbg = getenv("VDB_FLAT_DBG"); g.debug = dbg ? atoi(dbg) : 0; }
     g.m_tiles = (a.nq + BM * CG - 1) / (BM * CG); g.k_blocks = p.dpad / BK; g.nq = a.nq; g.arow = a.d_arow; g.bconst = a.metric == 0 ? -2.0f : -1.0f;
     // pass 1: sample scores -> tau
     g.n_tiles = p.S_pad / BN; g.n_rows = p.S; g.row_step = p.step; g.scores = a.d_scores; g.ld_scores = p.S_pad;
     int rc = CG == 2 ? run_gemm<false, 2>(mq, mb_sample, g, st) : run_gemm<false, 1>(mq, mb_sample, g, st);
     if (rc) return rc;
-    static size_t tsm_set = 0;
     const size_t tsm = (size_t)std::max(p.P, TS_LCAP) * 4;
-    if (tsm > tsm_set) {
-        if (cudaFuncSetAttribute(threshold_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm) != cudaSuccess) return 15;
-        tsm_set = tsm;
-    }
+    if (cudaFuncSetAttribute(threshold_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsm) != cudaSuccess) return 15;
     threshold_select_kernel<<<a.nq, TS_NT, tsm, st>>>(a.d_scores, p.S_pad, p.S, p.P, p.s, a.d_tau, a.d_cnt);
     // pass 2: all rows, filter epilogue
     g.n_tiles = (int)(p.n_pad / BN); g.n_rows = a.n; g.row_step = 1; g.scores = nullptr;
@@ -870,11 +863,7 @@ int launch_flat_gemm_search(const FlatGemmArgs& a, cudaStream_t st) {
     const size_t region = std::max((size_t)p.cap * 8, (size_t)8 * RS_TILE * 4);
     s.tile_off = (int)((region + 15) & ~(size_t)15);              // byte offset of sel[] (tiles alias the survivor arrays)
     const size_t smem = (size_t)s.tile_off + (size_t)p.k2 * 4 + (size_t)p.k2p * 8 + (size_t)((a.dim + 3) & ~3) * 4 + 16;
-    static size_t smem_set = 0;
-    if (smem > smem_set) {
-        if (cudaFuncSetAttribute(flat_shortlist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 13;
-        smem_set = smem;
-    }
+    if (cudaFuncSetAttribute(flat_shortlist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 13;
     flat_shortlist_kernel<<<a.nq, 256, smem, st>>>(s);
     return cudaGetLastError() == cudaSuccess ? 0 : 14;
 }
