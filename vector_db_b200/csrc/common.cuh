@@ -156,4 +156,56 @@ __device__ __forceinline__ void block_bitonic_sort(uint64_t* keys, uint32_t* pay
     __syncthreads();
 }
 
+constexpr int RS_TILE = 32 * 33 + 32;      // rescore32: per-warp transpose tile + row numbers (floats)
+
+// Exact distances of 32 rows by one warp, in the reference's summation order, with coalesced row reads: lane l loads
+// element (32c + l) of every row, the per-element terms go through a padded shared-memory tile, and lane l then sums row
+// l's 32 terms in index order. MODE 0: R6 sum += (q-x)^2 (HnswPqIndex.java:741-750). MODE 1: R1 eight fma lanes + pairwise
+// combine + scalar tail (DistanceAVX2.cpp:9-33). MODE 2: dot, sum += x*q (HnswIndex.java:126-133).
+template <int MODE>
+__device__ __forceinline__ float rescore32(const float* __restrict__ base, int dim, const float* __restrict__ sq, uint32_t myrow,
+                                           float* __restrict__ tile, int lane) {
+    volatile uint32_t* rows = reinterpret_cast<volatile uint32_t*>(tile + 32 * 33);     // the warp's 32 row numbers, read back as broadcasts
+    __syncwarp();
+    rows[lane] = myrow;
+    __syncwarp();
+    float acc = 0.0f, l[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) l[j] = 0.0f;
+    const int d8 = dim & ~7;
+    const int nchunk = (dim + 31) >> 5;
+    for (int c = 0; c < nchunk; c++) {
+        const int col = c * 32 + lane;
+        const bool cok = col < dim;
+        const float qv = cok ? sq[col] : 0.0f;
+        __syncwarp();
+#pragma unroll
+        for (int r0 = 0; r0 < 32; r0 += 16) {
+            float v[16];
+#pragma unroll
+            for (int r = 0; r < 16; r++) v[r] = cok ? __ldg(base + (size_t)rows[r0 + r] * dim + col) : 0.0f;
+#pragma unroll
+            for (int r = 0; r < 16; r++) tile[(r0 + r) * 33 + lane] = MODE == 2 ? __fmul_rn(v[r], qv) : __fsub_rn(qv, v[r]);
+        }
+        __syncwarp();
+        const int lim = min(32, (MODE == 1 ? d8 : dim) - c * 32);
+#pragma unroll
+        for (int i = 0; i < 32; i++) {
+            if (i < lim) {
+                const float x = tile[lane * 33 + i];
+                if (MODE == 0) acc = __fadd_rn(acc, __fmul_rn(x, x));
+                else if (MODE == 1) l[i & 7] = __fmaf_rn(x, x, l[i & 7]);
+                else acc = __fadd_rn(acc, x);
+            }
+        }
+    }
+    if (MODE == 1) {
+        const float s0 = __fadd_rn(l[0], l[4]), s1 = __fadd_rn(l[1], l[5]), s2 = __fadd_rn(l[2], l[6]), s3 = __fadd_rn(l[3], l[7]);
+        acc = __fadd_rn(__fadd_rn(s0, s1), __fadd_rn(s2, s3));
+        const int c0 = (nchunk - 1) * 32;                    // the tail [d8, dim) lies inside the last chunk, still in the tile
+        for (int gi = d8; gi < dim; gi++) { const float x = tile[lane * 33 + (gi - c0)]; acc = __fadd_rn(acc, __fmul_rn(x, x)); }
+    }
+    return acc;
+}
+
 static inline int next_pow2(int v) { int p = 1; while (p < v) p <<= 1; return p; }

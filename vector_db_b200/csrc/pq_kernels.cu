@@ -170,25 +170,29 @@ void launch_adc_scan_plain(const uint8_t* d_codes, int64_t n, int M, const float
 // a7  exact rerank: recompute the exact distance of each shortlisted row in the reference's order (one thread per
 //     candidate keeps the order sequential), then (dist,id) top-k.   HnswPqIndex.java:646-664 / HNSWPQIndex.cpp:617-655
 // =====================================================================================================
-__global__ void rerank_kernel(const float* __restrict__ base, const int32_t* __restrict__ ids, int id_offset, int dim,
-                              const float* __restrict__ queries, const uint32_t* __restrict__ rows, int R, int cap, int order,
-                              int k, int32_t* __restrict__ out_ids, float* __restrict__ out_d) {
+__global__ void __launch_bounds__(256)
+rerank_kernel(const float* __restrict__ base, const int32_t* __restrict__ ids, int id_offset, int dim,
+              const float* __restrict__ queries, const uint32_t* __restrict__ rows, int R, int cap, int order,
+              int k, int32_t* __restrict__ out_ids, float* __restrict__ out_d) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float* sq = reinterpret_cast<float*>(smem_raw);
     uint64_t* bkey = reinterpret_cast<uint64_t*>(sq + ((dim + 3) & ~3));
-    const int q = blockIdx.x;
+    float* tiles = reinterpret_cast<float*>(bkey + cap);
+    const int q = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     for (int i = threadIdx.x; i < dim; i += blockDim.x) sq[i] = queries[(size_t)q * dim + i];
     __syncthreads();
-    for (int j = threadIdx.x; j < cap; j += blockDim.x) {
-        uint64_t key = KEY_MAX;
-        if (j < R) {
-            uint32_t row = rows[(size_t)q * R + j];
-            if (row != 0xffffffffu) {
-                float d = l2sq_order(sq, base + (size_t)row * dim, dim, order);
-                key = make_key(d, ids ? ids[row] : (int32_t)(id_offset + row));
-            }
-        }
-        bkey[j] = key;
+    // 32 candidates per warp pass: coalesced row reads, per-row sums in the reference order (rescore32, common.cuh)
+    float* tile = tiles + warp * RS_TILE;
+    for (int g = warp; g * 32 < cap; g += 8) {
+        const int j = g * 32 + lane;
+        uint32_t row = j < R ? rows[(size_t)q * R + j] : 0xffffffffu;
+        const unsigned live = __ballot_sync(0xffffffffu, row != 0xffffffffu);
+        if (!live) { bkey[j] = KEY_MAX; continue; }
+        const uint32_t any = __shfl_sync(0xffffffffu, row, __ffs(live) - 1);      // dead lanes walk a live row (result unused)
+        const bool ok = row != 0xffffffffu;
+        if (!ok) row = any;
+        const float d = order == ORDER_R1 ? rescore32<1>(base, dim, sq, row, tile, lane) : rescore32<0>(base, dim, sq, row, tile, lane);
+        bkey[j] = ok ? make_key(d, ids ? ids[row] : (int32_t)(id_offset + row)) : KEY_MAX;
     }
     block_bitonic_sort<false>(bkey, nullptr, cap);
     for (int j = threadIdx.x; j < k; j += blockDim.x) {
@@ -199,8 +203,8 @@ __global__ void rerank_kernel(const float* __restrict__ base, const int32_t* __r
 }
 void launch_rerank(const float* d_base, const int32_t* d_ids, int id_offset, int dim, const float* d_q, int nq,
                    const uint32_t* d_rows, int R, int order, int k, int32_t* d_out_ids, float* d_out_d, cudaStream_t st) {
-    const int cap = next_pow2(R);
-    const size_t smem = (size_t)((dim + 3) & ~3) * 4 + (size_t)cap * 8;
+    const int cap = std::max(32, next_pow2(R));
+    const size_t smem = (size_t)((dim + 3) & ~3) * 4 + (size_t)cap * 8 + (size_t)8 * RS_TILE * 4;
     cudaFuncSetAttribute(rerank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     rerank_kernel<<<nq, 256, smem, st>>>(d_base, d_ids, id_offset, dim, d_q, d_rows, R, cap, order, k, d_out_ids, d_out_d);
 }
