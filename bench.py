@@ -124,8 +124,9 @@ def peaks():
 
 
 def make_queries(po, rank, nq):
+    from vector_db_b200 import synth as sy
     # query seed 43; each replica serves a different slice of the query stream
-    return po.fill_uniform(43, rank * nq * DIM, nq * DIM).reshape(nq, DIM)
+    return sy.fill_uniform(43, rank * nq * DIM, nq * DIM).reshape(nq, DIM)
 
 
 # ------------------------------------------------------------------------------------------------ reference arm
@@ -136,10 +137,11 @@ def run_reference(args, rank, world):
     therefore not the reference for this metric (SURVEY.md §0 findings 6, 7)."""
     if rank != 0:
         return
-    from oracle import pyoracle as po
+    from oracle import pyoracle as po          # the reference arm runs the oracle port (contract ④)
+    from vector_db_b200 import synth as sy
     cores = os.cpu_count() or 1
     n, nq = args.n, min(args.cpu_sample, args.nq)
-    X = po.synth(42, n, DIM)
+    X = sy.synth(42, n, DIM)
     Q = make_queries(po, 0, nq)
     t0 = time.time()
     o = po.OracleHnsw(po.KIND_HNSWPQ, DIM, 2 * n, pq_m=PQ_M, level_seed=1234)
@@ -194,15 +196,16 @@ def adc_scan_aux(v, po, torch, rows, pk):
     queries x rows x 125 (SURVEY.md §8d, T = 1: no CTA shares a code tile between queries), codes larger than L2.
     296 queries per launch: CTAs of different queries walk the same codes almost in lock-step, so L2 serves most of the
     re-reads (ncu: dram bytes << algorithmic bytes, profiles/) and the shared-memory gather rate is the bound."""
+    from vector_db_b200 import synth as sy
     dim, M, k = 1000, 125, 10
     p = v.NativePqIndex(dim, rows, M=M)
-    p.train(po.synth(41, 2000, dim))
+    p.train(sy.synth(41, 2000, dim))
     p.fill_synthetic(42, rows)
     p.encode_all()
     out = {"workload": "C5-shaped flat ADC scan: %d rows x 125 B codes (%.0f MB > L2), k=%d" % (rows, rows * M / 1e6, k), "bound": "hbm",
            "peak": pk["hbm_gbs"], "unit": "GB/s", "kernels": "adc_scan_fast_kernel<4> + merge_keys + adc_refine (certified exact order)"}
     for name, nq in (("batch", 296),):
-        tq = torch.from_numpy(po.synth(43, nq, dim)).cuda()
+        tq = torch.from_numpy(sy.synth(43, nq, dim)).cuda()
         for _ in range(3):
             p.search_device(tq, k)
         torch.cuda.synchronize()
@@ -225,10 +228,11 @@ def flat_gemm_aux(v, po, torch, rows, pk):
     4 096 queries, k = 100, sq-L2 — bf16 tcgen05 GEMM with a fused threshold filter, certified fp32 re-score of a 512-row
     shortlist per query (flat_gemm.cu). FLOPs = 2 x Q x N x D; time = the whole search (query mirror, sample
     GEMM, threshold select, filter GEMM, shortlist re-score), CUDA events; the Q x N matrix is never written."""
+    from vector_db_b200 import synth as sy
     dim, nq, k = 768, 4096, 100
     f = v.NativeFlatIndex(dim, rows)
     f.fill_synthetic(42, rows)
-    tq = torch.from_numpy(po.synth(43, nq, dim)).cuda()
+    tq = torch.from_numpy(sy.synth(43, nq, dim)).cuda()
     for _ in range(3):
         f.search_device(tq, k)
     torch.cuda.synchronize()
@@ -255,6 +259,7 @@ def sharded_aux(v, po, torch, dist, rank, world, local, rows_c5, rows_c4):
     returns a local top-k with global ids; NCCL all_gather of the [nq][k] (dist,id) lists + the (dist,id) merge kernel.
     TOTAL rows are fixed, so these two lines are strong-scaling numbers (the headline `value` is weak scaling).
     CUDA events around whole batches, max over ranks."""
+    from vector_db_b200 import synth as sy
     from vector_db_b200.sharded import ShardedSearcher, plan_shards
 
     def timed(fn, iters, warm):
@@ -278,10 +283,10 @@ def sharded_aux(v, po, torch, dist, rank, world, local, rows_c5, rows_c4):
         dim, M, k, R, nq = 1000, 125, 10, 1000, 1024
         lo, hi = plan_shards(rows_c5, world)[rank]
         p = v.NativePqIndex(dim, hi - lo, M=M, id_offset=lo, rerank=R, device=local)
-        p.train(po.synth(41, 10000, dim))
+        p.train(sy.synth(41, 10000, dim))
         p.fill_synthetic(42, hi - lo)
         p.encode_all()
-        tq = torch.from_numpy(po.synth(43, nq, dim)).cuda()
+        tq = torch.from_numpy(sy.synth(43, nq, dim)).cuda()
         s = ShardedSearcher(p, rank, world)
         ms = timed(lambda: s.search(tq, k), 3, 1)
         p.close()
@@ -293,7 +298,7 @@ def sharded_aux(v, po, torch, dist, rank, world, local, rows_c5, rows_c4):
         lo, hi = plan_shards(rows_c4, world)[rank]
         f = v.NativeFlatIndex(dim, hi - lo, id_offset=lo, device=local)
         f.fill_synthetic(42, hi - lo)
-        tq = torch.from_numpy(po.synth(43, nq, dim)).cuda()
+        tq = torch.from_numpy(sy.synth(43, nq, dim)).cuda()
         s = ShardedSearcher(f, rank, world)
         ms = timed(lambda: s.search(tq, k), 5, 2)
         f.close()
@@ -307,9 +312,10 @@ def recall_gate_c1(v, po, torch, cores):
     """BASELINE.json configs[0] (the README benchmark the reference publishes Recall@10 97.6 % on): 10 000 x 512-d, HNSW+PQ
     64 x 8, 1 000 queries, k = 10 — the shape on which the reference's algorithm itself reaches Recall@10 >= 0.95 with
     uniform random data (at C3 its beam is capped at 5 000 of 100 000 rows, HnswPqIndex.java:621, and it reaches ~0.84)."""
+    from vector_db_b200 import synth as sy
     n, nq = 10_000, 1000
-    X = po.synth(42, n, DIM)
-    Q = po.synth(43, nq, DIM)
+    X = sy.synth(42, n, DIM)
+    Q = sy.synth(43, nq, DIM)
     idx = v.NativeHnswPqIndex(DIM, 2 * n, pqM=PQ_M, level_seed=1234)
     idx.addBatch(np.arange(n, dtype=np.int32), X)
     idx.buildIndex()
@@ -342,9 +348,10 @@ def recall_gate_c1(v, po, torch, cores):
 def recall_gate_c2(v, po, torch, cores):
     """BASELINE.json configs[1] (C2): 10 000 x 128-d, HNSW uncompressed (cosine, ef = 400, HnswIndex.java), k = 10, recall against
     the exact cosine ranking (the tensor-core flat search of the same library, itself bit-checked against the CPU brute force)."""
+    from vector_db_b200 import synth as sy
     n, nq, dim = 10_000, 1000, 128
-    X = po.synth(42, n, dim)
-    Q = po.synth(43, nq, dim)
+    X = sy.synth(42, n, dim)
+    Q = sy.synth(43, nq, dim)
     idx = v.NativeHnswIndex(dim, 2 * n, level_seed=1234)
     idx.addBatch(np.arange(n, dtype=np.int32), X)
     idx.buildIndex()
@@ -385,7 +392,8 @@ def run_b200(args, rank, world):
     import torch
     import torch.distributed as dist
     import __graft_entry__ as ge
-    from oracle import pyoracle as po          # checker + cpu_baseline leg only
+    from oracle import pyoracle as po          # checker + cpu_baseline leg only (inputs come from vector_db_b200.synth)
+    from vector_db_b200 import synth as sy
     if rank == 0:
         ge.build_product()
     if world > 1:
@@ -397,7 +405,7 @@ def run_b200(args, rank, world):
     pk, pk_kind = peaks()
     n, nq = args.n, args.nq
 
-    X = po.synth(42, n, DIM)
+    X = sy.synth(42, n, DIM)
     t0 = time.time()
     idx = v.NativeHnswPqIndex(DIM, 2 * n, pqM=PQ_M, level_seed=1234, device=local)
     idx.addBatch(np.arange(n, dtype=np.int32), X)

@@ -93,3 +93,14 @@ def test_shard_plan_and_merge_rule():
     i = np.array([[[7, 1, -1]], [[3, 9, 4]]], dtype=np.int32)
     od, oi = merge_topk_host(d, i, 3)
     assert list(oi[0]) == [3, 7, 9] and list(od[0]) == [0.5, 0.5, np.float32(0.6)]     # ties broken by id
+
+
+def test_product_synthetic_generator_matches_oracle():
+    """vector_db_b200.synth (host twin of fill_synth_kernel, used by bench.py / tools for inputs) == the oracle's generator."""
+    from oracle import pyoracle as po
+    from vector_db_b200 import synth as sy
+    a, b = po.synth(42, 777, 96), sy.synth(42, 777, 96)
+    assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+    a, b = po.fill_uniform(43, 123456789, 4097), sy.fill_uniform(43, 123456789, 4097, chunk=1000)
+    assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+    assert a.min() >= -1.0 and a.max() < 1.0

@@ -18,9 +18,10 @@ def main():
     ap.add_argument("--big", type=int, default=0, help="also time N=big rows generated on the device (no oracle)")
     a = ap.parse_args()
     import torch
-    from oracle import pyoracle as po
+    from oracle import pyoracle as po      # checker: CPU brute force / reference-order scan
+    from vector_db_b200 import synth as sy
     import vector_db_b200 as v
-    X, Q = po.synth(42, a.n, a.dim), po.synth(43, a.nq, a.dim)
+    X, Q = sy.synth(42, a.n, a.dim), sy.synth(43, a.nq, a.dim)
     f = v.NativeFlatIndex(a.dim, a.n, metric=a.metric, arith=a.arith)
     f.addBatch(np.arange(a.n, dtype=np.int32), X)
     t0 = time.time()
@@ -43,7 +44,7 @@ def main():
     if a.big:
         f = v.NativeFlatIndex(a.dim, a.big, metric=a.metric)
         f.fill_synthetic(42, a.big)
-        tq = torch.from_numpy(po.synth(43, 4096, a.dim)).cuda()
+        tq = torch.from_numpy(sy.synth(43, 4096, a.dim)).cuda()
         res = []
         for it in range(3):
             f.search_device(tq, a.k); torch.cuda.synchronize()

@@ -24,7 +24,7 @@ def main():
     ap.add_argument("--trav-batch", type=int, default=0)
     a = ap.parse_args()
     import torch
-    from oracle import pyoracle as po      # synthetic generator only
+    from vector_db_b200 import synth as sy
     import vector_db_b200 as v
     out = {"what": a.what}
     if a.what == "hnsw":
@@ -32,12 +32,12 @@ def main():
         if a.snapshot and os.path.exists(a.snapshot):
             idx.load(a.snapshot)
         else:
-            X = po.synth(42, a.n, a.dim)
+            X = sy.synth(42, a.n, a.dim)
             idx.addBatch(np.arange(a.n, dtype=np.int32), X)
             t0 = time.time(); idx.buildIndex(); out["build_s"] = time.time() - t0
             if a.snapshot:
                 idx.save(a.snapshot)
-        tq = torch.from_numpy(po.synth(43, a.nq, a.dim)).cuda()
+        tq = torch.from_numpy(sy.synth(43, a.nq, a.dim)).cuda()
         ms = []
         for _ in range(a.iters):
             idx.search_device(tq, a.k); torch.cuda.synchronize()
@@ -47,10 +47,10 @@ def main():
     elif a.what == "adc":
         dim, M = 1000, 125
         p = v.NativePqIndex(dim, a.rows, M=M)
-        p.train(po.synth(41, 2000, dim))
+        p.train(sy.synth(41, 2000, dim))
         p.fill_synthetic(42, a.rows)
         p.encode_all()
-        tq = torch.from_numpy(po.synth(43, a.nq, dim)).cuda()
+        tq = torch.from_numpy(sy.synth(43, a.nq, dim)).cuda()
         ms = []
         for _ in range(a.iters):
             p.search_device(tq, a.k); torch.cuda.synchronize()
@@ -59,7 +59,7 @@ def main():
     else:
         f = v.NativeFlatIndex(a.dim, a.n)
         f.fill_synthetic(42, a.n)
-        tq = torch.from_numpy(po.synth(43, a.nq, a.dim)).cuda()
+        tq = torch.from_numpy(sy.synth(43, a.nq, a.dim)).cuda()
         ms = []
         for _ in range(a.iters):
             f.search_device(tq, a.k); torch.cuda.synchronize()

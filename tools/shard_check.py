@@ -34,7 +34,8 @@ def main():
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", 0)))
     dist.init_process_group("nccl")
-    from oracle import pyoracle as po
+    from oracle import pyoracle as po      # checker: CPU brute force / reference-order scan
+    from vector_db_b200 import synth as sy
     import vector_db_b200 as v
     from vector_db_b200.sharded import ShardedSearcher, plan_shards
     dev = torch.cuda.current_device()
@@ -45,11 +46,11 @@ def main():
     lo, hi = plan_shards(n, world)[rank]
     f = v.NativeFlatIndex(dim, hi - lo, id_offset=lo, device=dev)
     f.fill_synthetic(42, hi - lo)
-    Q = po.synth(43, nq, dim)
+    Q = sy.synth(43, nq, dim)
     tq = torch.from_numpy(Q).cuda()
     ids, d = ShardedSearcher(f, rank, world).search(tq, k)
     if rank == 0:
-        oi, od = po.flat_search(po.synth(42, n, dim), Q, k, nthreads=16)
+        oi, od = po.flat_search(sy.synth(42, n, dim), Q, k, nthreads=16)
         out["flat_parity"] = {"ids_equal": float((ids.cpu().numpy() == oi).mean()),
                               "dist_bits_equal": float((d.cpu().numpy().view(np.uint32) == od.view(np.uint32)).mean())}
     st = f.stats(); out.setdefault("flat_stats", {})["rank0"] = [st["flat_certified"], st["flat_fallback"]] if rank == 0 else None
@@ -59,15 +60,15 @@ def main():
     n, dim, M, k, R = 100_000, 128, 16, 10, 200
     lo, hi = plan_shards(n, world)[rank]
     p = v.NativePqIndex(dim, hi - lo, M=M, id_offset=lo, rerank=R, device=dev)
-    p.train(po.synth(41, 3000, dim))
+    p.train(sy.synth(41, 3000, dim))
     p.fill_synthetic(42, hi - lo)
     p.encode_all()
-    Q = po.synth(43, 32, dim)
+    Q = sy.synth(43, 32, dim)
     tq = torch.from_numpy(Q).cuda()
     ids, d = ShardedSearcher(p, rank, world).search(tq, k)
     if rank == 0:
         # the reference order: per-shard ADC top-R -> fp32 rerank -> top-k, then the (dist,id) merge == global rerank of the union
-        X = po.synth(42, n, dim)
+        X = sy.synth(42, n, dim)
         cb = p.codebooks()
         parts = []
         for (a0, a1) in plan_shards(n, world):
@@ -87,7 +88,7 @@ def main():
         lo, hi = plan_shards(n, world)[rank]
         f = v.NativeFlatIndex(dim, hi - lo, id_offset=lo, device=dev)
         f.fill_synthetic(42, hi - lo)
-        tq = torch.from_numpy(po.synth(43, nq, dim)).cuda()
+        tq = torch.from_numpy(sy.synth(43, nq, dim)).cuda()
         s = ShardedSearcher(f, rank, world)
         ms = timed(torch, dist, lambda: s.search(tq, k))
         st = f.stats()
@@ -100,10 +101,10 @@ def main():
         n, dim, M, k, R, nq = a.c5_rows, 1000, 125, 10, 1000, 1024
         lo, hi = plan_shards(n, world)[rank]
         p = v.NativePqIndex(dim, hi - lo, M=M, id_offset=lo, rerank=R, device=dev)
-        p.train(po.synth(41, 10000, dim))
+        p.train(sy.synth(41, 10000, dim))
         p.fill_synthetic(42, hi - lo)
         p.encode_all()
-        tq = torch.from_numpy(po.synth(43, nq, dim)).cuda()
+        tq = torch.from_numpy(sy.synth(43, nq, dim)).cuda()
         s = ShardedSearcher(p, rank, world)
         ms = timed(torch, dist, lambda: s.search(tq, k), iters=3, warm=1)
         out["c5"] = {"rows": n, "ms": ms, "qps": nq / ms * 1e3, "scan_gbs_aggregate": nq * n * M / (ms * 1e-3) / 1e9}
