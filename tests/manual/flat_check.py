@@ -1,9 +1,9 @@
 #!/usr/bin/env python
-"""tools/flat_check.py — bring-up check of the tensor-core flat search against the CPU oracle (GPU box only).
-    python tools/flat_check.py [--n 50000] [--dim 768] [--nq 200] [--k 100] [--metric 0]"""
+"""tests/manual/flat_check.py — bring-up check of the tensor-core flat search against the CPU oracle (GPU box only).
+    python tests/manual/flat_check.py [--n 50000] [--dim 768] [--nq 200] [--k 100] [--metric 0]"""
 import argparse, json, os, sys, time
 import numpy as np
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 
 

@@ -1,12 +1,12 @@
 #!/usr/bin/env python
-"""tools/shard_check.py — multi-GPU check of the id-range-sharded flat / PQ path, one process per GPU:
-    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tools/shard_check.py
+"""tests/manual/shard_check.py — multi-GPU check of the id-range-sharded flat / PQ path, one process per GPU:
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tests/manual/shard_check.py
 1. parity: sharded flat search (tensor-core path per shard + NCCL all_gather of the [nq][k] lists + (dist,id) merge kernel)
    against the CPU oracle's brute force over the whole logical dataset; same for the PQ ADC scan + rerank;
 2. timing (CUDA events, max over ranks): C4 (1M x 768 flat, k=100, 4096 queries) and a C5-shaped PQ scan, rows split N/g."""
 import argparse, json, os, sys
 import numpy as np
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 
 
