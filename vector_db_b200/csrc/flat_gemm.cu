@@ -560,7 +560,7 @@ struct ShortlistArgs {
     int flag_or;                 // later slabs: OR into flag[] and leave the per-query statistics to the first slab
 };
 
-__global__ void __launch_bounds__(256, 2)
+__global__ void __launch_bounds__(256, 3)
 flat_shortlist_kernel(const ShortlistArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     // [hk | rw] survivor scores / rows (dead after the selection, then reused for the per-warp transpose tiles),
@@ -572,94 +572,112 @@ flat_shortlist_kernel(const ShortlistArgs a) {
     uint64_t* rkey = reinterpret_cast<uint64_t*>(sel + a.k2);
     float* sq = reinterpret_cast<float*>(rkey + a.k2p);
     __shared__ uint32_t s_cnt0[32], s_nsel, s_ntie;
+    __shared__ int s_ok;
     const int q = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t cnt = a.cnt[q];
     const int c = (int)min(cnt, a.cap);
-    for (int i = threadIdx.x; i < c; i += blockDim.x) {
-        const uint64_t key = a.cand[(size_t)q * a.cap + i];
-        hk[i] = (uint32_t)(key >> 32); rw[i] = (uint32_t)key;
-    }
     for (int i = threadIdx.x; i < a.dim; i += blockDim.x) sq[i] = a.queries[(size_t)q * a.dim + i];
-    if (threadIdx.x < 32) s_cnt0[threadIdx.x] = 0u;
-    if (threadIdx.x == 0) { s_nsel = 0u; s_ntie = 0u; }
-    __syncthreads();
-    const int R = min(c, a.k2);
-    // ---- the k2 best survivors by approximate score: radix bisection for the (k2+1)-th smallest ordered score T (its
-    //      value is also the bound s_cut for every row left out), then one compaction pass. No sort of the ~2 000 survivors.
-    uint32_t T = 0xffffffffu;
-    int need_ties = 0;
-    if (c > a.k2) {
-        uint32_t prefix = 0u;
-        int r = a.k2;                                           // 0-based rank looked for
-        for (int b = 31; b >= 0; b--) {
-            uint32_t local = 0u;
-            for (int i = threadIdx.x; i < c; i += blockDim.x) local += (((hk[i] ^ prefix) >> b) == 0u) ? 1u : 0u;
-            local = __reduce_add_sync(0xffffffffu, local);
-            if (lane == 0 && local) atomicAdd(&s_cnt0[b], local);
-            __syncthreads();
-            const int cnt0 = (int)s_cnt0[b];                    // elements matching the prefix with bit b clear
-            if (r >= cnt0) { prefix |= 1u << b; r -= cnt0; }
-        }
-        T = prefix;
-        need_ties = r;                                          // how many survivors equal to T still belong to the best k2
-        for (int i0 = 0; i0 < c; i0 += blockDim.x) {
-            const int i = i0 + threadIdx.x;
-            const uint32_t h = i < c ? hk[i] : 0xffffffffu;
-            const bool lt = i < c && h < T;
-            const uint32_t bal = __ballot_sync(0xffffffffu, lt);
-            uint32_t base = 0u;
-            if (lane == 0 && bal) base = atomicAdd(&s_nsel, (uint32_t)__popc(bal));
-            base = __shfl_sync(0xffffffffu, base, 0);
-            if (lt) sel[base + __popc(bal & ((1u << lane) - 1u))] = rw[i];
-            else if (i < c && h == T) {
-                const uint32_t p = atomicAdd(&s_ntie, 1u);
-                if ((int)p < need_ties) sel[a.k2 - 1 - (int)p] = rw[i];
-            }
-        }
-    } else {
-        for (int i = threadIdx.x; i < c; i += blockDim.x) sel[i] = rw[i];
-    }
-    __syncthreads();                                            // hk / rw are dead from here on: the tiles reuse their space
     const float qn = a.qstat[q].y;
     float* tile = tiles + warp * RS_TILE;
-    for (int g = warp; g * 32 < a.k2p; g += 8) {
-        const int j = g * 32 + lane;
-        if (g * 32 >= R) { rkey[j] = KEY_MAX; continue; }
-        const uint32_t row = j < R ? sel[j] : sel[0];
-        float d;
-        if (a.metric == 1) d = cosine_dist_from_dot(rescore32<2>(a.base, a.dim, sq, row, tile, lane), a.norms[row], qn);
-        else if (a.order == ORDER_R1) d = rescore32<1>(a.base, a.dim, sq, row, tile, lane);
-        else d = rescore32<0>(a.base, a.dim, sq, row, tile, lane);
-        rkey[j] = j < R ? make_key(d, a.ids ? a.ids[row] : (int32_t)(a.id_offset + row)) : KEY_MAX;
-    }
-    block_bitonic_sort<false>(rkey, nullptr, a.k2p);
-    for (int j = threadIdx.x; j < a.k; j += blockDim.x) {
-        const uint64_t key = j < a.k2p ? rkey[j] : KEY_MAX;
-        if (key == KEY_MAX) { a.out_ids[(size_t)q * a.k + j] = -1; a.out_d[(size_t)q * a.k + j] = __int_as_float(0x7f800000); }
-        else { a.out_ids[(size_t)q * a.k + j] = key_id(key); a.out_d[(size_t)q * a.k + j] = key_dist(key); }
-    }
-    if (threadIdx.x == 0) {
-        bool ok;
-        if ((int64_t)cnt == a.n && c <= a.k2 && cnt <= a.cap) {
-            ok = true;                                       // every row was re-scored
-        } else if (cnt > a.cap || R < a.k) {
-            ok = false;                                      // list overflow, or too few survivors to fill k
+    // Two attempts: the exact re-score is the expensive part (k2 random rows from HBM per query), and for most queries the
+    // certificate already holds with the best k2/2 survivors; only if it does not, the full k2 are re-scored.
+    const int k2a = (a.k2 >= 256 && a.k2 / 2 >= a.k + 64) ? a.k2 / 2 : a.k2;
+    bool ok = false;
+    for (int attempt = 0; attempt < 2 && !ok; attempt++) {
+        const int kk = attempt == 0 ? k2a : a.k2;
+        if (attempt == 1 && (kk == k2a || c <= k2a)) break;      // nothing more to add
+        int kp = 32;
+        while (kp < kk) kp <<= 1;
+        for (int i = threadIdx.x; i < c; i += blockDim.x) {
+            const uint64_t key = a.cand[(size_t)q * a.cap + i];
+            hk[i] = (uint32_t)(key >> 32); rw[i] = (uint32_t)key;
+        }
+        if (threadIdx.x < 32) s_cnt0[threadIdx.x] = 0u;
+        if (threadIdx.x == 0) { s_nsel = 0u; s_ntie = 0u; }
+        __syncthreads();
+        const int R = min(c, kk);
+        // ---- the kk best survivors by approximate score: radix bisection for the (kk+1)-th smallest ordered score T (its
+        //      value is also the bound s_cut for every row left out), then one compaction pass. No sort of the survivors.
+        uint32_t T = 0xffffffffu;
+        if (c > kk) {
+            uint32_t prefix = 0u;
+            int r = kk;                                         // 0-based rank looked for
+            for (int b = 31; b >= 0; b--) {
+                uint32_t local = 0u;
+                for (int i = threadIdx.x; i < c; i += blockDim.x) local += (((hk[i] ^ prefix) >> b) == 0u) ? 1u : 0u;
+                local = __reduce_add_sync(0xffffffffu, local);
+                if (lane == 0 && local) atomicAdd(&s_cnt0[b], local);
+                __syncthreads();
+                const int cnt0 = (int)s_cnt0[b];                // elements matching the prefix with bit b clear
+                if (r >= cnt0) { prefix |= 1u << b; r -= cnt0; }
+            }
+            T = prefix;
+            const int need_ties = r;                            // how many survivors equal to T still belong to the best kk
+            for (int i0 = 0; i0 < c; i0 += blockDim.x) {
+                const int i = i0 + threadIdx.x;
+                const uint32_t h = i < c ? hk[i] : 0xffffffffu;
+                const bool lt = i < c && h < T;
+                const uint32_t bal = __ballot_sync(0xffffffffu, lt);
+                uint32_t base = 0u;
+                if (lane == 0 && bal) base = atomicAdd(&s_nsel, (uint32_t)__popc(bal));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (lt) sel[base + __popc(bal & ((1u << lane) - 1u))] = rw[i];
+                else if (i < c && h == T) {
+                    const uint32_t p = atomicAdd(&s_ntie, 1u);
+                    if ((int)p < need_ties) sel[kk - 1 - (int)p] = rw[i];
+                }
+            }
         } else {
-            // rows not re-scored have approximate score >= s_cut
-            const double s_cut = c > a.k2 ? (double)ord2f(T) : (double)a.tau[q];
-            const double dk = (double)key_dist(rkey[a.k - 1]);
-            const double amax = (double)__uint_as_float(*a.amax_bits), qn2 = (double)a.qstat[q].x;
-            const double gamma = (double)a.dim * 2.384185791015625e-07;          // dim * 2^-22: fp32 summation slack
-            const double ecs = (double)a.err_rel * sqrt(qn2 * amax);               // |acc - q'.x'| for any row
-            if (a.metric == 0) {
-                const double lb = s_cut + qn2 - 2.0 * ecs - (amax + qn2 + fabs(s_cut)) * gamma;
-                ok = lb > 0.0 && dk * (1.0 + gamma) < lb * (1.0 - gamma);
+            for (int i = threadIdx.x; i < c; i += blockDim.x) sel[i] = rw[i];
+        }
+        __syncthreads();                                        // hk / rw are dead from here on: the tiles reuse their space
+        for (int g = warp; g * 32 < kp; g += 8) {
+            const int j = g * 32 + lane;
+            if (g * 32 >= R) { rkey[j] = KEY_MAX; continue; }
+            const uint32_t row = j < R ? sel[j] : sel[0];
+            float d;
+            if (a.metric == 1) d = cosine_dist_from_dot(rescore32<2>(a.base, a.dim, sq, row, tile, lane), a.norms[row], qn);
+            else if (a.order == ORDER_R1) d = rescore32<1>(a.base, a.dim, sq, row, tile, lane);
+            else d = rescore32<0>(a.base, a.dim, sq, row, tile, lane);
+            rkey[j] = j < R ? make_key(d, a.ids ? a.ids[row] : (int32_t)(a.id_offset + row)) : KEY_MAX;
+        }
+        block_bitonic_sort<false>(rkey, nullptr, kp);
+        if (threadIdx.x == 0) {
+            bool good;
+            if ((int64_t)cnt == a.n && c <= kk && cnt <= a.cap) {
+                good = true;                                     // every row was re-scored
+            } else if (cnt > a.cap || R < a.k) {
+                good = false;                                    // list overflow, or too few survivors to fill k
             } else {
-                const double u = -s_cut + ecs;                                     // upper bound on dot(x, q^) of an outsider
-                const double lb = 1.0 - (u >= 0.0 ? u * (1.0 + 1e-5) : u * (1.0 - 1e-5)) - gamma - 1e-5;
-                ok = dk + gamma + 1e-5 < lb;
+                // rows not re-scored have approximate score >= s_cut
+                const double s_cut = c > kk ? (double)ord2f(T) : (double)a.tau[q];
+                const double dk = (double)key_dist(rkey[a.k - 1]);
+                const double amax = (double)__uint_as_float(*a.amax_bits), qn2 = (double)a.qstat[q].x;
+                const double gamma = (double)a.dim * 2.384185791015625e-07;          // dim * 2^-22: fp32 summation slack
+                const double ecs = (double)a.err_rel * sqrt(qn2 * amax);               // |acc - q'.x'| for any row
+                if (a.metric == 0) {
+                    const double lb = s_cut + qn2 - 2.0 * ecs - (amax + qn2 + fabs(s_cut)) * gamma;
+                    good = lb > 0.0 && dk * (1.0 + gamma) < lb * (1.0 - gamma);
+                } else {
+                    const double u = -s_cut + ecs;                                     // upper bound on dot(x, q^) of an outsider
+                    const double lb = 1.0 - (u >= 0.0 ? u * (1.0 + 1e-5) : u * (1.0 - 1e-5)) - gamma - 1e-5;
+                    good = dk + gamma + 1e-5 < lb;
+                }
+            }
+            s_ok = good ? 1 : 0;
+        }
+        __syncthreads();
+        ok = s_ok != 0;
+        if (ok || attempt == 1 || kk == a.k2 || c <= k2a) {      // final attempt for this query: emit its list
+            for (int j = threadIdx.x; j < a.k; j += blockDim.x) {
+                const uint64_t key = j < kp ? rkey[j] : KEY_MAX;
+                if (key == KEY_MAX) { a.out_ids[(size_t)q * a.k + j] = -1; a.out_d[(size_t)q * a.k + j] = __int_as_float(0x7f800000); }
+                else { a.out_ids[(size_t)q * a.k + j] = key_id(key); a.out_d[(size_t)q * a.k + j] = key_dist(key); }
             }
         }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
         if (a.flag_or) {
             if (!ok && !a.flag[q]) { a.flag[q] = 1; atomicAdd(a.stats + 1, 1ull); atomicAdd(a.stats, ~0ull); }   // certified -> fallback
         } else {
