@@ -713,14 +713,18 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
                 newfrontF = takenF < b ? S.candF[takenF] : (fndF > B ? S.candF[B - 1] + 1 : toF);
             }
             HN_MARK(1);
-            // C2. neighbour lists (loads of four rows in flight per warp) + visited test-and-set; fresh nodes appended
+            // C2. neighbour lists (loads of eight rows in flight per warp) + visited test-and-set; fresh nodes are appended
+            //     and their traversal rows pulled towards L2 right away (the misses overlap in one memory round trip and
+            //     are under way while the rest of the lists are still being examined)
             {
                 const int nj = (p.deg + 31) >> 5;
                 const int nitems = nsel * nj;
-                for (int it0 = warp; it0 < nitems; it0 += HN_WARPS * 4) {
-                    int nb[4];
+                const int lines = (p.tstride + 127) >> 7;
+                const unsigned char* tb = reinterpret_cast<const unsigned char*>(p.tbase);
+                for (int it0 = warp; it0 < nitems; it0 += HN_WARPS * 8) {
+                    int nb[8];
 #pragma unroll
-                    for (int t = 0; t < 4; t++) {
+                    for (int t = 0; t < 8; t++) {
                         const int it = it0 + t * HN_WARPS;
                         nb[t] = -1;
                         if (it < nitems) {
@@ -729,7 +733,7 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
                         }
                     }
 #pragma unroll
-                    for (int t = 0; t < 4; t++) {
+                    for (int t = 0; t < 8; t++) {
                         bool fresh = false;
                         if (nb[t] >= 0) {
                             const uint32_t bit = 1u << (nb[t] & 31);
@@ -737,27 +741,21 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
                             fresh = !(old & bit);
                         }
                         const unsigned m = __ballot_sync(0xffffffffu, fresh);
+                        if (m == 0u) continue;
                         int basec = 0;
-                        if (lane == 0 && m) basec = atomicAdd(&S.nfresh, __popc(m));
+                        if (lane == 0) basec = atomicAdd(&S.nfresh, __popc(m));
                         basec = __shfl_sync(0xffffffffu, basec, 0);
-                        if (fresh) fnode[basec + __popc(m & ((1u << lane) - 1u))] = nb[t];
+                        if (fresh) {
+                            fnode[basec + __popc(m & ((1u << lane) - 1u))] = nb[t];
+                            const unsigned char* rp = tb + (size_t)nb[t] * p.tstride;
+                            for (int l = 0; l < lines; l++) asm volatile("prefetch.global.L2 [%0];" ::"l"(rp + ((size_t)l << 7)));
+                        }
                     }
                 }
             }
             __syncthreads();
             const int nf = S.nfresh;
             if (tid == 0) { exps += nsel; evals += nf; S.ph[7]++; }
-            // pull every fresh row towards L2 now: the misses (rows not resident) overlap in ONE memory round trip instead
-            // of stalling each stage of the distance loop in turn
-            {
-                const int lines = (p.tstride + 127) >> 7;
-                const int lsh = (lines & (lines - 1)) == 0 ? 31 - __clz(lines) : -1;      // power of two: shift instead of divide
-                const unsigned char* tb = reinterpret_cast<const unsigned char*>(p.tbase);
-                for (int t = tid; t < nf * lines; t += HN_NT) {
-                    const int r = lsh >= 0 ? (t >> lsh) : t / lines, l = t - r * lines;
-                    asm volatile("prefetch.global.L2 [%0];" ::"l"(tb + (size_t)fnode[r] * p.tstride + ((size_t)l << 7)));
-                }
-            }
             HN_MARK(2);
             // C3. distances of the fresh rows; acceptance: results.size() < ef || d < furthest
             //     (furthest live: HnswPqIndex.java:953-963; stale == entry distance until the first eviction: :876-884,
