@@ -6,12 +6,14 @@
 // Why not one thread per row (pq_kernels.cu adc_scan_topr_kernel, kept as the exact fallback): 32 lanes gathering
 // lut[m][c_lane] for the SAME m hit random banks of one 1 KB LUT row — ~3.5-way conflicts — and each lane reads its own
 // 125-byte row (uncoalesced). This kernel instead
-//   * stores codes TRANSPOSED in blocks of 16 rows: codesT[block][m][16 rows] — lane l loads 16 bytes = subspace
-//     m = l + 32 j of 16 consecutive rows; a warp's load is 512 contiguous bytes (coalesced, 128-bit);
+//   * stores codes TRANSPOSED in blocks of 16 rows: codesT[block][m][16 rows] — a lane loads 16 bytes = one subspace of 16
+//     consecutive rows; a HALF-warp works one block (lane l16 takes subspaces l16 + 16 j), the two halves of a warp take two
+//     consecutive blocks, so a warp's load is two runs of 256 contiguous bytes (coalesced, 128-bit);
 //   * lays the LUT out in shared memory as  offset(m, c) = (m >> 6) * 64 KB + c * 256 B + (m & 63) * 4 B, so lane l's
 //     gathers all land in bank l: conflict-free BY CONSTRUCTION for any code values, and the whole address is ONE
 //     byte-permute of (code word, lane constant): PRMT + LDS + FADD per gathered value;
-//   * reduces the 16 per-lane partial sums across the warp with a transposing butterfly (16 shuffles per 16 rows);
+//   * reduces the 16 per-lane partial sums across the 16 lanes of the half-warp with a transposing butterfly: 15 shuffles
+//     per 32 rows (a whole-warp butterfly needs 17 per 16), every lane ends with one row;
 //   * keeps a per-CTA candidate buffer with a lazily tightened threshold; after warm-up almost every row fails one compare.
 // The sums are associated differently from R3 (within 2*M*2^-24 relative), so the scan returns a shortlist of R2 > R rows
 // and adc_refine_kernel re-evaluates exactly those in order R3, sorts by (dist, id) and CERTIFIES that no row outside the
@@ -23,12 +25,12 @@
 
 #define AF_NT 512
 #define AF_WARPS (AF_NT / 32)
-#define AF_K 8                                  // 16-row blocks per warp between barriers
-#define AF_SPAN (16 * AF_WARPS * AF_K)          // rows per super-iteration (= max insertions between barriers)
+#define AF_K 4                                  // pairs of 16-row blocks per warp between barriers (even)
+#define AF_SPAN (32 * AF_WARPS * AF_K)          // rows per super-iteration (= max insertions between barriers)
 
 // ---- codes [n][M] -> codesT [ceil(n/16)][M][16]; rows past n are code 0 (never reported: row < n is checked).
-//      Inside a chunk the 16 rows are stored in the order the reading lane's butterfly wants (see the scan kernel): byte a
-//      = row a ^ p(lane), which removes every select from the transposing reduction. ----
+//      The 16-byte chunk of subspace m is read by lane (m & 15) of a half-warp; inside the chunk byte a holds row
+//      a ^ (m & 15), the order that lane's butterfly wants (see the scan kernel): no selects in the transposing reduction. ----
 __global__ void transpose_codes_kernel(const uint8_t* __restrict__ codes, int64_t n, int M, int64_t row0, uint8_t* __restrict__ codesT) {
     // one thread per output byte of blocks covering rows [row0, n)
     const int64_t b0 = row0 >> 4;
@@ -36,8 +38,7 @@ __global__ void transpose_codes_kernel(const uint8_t* __restrict__ codes, int64_
     for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
         const int64_t bm = t >> 4;
         const int m = (int)(bm % M);
-        const int l = m & 31;             // the lane that reads this 16-byte chunk; byte a holds row a ^ p(l), p = row_of_lane
-        const int r = (int)(t & 15) ^ ((((l >> 4) & 1) << 3) | (((l >> 3) & 1) << 2) | (((l >> 2) & 1) << 1) | ((l >> 1) & 1));
+        const int r = (int)(t & 15) ^ (m & 15);
         const int64_t row = ((b0 + bm / M) << 4) + r;
         codesT[(b0 * M << 4) + t] = row < n ? codes[row * M + m] : (uint8_t)0;
     }
@@ -72,102 +73,121 @@ __device__ __forceinline__ uint4 ld_stream(const uint4* p) {     // codes are re
     return r;
 }
 
-// loads are never predicated: a lane past M reads the row's last chunk (its LUT column is all zero, so whatever it gathers
-// adds 0.0), a block past the chunk's end re-reads the last valid block (its rows are not reported)
-template <int NJ>
-__device__ __forceinline__ void load_block(const uint4* __restrict__ p, int lastoff, uint4 (&v)[NJ]) {
-#pragma unroll
-    for (int j = 0; j < NJ - 1; j++) v[j] = ld_stream(p + 32 * j);
-    v[NJ - 1] = ld_stream(p + lastoff);
+// One 16-row block is worked by a HALF-warp: lane l16 of half h gathers subspaces m = 64 g + l16 + 16 (jj ^ h), jj = 0..3, of
+// LUT group g (a "quad" of four 16-byte chunks per lane and group), so at every step the 32 lanes of the warp — two blocks —
+// touch 32 different banks. Loads are never predicated: a lane whose subspace is past M reads the row's last chunk (its LUT
+// column is all zero, so whatever it gathers adds 0.0); a block past the chunk's end re-reads the last valid block (its rows
+// are not reported).
+template <int NQ>
+__device__ __forceinline__ void load_quad(const uint4* __restrict__ pe, const uint4* __restrict__ po, int g, const int (&offl)[4], uint4 (&v)[4]) {
+    if (g < NQ - 1) {
+        v[0] = ld_stream(pe + 64 * g); v[1] = ld_stream(po + 64 * g); v[2] = ld_stream(pe + 64 * g + 32); v[3] = ld_stream(po + 64 * g + 32);
+    } else {
+        v[0] = ld_stream(pe + offl[0]); v[1] = ld_stream(po + offl[1]); v[2] = ld_stream(pe + offl[2]); v[3] = ld_stream(po + offl[3]);
+    }
 }
 
-// gather + transposing butterfly for one 16-row block held in v[]; returns this lane's row total (valid on every lane pair)
-template <int NJ>
-__device__ __forceinline__ float block_distance(const uint4 (&v)[NJ], const uint32_t (&lbase)[NJ], const unsigned char* __restrict__ lutb) {
-    float acc[16];
+// 64 gathers of one quad into the 16 per-lane partial sums; the group's 64 KB image is an immediate offset of the LDS
+template <bool FIRST>
+__device__ __forceinline__ void gather_quad(const uint4 (&v)[4], const uint32_t (&lbase)[4], const unsigned char* __restrict__ lutg, float (&acc)[16]) {
 #pragma unroll
-    for (int j = 0; j < NJ; j++) {
-        const uint32_t w[4] = {v[j].x, v[j].y, v[j].z, v[j].w};
+    for (int jj = 0; jj < 4; jj++) {
+        const uint32_t w[4] = {v[jj].x, v[jj].y, v[jj].z, v[jj].w};
 #pragma unroll
         for (int i = 0; i < 4; i++) {
-            const float v0 = *reinterpret_cast<const float*>(lutb + __byte_perm(w[i], lbase[j], 0x7604));
-            const float v1 = *reinterpret_cast<const float*>(lutb + __byte_perm(w[i], lbase[j], 0x7614));
-            const float v2 = *reinterpret_cast<const float*>(lutb + __byte_perm(w[i], lbase[j], 0x7624));
-            const float v3 = *reinterpret_cast<const float*>(lutb + __byte_perm(w[i], lbase[j], 0x7634));
-            if (j == 0) { acc[4 * i + 0] = v0; acc[4 * i + 1] = v1; acc[4 * i + 2] = v2; acc[4 * i + 3] = v3; }
+            const float v0 = *reinterpret_cast<const float*>(lutg + __byte_perm(w[i], lbase[jj], 0x7604));
+            const float v1 = *reinterpret_cast<const float*>(lutg + __byte_perm(w[i], lbase[jj], 0x7614));
+            const float v2 = *reinterpret_cast<const float*>(lutg + __byte_perm(w[i], lbase[jj], 0x7624));
+            const float v3 = *reinterpret_cast<const float*>(lutg + __byte_perm(w[i], lbase[jj], 0x7634));
+            if (FIRST && jj == 0) { acc[4 * i + 0] = v0; acc[4 * i + 1] = v1; acc[4 * i + 2] = v2; acc[4 * i + 3] = v3; }
             else {
                 acc[4 * i + 0] = __fadd_rn(acc[4 * i + 0], v0); acc[4 * i + 1] = __fadd_rn(acc[4 * i + 1], v1);
                 acc[4 * i + 2] = __fadd_rn(acc[4 * i + 2], v2); acc[4 * i + 3] = __fadd_rn(acc[4 * i + 3], v3);
             }
         }
     }
-    // 16 partial sums x 32 lanes -> one total per row (each on two lanes). The chunk's rows were stored pre-permuted by
-    // this lane's bits (transpose_codes_kernel), so every lane keeps acc[r] and sends acc[r + half]: no selects.
-#pragma unroll
-    for (int r = 0; r < 8; r++) acc[r] = __fadd_rn(acc[r], __shfl_xor_sync(0xffffffffu, acc[r + 8], 16));
-#pragma unroll
-    for (int r = 0; r < 4; r++) acc[r] = __fadd_rn(acc[r], __shfl_xor_sync(0xffffffffu, acc[r + 4], 8));
-#pragma unroll
-    for (int r = 0; r < 2; r++) acc[r] = __fadd_rn(acc[r], __shfl_xor_sync(0xffffffffu, acc[r + 2], 4));
-    acc[0] = __fadd_rn(acc[0], __shfl_xor_sync(0xffffffffu, acc[1], 2));
-    return __fadd_rn(acc[0], __shfl_xor_sync(0xffffffffu, acc[0], 1));
 }
 
-// NJ = ceil(M/32) 16-byte loads per lane and block. grid = (chunks, queries).
-template <int NJ>
+// 16 partial sums x 16 lanes -> one row total per lane (row l16 of the half-warp's block). The chunk's rows were stored
+// pre-permuted by this lane's bits (transpose_codes_kernel: acc[a] is row a ^ l16), so every lane keeps acc[r] and sends
+// acc[r + half]: 15 shuffles per 32 rows, no selects.
+__device__ __forceinline__ float half_warp_transpose_sum(float (&acc)[16]) {
+#pragma unroll
+    for (int r = 0; r < 8; r++) acc[r] = __fadd_rn(acc[r], __shfl_xor_sync(0xffffffffu, acc[r + 8], 8));
+#pragma unroll
+    for (int r = 0; r < 4; r++) acc[r] = __fadd_rn(acc[r], __shfl_xor_sync(0xffffffffu, acc[r + 4], 4));
+#pragma unroll
+    for (int r = 0; r < 2; r++) acc[r] = __fadd_rn(acc[r], __shfl_xor_sync(0xffffffffu, acc[r + 2], 2));
+    return __fadd_rn(acc[0], __shfl_xor_sync(0xffffffffu, acc[1], 1));
+}
+
+// NQ = ceil(M/64) LUT groups = quads per lane and block. grid = (chunks, queries).
+template <int NQ>
 __global__ void __launch_bounds__(AF_NT, 1)
-adc_scan_fast_kernel(const uint4* __restrict__ codesT, int64_t n, int M, const float* __restrict__ lutg, int groups, int R2, int cap,
+adc_scan_fast_kernel(const uint4* __restrict__ codesT, int64_t n, int M, const float* __restrict__ lutg, int R2, int cap,
                      int64_t blocks_per_chunk, uint64_t* __restrict__ out_keys, uint32_t* __restrict__ out_rows) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    float* lut = reinterpret_cast<float*>(smem_raw);                                  // [groups][256][64]
-    uint64_t* buf = reinterpret_cast<uint64_t*>(smem_raw + (size_t)groups * 65536);   // [cap] candidate keys
+    float* lut = reinterpret_cast<float*>(smem_raw);                                  // [NQ][256][64]
+    uint64_t* buf = reinterpret_cast<uint64_t*>(smem_raw + (size_t)NQ * 65536);       // [cap] candidate keys
     __shared__ int s_cnt;
     __shared__ float s_tau;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, h = lane >> 4, l16 = lane & 15;
     const int q = blockIdx.y, chunk = blockIdx.x, nchunks = gridDim.x;
     {
-        const float4* src = reinterpret_cast<const float4*>(lutg + (size_t)q * groups * 16384);
+        const float4* src = reinterpret_cast<const float4*>(lutg + (size_t)q * NQ * 16384);
         float4* dst = reinterpret_cast<float4*>(lut);
-        for (int i = tid; i < groups * 4096; i += AF_NT) dst[i] = __ldg(src + i);
+        for (int i = tid; i < NQ * 4096; i += AF_NT) dst[i] = __ldg(src + i);
     }
     for (int i = tid; i < cap; i += AF_NT) buf[i] = KEY_MAX;
     if (tid == 0) { s_cnt = 0; s_tau = __int_as_float(0x7f800000); }
     __syncthreads();
     const int64_t nblk = (n + 15) >> 4;
     const int64_t b0 = (int64_t)chunk * blocks_per_chunk, b1 = min(nblk, b0 + blocks_per_chunk);
-    // lane constants: byte offset of (group, m & 63) for each j; the code byte is permuted into byte 1 (c * 256)
-    uint32_t lbase[NJ];
+    // lane constants: byte offset of (m & 63) inside a group for each jj; the code byte is permuted into byte 1 (c * 256)
+    uint32_t lbase[4];
+    int offl[4];          // last group: chunk offsets relative to pe (even jj) / po (odd jj), clamped to subspace M - 1
 #pragma unroll
-    for (int j = 0; j < NJ; j++) lbase[j] = ((uint32_t)(j >> 1) << 16) | (uint32_t)((lane + 32 * (j & 1)) * 4);
+    for (int jj = 0; jj < 4; jj++) {
+        const int ml = l16 + 16 * (jj ^ h);
+        lbase[jj] = (uint32_t)(ml * 4);
+        offl[jj] = min(64 * (NQ - 1) + ml, M - 1) - (l16 + 16 * ((jj & 1) ^ h));
+    }
     const unsigned char* lutb = reinterpret_cast<const unsigned char*>(lut);
-    const int row_of_lane = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
 
     // block indices relative to the chunk start (32-bit); rows of the chunk that exist: nrel
     const int nb = (int)(b1 - b0);
     const int nrel = (int)min((int64_t)nb << 4, n - (b0 << 4));
-    const int lastoff = min(lane + 32 * (NJ - 1), M - 1) - lane;
-    const int64_t bstride = (int64_t)AF_WARPS * M;
-    const uint4* bp = codesT + (b0 + min(warp, nb - 1)) * M + lane;     // this lane's chunk of this warp's current block
-    uint4 va[NJ], vb[NJ];
-    load_block<NJ>(bp, lastoff, va);
-    auto advance = [&](int next_blk) { if (next_blk < nb) bp += bstride; };   // clamp: past the end, re-read the last block
-    auto report = [&](float d, int blk) {
-        const int row = (blk << 4) + row_of_lane;
-        if (!(lane & 1) && row < nrel && d < s_tau) {
+    const uint4* base_e = codesT + b0 * M + l16 + 16 * h;          // this lane's even-jj chunks of block 0 of the chunk
+    const uint4* base_o = codesT + b0 * M + l16 + 16 * (1 - h);
+    auto block_off = [&](int pair) { return (int64_t)(min(2 * pair + h, nb - 1) * M); };   // < 2^31: nb * M uint4s per chunk
+    uint4 va[4], vb[4];
+    float acc[16];
+    auto report = [&](float d, int pair) {
+        const int row = ((2 * pair + h) << 4) + l16;
+        if (row < nrel && d < s_tau) {
             const int slot = atomicAdd(&s_cnt, 1);
             buf[slot] = ((uint64_t)f2ord(d) << 32) | (uint32_t)((b0 << 4) + row);
         }
     };
-    for (int sb = 0; sb < nb; sb += AF_WARPS * AF_K) {
+    const int npairs = (nb + 1) >> 1;
+    int64_t o = block_off(warp);
+    load_quad<NQ>(base_e + o, base_o + o, 0, offl, va);
+    for (int sp = 0; sp < npairs; sp += AF_WARPS * AF_K) {
 #pragma unroll 1
         for (int kk = 0; kk < AF_K; kk += 2) {
-            const int blk = sb + kk * AF_WARPS + warp;
-            advance(blk + AF_WARPS);
-            load_block<NJ>(bp, lastoff, vb);                           // next block in flight while this one is gathered
-            report(block_distance<NJ>(va, lbase, lutb), blk);
-            advance(blk + 2 * AF_WARPS);
-            load_block<NJ>(bp, lastoff, va);
-            report(block_distance<NJ>(vb, lbase, lutb), blk + AF_WARPS);
+            // two block pairs = 2 NQ quads, alternating between the two register buffers; the next quad is always in flight
+            const int pair = sp + kk * AF_WARPS + warp;
+#pragma unroll
+            for (int t = 0; t < 2 * NQ; t++) {
+                const int g = t % NQ, pr = t / NQ;                        // compile-time after unrolling
+                const int gn = (t + 1) % NQ, prn = (t + 1) / NQ;          // the quad to prefetch (prn == 2: first of the next iteration)
+                if (gn == 0) o = block_off(pair + prn * AF_WARPS);
+                if (t & 1) load_quad<NQ>(base_e + o, base_o + o, gn, offl, va); else load_quad<NQ>(base_e + o, base_o + o, gn, offl, vb);
+                const unsigned char* lg = lutb + g * 65536;
+                if (t & 1) { if (g == 0) gather_quad<true>(vb, lbase, lg, acc); else gather_quad<false>(vb, lbase, lg, acc); }
+                else       { if (g == 0) gather_quad<true>(va, lbase, lg, acc); else gather_quad<false>(va, lbase, lg, acc); }
+                if (g == NQ - 1) report(half_warp_transpose_sum(acc), pair + pr * AF_WARPS);
+            }
         }
         __syncthreads();
         if (s_cnt > cap - AF_SPAN) {                      // uniform: s_cnt only changes between barriers
@@ -236,7 +256,7 @@ int launch_adc_scan_fast(const uint8_t* d_codesT, const uint8_t* d_codes, int64_
                          uint64_t* d_keys, uint32_t* d_rows, int* d_flag, cudaStream_t st) {
     if (!adc_fast_supported(M, R)) return 1;
     const int R2 = adc_fast_r2(R);
-    const int groups = (M + 63) / 64, nj = (M + 31) / 32;
+    const int groups = (M + 63) / 64;
     const int cap = next_pow2(R2 + AF_SPAN);
     const size_t smem = (size_t)groups * 65536 + (size_t)cap * 8;
     if (smem > 226 * 1024) return 1;
@@ -245,19 +265,16 @@ int launch_adc_scan_fast(const uint8_t* d_codesT, const uint8_t* d_codes, int64_
     dim3 grid(nchunks, nq);
     uint64_t* mk = nchunks > 1 ? d_keys_tmp + (size_t)nq * nchunks * R2 : d_keys_tmp;
     uint32_t* mr = nchunks > 1 ? d_rows_tmp + (size_t)nq * nchunks * R2 : d_rows_tmp;
-#define AF_LAUNCH(NJ)                                                                                                        \
+#define AF_LAUNCH(NQ)                                                                                                        \
     do {                                                                                                                     \
-        cudaFuncSetAttribute(adc_scan_fast_kernel<NJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);              \
-        adc_scan_fast_kernel<NJ><<<grid, AF_NT, smem, st>>>(reinterpret_cast<const uint4*>(d_codesT), n, M, d_lutg, groups, R2, cap, bpc, \
+        cudaFuncSetAttribute(adc_scan_fast_kernel<NQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);              \
+        adc_scan_fast_kernel<NQ><<<grid, AF_NT, smem, st>>>(reinterpret_cast<const uint4*>(d_codesT), n, M, d_lutg, R2, cap, bpc, \
                                                             d_keys_tmp, d_rows_tmp);                                          \
     } while (0)
-    switch (nj) {
+    switch (groups) {
         case 1: AF_LAUNCH(1); break;
         case 2: AF_LAUNCH(2); break;
-        case 3: AF_LAUNCH(3); break;
-        case 4: AF_LAUNCH(4); break;
-        case 5: AF_LAUNCH(5); break;
-        default: AF_LAUNCH(6); break;
+        default: AF_LAUNCH(3); break;
     }
 #undef AF_LAUNCH
     if (nchunks > 1) launch_merge_keys(d_keys_tmp, d_rows_tmp, nq, nchunks, R2, mk, mr, st);
