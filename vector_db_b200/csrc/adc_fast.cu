@@ -25,7 +25,9 @@
 
 #define AF_NT 512
 #define AF_WARPS (AF_NT / 32)
+#ifndef AF_K
 #define AF_K 4                                  // pairs of 16-row blocks per warp between barriers (even)
+#endif
 #define AF_SPAN (32 * AF_WARPS * AF_K)          // rows per super-iteration (= max insertions between barriers)
 
 // ---- codes [n][M] -> codesT [ceil(n/16)][M][16]; rows past n are code 0 (never reported: row < n is checked).

@@ -435,14 +435,70 @@ __device__ __forceinline__ void mma_bf16_16816(float (&c)[4], uint32_t a0, uint3
 }
 // sqh: the query rounded to bf16, zero padded, in shared memory ([tstride/2] elements). All threads of the CTA call.
 // FULL: the row is a whole number of 16-block stages (tstride % 256 == 0, e.g. 512-d bf16): no per-load bound checks
+// 32-byte global load (sm_100: LDG.E.256): lanes c = 0..3 of a row group cover one whole 128-byte line of their row, so a
+// warp-wide load touches 8 lines for 128 useful bytes each (the 16-byte form: 8 lines for 64 bytes each). Rows are read once
+// per query: no L1 allocation (the 2 x 111 KB of shared memory leave ~30 KB of L1). Measured on C3 (1184 queries):
+// 16-byte loads + L2 prefetch 11.95 ms, 32-byte loads 11.42, 32-byte loads without the prefetch 11.00, + no_allocate 10.74.
+struct U8 { uint4 lo, hi; };
+__device__ __forceinline__ U8 ld256_nc(const unsigned char* p) {
+    U8 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r.lo.x), "=r"(r.lo.y), "=r"(r.lo.z), "=r"(r.lo.w), "=r"(r.hi.x), "=r"(r.hi.y), "=r"(r.hi.z), "=r"(r.hi.w) : "l"(p));
+    return r;
+}
+#ifndef HN_NL
+#define HN_NL 2           // 32-byte loads per lane, row and stage (a stage = HN_NL * 128 bytes of each row)
+#endif
+// Whole-stage rows (tstride % 256 == 0, e.g. 512-d bf16): 32-byte loads, no bound checks. One stage in flight per warp and
+// NO register double buffer: measured on C3 (1184 queries, B200) the double-buffered forms were all slower — 16-byte loads +
+// prefetched next stage 11.95 ms, 32-byte loads + next stage 10.74 (the second buffer spills at the 128-register cap), a
+// four-deep register ring 14.9, a non-inlined copy with its own registers 12.4 — than load / multiply / load: 9.78 ms.
+// The phase is not short of loads in flight (16 warps x 4 KB per SM); it is short of registers.
+__device__ __forceinline__ void fresh_distances_mma_full(const HnswSearchParams& p, const uint4* __restrict__ sqh, float qnorm, float qq,
+                                                         const int* __restrict__ fnode, int nf, const FreshOut& o) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int g = lane >> 2, c = lane & 3;
+    const unsigned char* tb = reinterpret_cast<const unsigned char*>(p.tbase);
+    const int tstride = p.tstride;
+    const int nst = tstride / (HN_NL * 128);
+    for (int tile = warp; tile * 16 < nf; tile += HN_WARPS) {
+        const int j0 = tile * 16 + g, j1 = j0 + 8;
+        const int n0 = fnode[min(j0, nf - 1)], n1 = fnode[min(j1, nf - 1)];
+        const unsigned char* r0 = tb + (size_t)n0 * tstride + c * 32;
+        const unsigned char* r1 = tb + (size_t)n1 * tstride + c * 32;
+        const float sc0 = (c == 0 && j0 < nf) ? row_scalar<true>(p, n0) : 0.0f;
+        const float sc1 = (c == 0 && j1 < nf) ? row_scalar<true>(p, n1) : 0.0f;
+        float acc0[4] = {0.0f, 0.0f, 0.0f, 0.0f}, acc1[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+        for (int st = 0; st < nst; st++) {
+            U8 A0[HN_NL], A1[HN_NL];
+#pragma unroll
+            for (int i = 0; i < HN_NL; i++) { A0[i] = ld256_nc(r0 + (st * HN_NL + i) * 128); A1[i] = ld256_nc(r1 + (st * HN_NL + i) * 128); }
+#pragma unroll
+            for (int i = 0; i < HN_NL; i++) {
+                const uint4* qp = sqh + ((st * HN_NL + i) * 8 + c * 2);       // the query's 32 bytes at the same k positions
+                const uint4 qa = qp[0], qb = qp[1];
+                mma_bf16_16816(acc0, A0[i].lo.x, A1[i].lo.x, A0[i].lo.y, A1[i].lo.y, qa.x, qa.y);
+                mma_bf16_16816(acc1, A0[i].lo.z, A1[i].lo.z, A0[i].lo.w, A1[i].lo.w, qa.z, qa.w);
+                mma_bf16_16816(acc0, A0[i].hi.x, A1[i].hi.x, A0[i].hi.y, A1[i].hi.y, qb.x, qb.y);
+                mma_bf16_16816(acc1, A0[i].hi.z, A1[i].hi.z, A0[i].hi.w, A1[i].hi.w, qb.z, qb.w);
+            }
+        }
+        if (c == 0) {
+            if (j0 < nf) accept_key(o, finish_dist<true>(p, acc0[0] + acc1[0], sc0, qnorm, qq), n0);
+            if (j1 < nf) accept_key(o, finish_dist<true>(p, acc0[2] + acc1[2], sc1, qnorm, qq), n1);
+        }
+    }
+}
+// sqh: the query rounded to bf16, zero padded, in shared memory ([tstride/2] elements). All threads of the CTA call.
 template <bool FULL>
 __device__ __forceinline__ void fresh_distances_mma(const HnswSearchParams& p, const uint4* __restrict__ sqh, float qnorm, float qq,
                                                     const int* __restrict__ fnode, int nf, const FreshOut& o) {
+    if constexpr (FULL) { fresh_distances_mma_full(p, sqh, qnorm, qq, fnode, nf, o); return; }
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int g = lane >> 2, c = lane & 3;
+    const unsigned char* tb = reinterpret_cast<const unsigned char*>(p.tbase);
     const int nblk = p.tstride >> 4;                  // 16-byte column blocks per row
     const int nst = (nblk + 15) >> 4;                 // stages of 16 blocks (4 per lane)
-    const unsigned char* tb = reinterpret_cast<const unsigned char*>(p.tbase);
     for (int tile = warp; tile * 16 < nf; tile += HN_WARPS) {
         const int j0 = tile * 16 + g, j1 = j0 + 8;
         const int n0 = fnode[min(j0, nf - 1)], n1 = fnode[min(j1, nf - 1)];
@@ -479,7 +535,31 @@ __device__ __forceinline__ void fresh_distances_mma(const HnswSearchParams& p, c
     }
 }
 
-#define HN_FCAP 2048      // side buffer capacity (entries)
+// Bitonic sort of 64 keys held two per lane (element 2 * lane + r): stride 1 is in-register, larger strides are shuffles.
+__device__ __forceinline__ uint64_t shfl_xor_u64(uint64_t v, int m) {
+    const uint32_t lo = __shfl_xor_sync(0xffffffffu, (uint32_t)v, m), hi = __shfl_xor_sync(0xffffffffu, (uint32_t)(v >> 32), m);
+    return ((uint64_t)hi << 32) | lo;
+}
+__device__ __forceinline__ void warp_sort64(uint64_t& e0, uint64_t& e1, int lane) {
+#pragma unroll
+    for (int k = 2; k <= 64; k <<= 1) {
+        const bool up = ((2 * lane) & k) == 0;             // ascending sub-sequence (k = 64: always)
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            if (j == 1) {
+                if ((e0 > e1) == up) { const uint64_t t = e0; e0 = e1; e1 = t; }
+            } else {
+                const int m = j >> 1;                      // partner element i ^ j lives in lane ^ (j / 2), same r
+                const uint64_t p0 = shfl_xor_u64(e0, m), p1 = shfl_xor_u64(e1, m);
+                const bool keepmin = ((lane & m) == 0) == up;
+                e0 = keepmin ? (e0 < p0 ? e0 : p0) : (e0 > p0 ? e0 : p0);
+                e1 = keepmin ? (e1 < p1 ? e1 : p1) : (e1 > p1 ? e1 : p1);
+            }
+        }
+    }
+}
+
+#define HN_FCAP 2048      // side buffer capacity (entries); must stay >= HN_FMAX (a round's accepted keys always fit)
 #define HN_FTH 1024       // side buffer is folded into the main array when it holds more than this
 
 struct HnswShared {
@@ -494,6 +574,7 @@ struct HnswShared {
     float dentry, qnorm, qq;
     long long ph[8];      // profile: per-phase cycles of thread 0
     long long tp;
+    long long hist[4];    // profile: rounds with > 256 accepted keys, sum of accepted keys, rounds with 129..256, sort cycles of the first
 };
 
 // Collect the indices of the first (up to) B unexpanded entries of the sorted array a[from..lim) into cand[] (sorted
@@ -605,6 +686,7 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
     const int uncertain_ok = B == 1 ? 1 : 128;    // side-buffer entries tolerated while candidates come from the array's tail
     unsigned long long evals = 0, exps = 0;
     if (tid < 8) S.ph[tid] = 0;
+    if (tid < 4) S.hist[tid] = 0;
 #define HN_MARK(slot) do { if (p.profile && tid == 0) { const long long now_ = clock64(); S.ph[slot] += now_ - S.tp; S.tp = now_; } } while (0)
 
     for (int q = blockIdx.x; q < p.nq; q += gridDim.x) {
@@ -748,7 +830,8 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
                         if (fresh) {
                             fnode[basec + __popc(m & ((1u << lane) - 1u))] = nb[t];
                             const unsigned char* rp = tb + (size_t)nb[t] * p.tstride;
-                            for (int l = 0; l < lines; l++) asm volatile("prefetch.global.L2 [%0];" ::"l"(rp + ((size_t)l << 7)));
+                            if (p.prefetch)
+                                for (int l = 0; l < lines; l++) asm volatile("prefetch.global.L2 [%0];" ::"l"(rp + ((size_t)l << 7)));
                         }
                     }
                 }
@@ -773,41 +856,51 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
             HN_MARK(3);
             int r0 = newfrontF;
             if (nacc > 0) {
-                // C4. sort the accepted keys (rank sort: no barriers inside; bitonic for the rare large case)
-                if (nacc <= HN_NT) {
-                    // 2-D rank sort: key j = tid % n2 is compared with the slice `part` = tid / n2 of all keys; partial
-                    // ranks meet in shared memory. No barrier inside the counting loop, all 8 warps busy.
-                    int* rank = fnode;                                 // fnode is idle after the distance phase
-                    int n2 = 32; while (n2 < nacc) n2 <<= 1;
-                    const int parts = HN_NT / n2, j = tid & (n2 - 1), part = tid / n2;
-                    if (tid < nacc) rank[tid] = 0;
-                    __syncthreads();
-                    uint64_t kj = KEY_MAX;
-                    if (j < nacc) {
-                        kj = fkey[j];
-                        const int per = (nacc + parts - 1) / parts;
-                        const int i0 = part * per, i1 = min(nacc, i0 + per);
-                        int r = 0;
-                        for (int i = i0; i < i1; i++) r += fkey[i] < kj ? 1 : 0;
-                        if (r) atomicAdd(&rank[j], r);
+                const uint64_t* skeys = fkey;      // the round's accepted keys, sorted
+                int* rr = fnode;                   // rank scratch of the merges
+                // C4. sort the accepted keys. Up to 512: every warp sorts one 64-key chunk of the append list in registers
+                //     (bitonic network over shuffles, no barrier), then each key finds its slot in the union by adding its
+                //     lower bounds in the other chunks (<= 7 binary searches of 6 steps); two barriers in all. The block-wide
+                //     bitonic sort (45 barrier steps for 512 keys) is left for larger rounds.
+                if (nacc <= 8 * 64) {
+                    const int c0 = warp * 64;
+                    if (c0 < nacc) {
+                        uint64_t e0 = c0 + 2 * lane < nacc ? fkey[c0 + 2 * lane] : KEY_MAX;
+                        uint64_t e1 = c0 + 2 * lane + 1 < nacc ? fkey[c0 + 2 * lane + 1] : KEY_MAX;
+                        warp_sort64(e0, e1, lane);
+                        fkey[c0 + 2 * lane] = e0; fkey[c0 + 2 * lane + 1] = e1;
                     }
                     __syncthreads();
-                    if (part == 0 && j < nacc) fkey[rank[j]] = kj;
+                    uint64_t* sk = reinterpret_cast<uint64_t*>(fnode);          // fnode is idle after the distance phase
+                    const int nch = (nacc + 63) >> 6;
+                    for (int idx = tid; idx < nacc; idx += HN_NT) {
+                        const uint64_t key = fkey[idx];
+                        const int mych = idx >> 6;
+                        int r = idx & 63;
+                        for (int ch = 0; ch < nch; ch++)
+                            if (ch != mych) r += lower_bound_u64(fkey + ch * 64, min(64, nacc - ch * 64), key);
+                        sk[r] = key;
+                    }
                     __syncthreads();
+                    skeys = sk; rr = reinterpret_cast<int*>(fkey);              // the append list is dead from here on
                 } else {
                     int fp2 = 1; while (fp2 < nacc) fp2 <<= 1;
                     for (int i = nacc + tid; i < fp2; i += HN_NT) fkey[i] = KEY_MAX;
                     block_bitonic_sort<false>(fkey, nullptr, fp2);
                 }
+                if (p.profile && tid == 0) {
+                    S.hist[1] += nacc;
+                    if (nacc > HN_NT) { S.hist[0]++; S.hist[3] += clock64() - S.tp; } else if (nacc > 128) S.hist[2]++;
+                }
                 HN_MARK(4);
                 // C5. merge into the side buffer (other half), by ranking; a buffer that would overflow is folded first
                 if (countF + nacc > HN_FCAP) {
                     if (tid == 0) { S.frontP = newfrontP; S.frontF = newfrontF; }
-                    fold_side_buffer(P, F0, S, ef, fnode);
+                    fold_side_buffer(P, F0, S, ef, rr);
                     newfrontP = S.frontP; newfrontF = 0; r0 = 0; countF = 0;
                 }
-                merge_ranked(Fc, countF, fkey, nacc, Fn, HN_FCAP, fnode);
-                r0 = fnode[0];
+                merge_ranked(Fc, countF, skeys, nacc, Fn, HN_FCAP, rr);
+                r0 = rr[0];
             }
             if (tid == 0) {
                 if (nacc > 0) { S.countF = countF + nacc; S.whichF ^= 1; }
@@ -855,7 +948,10 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
     if (p.counters && tid == 0) {
         if (evals) atomicAdd(&p.counters[0], evals);
         if (exps) atomicAdd(&p.counters[1], exps);
-        if (p.profile) for (int i = 0; i < 8; i++) atomicAdd(&p.counters[2 + i], (unsigned long long)S.ph[i]);
+        if (p.profile) {
+            for (int i = 0; i < 8; i++) atomicAdd(&p.counters[2 + i], (unsigned long long)S.ph[i]);
+            for (int i = 0; i < 4; i++) atomicAdd(&p.counters[12 + i], (unsigned long long)S.hist[i]);
+        }
     }
 }
 

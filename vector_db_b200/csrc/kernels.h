@@ -53,6 +53,7 @@ struct HnswSearchParams {
     int batch;                // candidates expanded per round (1 = the Java order)
     int profile;              // accumulate thread-0 cycle counters per phase into counters[2..9]
     int visited_in_smem;
+    int prefetch;             // pull fresh rows towards L2 as soon as they are discovered (traversal copy well beyond L2 only)
 };
 int launch_hnsw_search(const HnswSearchParams& p, int grid, cudaStream_t st);
 size_t hnsw_search_smem_bytes(const HnswSearchParams& p);

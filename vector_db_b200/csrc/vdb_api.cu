@@ -442,6 +442,10 @@ static int search_graph(vdb_index* x, const float* d_q, int64_t nq, int k, int32
     p.batch = std::max(1, std::min(p.batch, hnsw_max_batch(p.deg)));
     p.profile = getenv("VDB_HNSW_PROFILE") ? 1 : 0;
     if (const char* eb = getenv("VDB_HNSW_BATCH")) p.batch = std::max(1, std::min(atoi(eb), hnsw_max_batch(p.deg)));
+    // L2 prefetch of discovered rows: a gain only when the traversal copy is well beyond the 126 MB L2 (rows come from HBM);
+    // on a mostly L2-resident copy (C3: 102 MB) the prefetch instructions cost more L1TEX wavefronts than they save latency
+    p.prefetch = (size_t)x->n * (size_t)p.tstride > ((size_t)192 << 20) ? 1 : 0;
+    if (const char* ep = getenv("VDB_HNSW_PREFETCH")) p.prefetch = atoi(ep) ? 1 : 0;
     p.visited_in_smem = 1;
     size_t smem = hnsw_search_smem_bytes(p);
     if (smem > 112 * 1024) { p.visited_in_smem = 0; smem = hnsw_search_smem_bytes(p); }
@@ -664,6 +668,8 @@ extern "C" int vdb_get_stats(vdb_index* x, vdb_stats* out) {
     if (getenv("VDB_HNSW_PROFILE"))
         fprintf(stderr, "[vdb hnsw profile] cycles: setup %llu select %llu gather %llu dist %llu sort %llu merge %llu final %llu | rounds %llu\n",
                 c[2], c[3], c[4], c[5], c[6], c[7], c[8], c[9]);
+    if (getenv("VDB_HNSW_PROFILE"))
+        fprintf(stderr, "[vdb hnsw profile] accepted keys: sum %llu | rounds with > 256: %llu (sort cycles %llu), with 129..256: %llu\n", c[13], c[12], c[15], c[14]);
     x->stats.dist_evals = (int64_t)c[0]; x->stats.expansions = (int64_t)c[1];
     x->stats.flat_certified = (int64_t)c[10]; x->stats.flat_fallback = (int64_t)c[11];
     *out = x->stats;
