@@ -535,28 +535,66 @@ __device__ __forceinline__ void fresh_distances_mma(const HnswSearchParams& p, c
     }
 }
 
-// Bitonic sort of 64 keys held two per lane (element 2 * lane + r): stride 1 is in-register, larger strides are shuffles.
+// Bitonic sort of 32 * PER keys held PER per lane (element PER * lane + r) entirely in registers: strides below PER are
+// in-register compare-exchanges, larger strides are shuffles with lane ^ (stride / PER). No barrier, no shared memory.
 __device__ __forceinline__ uint64_t shfl_xor_u64(uint64_t v, int m) {
     const uint32_t lo = __shfl_xor_sync(0xffffffffu, (uint32_t)v, m), hi = __shfl_xor_sync(0xffffffffu, (uint32_t)(v >> 32), m);
     return ((uint64_t)hi << 32) | lo;
 }
-__device__ __forceinline__ void warp_sort64(uint64_t& e0, uint64_t& e1, int lane) {
+template <int PER>
+__device__ __forceinline__ void warp_sort_regs(uint64_t (&e)[PER], int lane) {
 #pragma unroll
-    for (int k = 2; k <= 64; k <<= 1) {
-        const bool up = ((2 * lane) & k) == 0;             // ascending sub-sequence (k = 64: always)
+    for (int k = 2; k <= 32 * PER; k <<= 1) {
 #pragma unroll
         for (int j = k >> 1; j > 0; j >>= 1) {
-            if (j == 1) {
-                if ((e0 > e1) == up) { const uint64_t t = e0; e0 = e1; e1 = t; }
+            if (j < PER) {
+#pragma unroll
+                for (int r = 0; r < PER; r++) {
+                    if ((r & j) == 0) {
+                        const bool up = k < PER ? ((r & k) == 0) : ((lane & (k / PER)) == 0);
+                        const uint64_t x = e[r], y = e[r | j];
+                        if ((x > y) == up) { e[r] = y; e[r | j] = x; }
+                    }
+                }
             } else {
-                const int m = j >> 1;                      // partner element i ^ j lives in lane ^ (j / 2), same r
-                const uint64_t p0 = shfl_xor_u64(e0, m), p1 = shfl_xor_u64(e1, m);
-                const bool keepmin = ((lane & m) == 0) == up;
-                e0 = keepmin ? (e0 < p0 ? e0 : p0) : (e0 > p0 ? e0 : p0);
-                e1 = keepmin ? (e1 < p1 ? e1 : p1) : (e1 > p1 ? e1 : p1);
+                const int m = j / PER;
+                const bool keepmin = ((lane & m) == 0) == ((lane & (k / PER)) == 0);
+#pragma unroll
+                for (int r = 0; r < PER; r++) {
+                    const uint64_t q = shfl_xor_u64(e[r], m);
+                    e[r] = keepmin ? (e[r] < q ? e[r] : q) : (e[r] > q ? e[r] : q);
+                }
             }
         }
     }
+}
+// Sort keys[0..n) (n <= 8 * 32 * PER) into out[0..n): warp w sorts chunk w of 32 * PER keys in registers, then every key finds
+// its slot in the union by adding its lower bounds in the other chunks. Two barriers. out must not alias keys; keys is
+// clobbered (padded with KEY_MAX up to the end of the last chunk).
+template <int PER>
+__device__ __forceinline__ void chunk_sort_merge(uint64_t* __restrict__ keys, int n, uint64_t* __restrict__ out) {
+    constexpr int CH = 32 * PER;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int c0 = warp * CH;
+    if (c0 < n) {
+        uint64_t e[PER];
+#pragma unroll
+        for (int r = 0; r < PER; r++) e[r] = c0 + PER * lane + r < n ? keys[c0 + PER * lane + r] : KEY_MAX;
+        warp_sort_regs<PER>(e, lane);
+#pragma unroll
+        for (int r = 0; r < PER; r++) keys[c0 + PER * lane + r] = e[r];
+    }
+    __syncthreads();
+    const int nch = (n + CH - 1) / CH;
+    for (int idx = tid; idx < n; idx += HN_NT) {
+        const uint64_t key = keys[idx];
+        const int mych = idx / CH;
+        int r = idx - mych * CH;
+        for (int ch = 0; ch < nch; ch++)
+            if (ch != mych) r += lower_bound_u64(keys + ch * CH, min(CH, n - ch * CH), key);
+        out[r] = key;
+    }
+    __syncthreads();
 }
 
 #define HN_FCAP 2048      // side buffer capacity (entries); must stay >= HN_FMAX (a round's accepted keys always fit)
@@ -814,6 +852,10 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
                             if (j < p.deg) nb[t] = __ldg(p.adj + (size_t)S.sel[s] * p.deg + j);
                         }
                     }
+                    // visited test-and-set of all eight lists first (independent shared-memory atomics, pipelined), then ONE
+                    // append reservation for the warp instead of one per list
+                    unsigned m[8];
+                    int tot = 0;
 #pragma unroll
                     for (int t = 0; t < 8; t++) {
                         bool fresh = false;
@@ -822,17 +864,23 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
                             const uint32_t old = atomicOr(&vis[nb[t] >> 5], bit);
                             fresh = !(old & bit);
                         }
-                        const unsigned m = __ballot_sync(0xffffffffu, fresh);
-                        if (m == 0u) continue;
-                        int basec = 0;
-                        if (lane == 0) basec = atomicAdd(&S.nfresh, __popc(m));
-                        basec = __shfl_sync(0xffffffffu, basec, 0);
-                        if (fresh) {
-                            fnode[basec + __popc(m & ((1u << lane) - 1u))] = nb[t];
-                            const unsigned char* rp = tb + (size_t)nb[t] * p.tstride;
-                            if (p.prefetch)
+                        m[t] = __ballot_sync(0xffffffffu, fresh);
+                        tot += __popc(m[t]);
+                    }
+                    if (tot == 0) continue;
+                    int basec = 0;
+                    if (lane == 0) basec = atomicAdd(&S.nfresh, tot);
+                    basec = __shfl_sync(0xffffffffu, basec, 0);
+#pragma unroll
+                    for (int t = 0; t < 8; t++) {
+                        if ((m[t] >> lane) & 1u) {
+                            fnode[basec + __popc(m[t] & ((1u << lane) - 1u))] = nb[t];
+                            if (p.prefetch) {
+                                const unsigned char* rp = tb + (size_t)nb[t] * p.tstride;
                                 for (int l = 0; l < lines; l++) asm volatile("prefetch.global.L2 [%0];" ::"l"(rp + ((size_t)l << 7)));
+                            }
                         }
+                        basec += __popc(m[t]);
                     }
                 }
             }
@@ -858,35 +906,25 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
             if (nacc > 0) {
                 const uint64_t* skeys = fkey;      // the round's accepted keys, sorted
                 int* rr = fnode;                   // rank scratch of the merges
-                // C4. sort the accepted keys. Up to 512: every warp sorts one 64-key chunk of the append list in registers
-                //     (bitonic network over shuffles, no barrier), then each key finds its slot in the union by adding its
-                //     lower bounds in the other chunks (<= 7 binary searches of 6 steps); two barriers in all. The block-wide
-                //     bitonic sort (45 barrier steps for 512 keys) is left for larger rounds.
-                if (nacc <= 8 * 64) {
-                    const int c0 = warp * 64;
-                    if (c0 < nacc) {
-                        uint64_t e0 = c0 + 2 * lane < nacc ? fkey[c0 + 2 * lane] : KEY_MAX;
-                        uint64_t e1 = c0 + 2 * lane + 1 < nacc ? fkey[c0 + 2 * lane + 1] : KEY_MAX;
-                        warp_sort64(e0, e1, lane);
-                        fkey[c0 + 2 * lane] = e0; fkey[c0 + 2 * lane + 1] = e1;
-                    }
-                    __syncthreads();
-                    uint64_t* sk = reinterpret_cast<uint64_t*>(fnode);          // fnode is idle after the distance phase
-                    const int nch = (nacc + 63) >> 6;
-                    for (int idx = tid; idx < nacc; idx += HN_NT) {
-                        const uint64_t key = fkey[idx];
-                        const int mych = idx >> 6;
-                        int r = idx & 63;
-                        for (int ch = 0; ch < nch; ch++)
-                            if (ch != mych) r += lower_bound_u64(fkey + ch * 64, min(64, nacc - ch * 64), key);
-                        sk[r] = key;
-                    }
-                    __syncthreads();
+                // C4. sort the accepted keys: every warp sorts one chunk of the append list in registers (bitonic network over
+                //     shuffles, no barrier), then each key finds its slot in the union by adding its lower bounds in the other
+                //     chunks (<= 7 binary searches); two barriers in all, against 45..66 barrier steps of a block-wide bitonic
+                //     sort (which took 80 % of this phase in the 16 % of the rounds with more than 256 keys).
+                bool direct = false;
+                if (nacc <= 8 * 128) {
+                    uint64_t* sk = reinterpret_cast<uint64_t*>(fnode);          // fnode (idle after the distance phase) holds 1024 keys
+                    if (nacc <= 8 * 64) chunk_sort_merge<2>(fkey, nacc, sk); else chunk_sort_merge<4>(fkey, nacc, sk);
                     skeys = sk; rr = reinterpret_cast<int*>(fkey);              // the append list is dead from here on
                 } else {
-                    int fp2 = 1; while (fp2 < nacc) fp2 <<= 1;
-                    for (int i = nacc + tid; i < fp2; i += HN_NT) fkey[i] = KEY_MAX;
-                    block_bitonic_sort<false>(fkey, nullptr, fp2);
+                    // a large round (the early rounds accept everything): empty the side buffer first, then sort straight into
+                    // its idle half, which becomes the new side buffer without a merge (nacc <= HN_FMAX = HN_FCAP)
+                    if (countF > 0) {
+                        if (tid == 0) { S.frontP = newfrontP; S.frontF = newfrontF; }
+                        fold_side_buffer(P, F0, S, ef, fnode);
+                        newfrontP = S.frontP; newfrontF = 0; countF = 0;
+                    }
+                    chunk_sort_merge<8>(fkey, nacc, Fn);
+                    direct = true;
                 }
                 if (p.profile && tid == 0) {
                     S.hist[1] += nacc;
@@ -894,13 +932,16 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
                 }
                 HN_MARK(4);
                 // C5. merge into the side buffer (other half), by ranking; a buffer that would overflow is folded first
-                if (countF + nacc > HN_FCAP) {
-                    if (tid == 0) { S.frontP = newfrontP; S.frontF = newfrontF; }
-                    fold_side_buffer(P, F0, S, ef, rr);
-                    newfrontP = S.frontP; newfrontF = 0; r0 = 0; countF = 0;
+                if (direct) r0 = 0;
+                else {
+                    if (countF + nacc > HN_FCAP) {
+                        if (tid == 0) { S.frontP = newfrontP; S.frontF = newfrontF; }
+                        fold_side_buffer(P, F0, S, ef, rr);
+                        newfrontP = S.frontP; newfrontF = 0; r0 = 0; countF = 0;
+                    }
+                    merge_ranked(Fc, countF, skeys, nacc, Fn, HN_FCAP, rr);
+                    r0 = rr[0];
                 }
-                merge_ranked(Fc, countF, skeys, nacc, Fn, HN_FCAP, rr);
-                r0 = rr[0];
             }
             if (tid == 0) {
                 if (nacc > 0) { S.countF = countF + nacc; S.whichF ^= 1; }
