@@ -89,6 +89,13 @@ __device__ __forceinline__ void load_quad(const uint4* __restrict__ pe, const ui
     }
 }
 
+// two fp32 additions in one instruction (sm_100 FADD2, add.rn.f32x2): the same round-to-nearest sums as two FADDs, half the
+// issue slots — the scan is co-limited by issue (PRMT + LDS + add per gathered value) and the shared-memory crossbar
+__device__ __forceinline__ void fadd2(float& a0, float& a1, float b0, float b1) {
+    asm("{\n\t.reg .b64 ra, rb;\n\tmov.b64 ra, {%0, %1};\n\tmov.b64 rb, {%2, %3};\n\tadd.rn.f32x2 ra, ra, rb;\n\tmov.b64 {%0, %1}, ra;\n\t}"
+        : "+f"(a0), "+f"(a1) : "f"(b0), "f"(b1));
+}
+
 // 64 gathers of one quad into the 16 per-lane partial sums; the group's 64 KB image is an immediate offset of the LDS
 template <bool FIRST>
 __device__ __forceinline__ void gather_quad(const uint4 (&v)[4], const uint32_t (&lbase)[4], const unsigned char* __restrict__ lutg, float (&acc)[16]) {
@@ -102,10 +109,7 @@ __device__ __forceinline__ void gather_quad(const uint4 (&v)[4], const uint32_t 
             const float v2 = *reinterpret_cast<const float*>(lutg + __byte_perm(w[i], lbase[jj], 0x7624));
             const float v3 = *reinterpret_cast<const float*>(lutg + __byte_perm(w[i], lbase[jj], 0x7634));
             if (FIRST && jj == 0) { acc[4 * i + 0] = v0; acc[4 * i + 1] = v1; acc[4 * i + 2] = v2; acc[4 * i + 3] = v3; }
-            else {
-                acc[4 * i + 0] = __fadd_rn(acc[4 * i + 0], v0); acc[4 * i + 1] = __fadd_rn(acc[4 * i + 1], v1);
-                acc[4 * i + 2] = __fadd_rn(acc[4 * i + 2], v2); acc[4 * i + 3] = __fadd_rn(acc[4 * i + 3], v3);
-            }
+            else { fadd2(acc[4 * i + 0], acc[4 * i + 1], v0, v1); fadd2(acc[4 * i + 2], acc[4 * i + 3], v2, v3); }
         }
     }
 }
@@ -115,11 +119,12 @@ __device__ __forceinline__ void gather_quad(const uint4 (&v)[4], const uint32_t 
 // acc[r + half]: 15 shuffles per 32 rows, no selects.
 __device__ __forceinline__ float half_warp_transpose_sum(float (&acc)[16]) {
 #pragma unroll
-    for (int r = 0; r < 8; r++) acc[r] = __fadd_rn(acc[r], __shfl_xor_sync(0xffffffffu, acc[r + 8], 8));
+    for (int r = 0; r < 8; r += 2)
+        fadd2(acc[r], acc[r + 1], __shfl_xor_sync(0xffffffffu, acc[r + 8], 8), __shfl_xor_sync(0xffffffffu, acc[r + 9], 8));
 #pragma unroll
-    for (int r = 0; r < 4; r++) acc[r] = __fadd_rn(acc[r], __shfl_xor_sync(0xffffffffu, acc[r + 4], 4));
-#pragma unroll
-    for (int r = 0; r < 2; r++) acc[r] = __fadd_rn(acc[r], __shfl_xor_sync(0xffffffffu, acc[r + 2], 2));
+    for (int r = 0; r < 4; r += 2)
+        fadd2(acc[r], acc[r + 1], __shfl_xor_sync(0xffffffffu, acc[r + 4], 4), __shfl_xor_sync(0xffffffffu, acc[r + 5], 4));
+    fadd2(acc[0], acc[1], __shfl_xor_sync(0xffffffffu, acc[2], 2), __shfl_xor_sync(0xffffffffu, acc[3], 2));
     return __fadd_rn(acc[0], __shfl_xor_sync(0xffffffffu, acc[1], 1));
 }
 
