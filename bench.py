@@ -29,9 +29,9 @@ N_BASE, DIM, PQ_M, NQ, K = 100_000, 512, 64, 4096, 10
 METRIC = "QPS @ Recall@10>=0.95, 512-d HNSW+PQ"
 # dram__bytes_read+write per launch of the dominant kernel from the committed ncu --set full capture (profiles/), or None
 # dram__bytes_read.sum + dram__bytes_write.sum of hnsw_search_kernel<bf16> from the `ncu --set full` capture summarised in
-# profiles/r1_hnsw_v4_ncu_full.txt (592-query launch on the same 100k x 512 index: 2.0086 GB read + 0.0371 GB written), per query;
+# profiles/r1_hnsw_v6_ncu_full.txt (592-query launch on the same 100k x 512 index: 1.8100 GB read + 0.0066 GB written), per query;
 # the roofline object scales it to the queries of one bench launch.
-NCU_DRAM_BYTES_PER_QUERY = (2.008609e9 + 37.144320e6) / 592
+NCU_DRAM_BYTES_PER_QUERY = (1.809985e9 + 6.616320e6) / 592
 WORKLOAD = "C3: 100k x 512-d uniform[-1,1), HNSW+PQ recommendedConfig(512)=(64,8), batch 4096 queries, k=10"
 
 
@@ -504,7 +504,7 @@ def run_b200(args, rank, world):
     ach = alg_bytes / (kms * 1e-3) / 1e9
     roofline = {"kernel": "hnsw_search_kernel<bf16>", "bound": "hbm", "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s",
                 "frac": ach / pk["hbm_gbs"], "traffic": NCU_DRAM_BYTES_PER_QUERY * nq if n == N_BASE else None,
-                "traffic_source": "profiles/r1_hnsw_v4_ncu_full.txt (ncu --set full, 592-query launch, scaled per query)", "peak_source": pk_kind + " (MEASURED_PEAKS.json hbm_gbs, burst copy)",
+                "traffic_source": "profiles/r1_hnsw_v6_ncu_full.txt (ncu --set full, 592-query launch, scaled per query)", "peak_source": pk_kind + " (MEASURED_PEAKS.json hbm_gbs, burst copy)",
                 "algorithmic_bytes_per_launch": alg_bytes, "bytes_per_unit": "V*%d (bf16 row) + E*128 (neighbour list) per query" % row_bytes,
                 "dist_evals_per_query": V / nq, "expansions_per_query": E / nq, "kernel_ms": kms,
                 "note": "random 1 KB row gathers over a %.0f MB bf16 copy that is mostly L2-resident: the kernel is bound by the "

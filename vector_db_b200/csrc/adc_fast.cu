@@ -30,26 +30,29 @@
 #endif
 #define AF_SPAN (32 * AF_WARPS * AF_K)          // rows per super-iteration (= max insertions between barriers)
 
-// ---- codes [n][M] -> codesT [ceil(n/16)][M][16]; rows past n are code 0 (never reported: row < n is checked).
+// ---- codes [n][M] -> codesT [ceil(n/16)][Mp][16], Mp = M rounded up to 8 chunks so that every 16-row block starts on a
+//      128-byte line (M = 125: 2048-byte blocks instead of 2000; the half-warp's 256-byte runs then touch 2 lines, not 3);
+//      rows past n and chunks past M are code 0 (never reported / gathered from all-zero LUT columns).
 //      The 16-byte chunk of subspace m is read by lane (m & 15) of a half-warp; inside the chunk byte a holds row
 //      a ^ (m & 15), the order that lane's butterfly wants (see the scan kernel): no selects in the transposing reduction. ----
-__global__ void transpose_codes_kernel(const uint8_t* __restrict__ codes, int64_t n, int M, int64_t row0, uint8_t* __restrict__ codesT) {
-    // one thread per output byte of blocks covering rows [row0, n)
+__global__ void transpose_codes_kernel(const uint8_t* __restrict__ codes, int64_t n, int M, int Mp, int64_t row0, uint8_t* __restrict__ codesT) {
+    // one thread per output byte of blocks covering rows [row0, n); chunks m in [M, Mp) are zero padding
     const int64_t b0 = row0 >> 4;
-    const int64_t total = (((n + 15) >> 4) - b0) * (int64_t)M * 16;
+    const int64_t total = (((n + 15) >> 4) - b0) * (int64_t)Mp * 16;
     for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
         const int64_t bm = t >> 4;
-        const int m = (int)(bm % M);
+        const int m = (int)(bm % Mp);
         const int r = (int)(t & 15) ^ (m & 15);
-        const int64_t row = ((b0 + bm / M) << 4) + r;
-        codesT[(b0 * M << 4) + t] = row < n ? codes[row * M + m] : (uint8_t)0;
+        const int64_t row = ((b0 + bm / Mp) << 4) + r;
+        codesT[(b0 * Mp << 4) + t] = (row < n && m < M) ? codes[row * M + m] : (uint8_t)0;
     }
 }
 void launch_transpose_codes(const uint8_t* d_codes, int64_t n, int M, int64_t row0, uint8_t* d_codesT, cudaStream_t st) {
-    const int64_t total = (((n + 15) >> 4) - (row0 >> 4)) * (int64_t)M * 16;
+    const int Mp = adc_mpad(M);
+    const int64_t total = (((n + 15) >> 4) - (row0 >> 4)) * (int64_t)Mp * 16;
     if (total <= 0) return;
     const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 32);
-    transpose_codes_kernel<<<blocks, 256, 0, st>>>(d_codes, n, M, row0, d_codesT);
+    transpose_codes_kernel<<<blocks, 256, 0, st>>>(d_codes, n, M, Mp, row0, d_codesT);
 }
 
 // ---- LUT image in the gather layout: lutg[q][(m>>6)*16384 + c*64 + (m&63)] (floats) ----
@@ -275,7 +278,7 @@ int launch_adc_scan_fast(const uint8_t* d_codesT, const uint8_t* d_codes, int64_
 #define AF_LAUNCH(NQ)                                                                                                        \
     do {                                                                                                                     \
         cudaFuncSetAttribute(adc_scan_fast_kernel<NQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);              \
-        adc_scan_fast_kernel<NQ><<<grid, AF_NT, smem, st>>>(reinterpret_cast<const uint4*>(d_codesT), n, M, d_lutg, R2, cap, bpc, \
+        adc_scan_fast_kernel<NQ><<<grid, AF_NT, smem, st>>>(reinterpret_cast<const uint4*>(d_codesT), n, adc_mpad(M), d_lutg, R2, cap, bpc, \
                                                             d_keys_tmp, d_rows_tmp);                                          \
     } while (0)
     switch (groups) {

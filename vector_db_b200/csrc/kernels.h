@@ -8,6 +8,7 @@ void launch_adc_scan_topr(const uint8_t* d_codes, int64_t n, int M, const float*
                           int id_offset, int R, int nchunks, uint64_t* d_keys_tmp, uint32_t* d_rows_tmp, uint64_t* d_keys,
                           uint32_t* d_rows, cudaStream_t st, const int* only_flag = nullptr);
 // adc_fast.cu
+static inline int adc_mpad(int M) { return (M + 7) & ~7; }    // chunks per 16-row block of the transposed code layout
 void launch_transpose_codes(const uint8_t* d_codes, int64_t n, int M, int64_t row0, uint8_t* d_codesT, cudaStream_t st);
 void launch_lut_to_gather_layout(const float* d_lut, int nq, int M, float* d_lutg, cudaStream_t st);
 int adc_fast_supported(int M, int R);

@@ -188,7 +188,7 @@ static int encode_pending(vdb_index* x) {
         // scan layout: 16-row blocks, subspace-major (adc_fast.cu); blocks that were complete stay, the rest is rewritten
         if (x->n_codesT > x->n_coded) x->n_codesT = x->n_coded;
         const int64_t row0 = x->n_codesT & ~(int64_t)15;
-        VDB_TRY(x->d_codesT.ensure((size_t)((x->n_dev + 15) / 16) * M * 16, (size_t)(row0 / 16) * M * 16, x->stream));
+        VDB_TRY(x->d_codesT.ensure((size_t)((x->n_dev + 15) / 16) * adc_mpad(M) * 16, (size_t)(row0 / 16) * adc_mpad(M) * 16, x->stream));
         launch_transpose_codes(x->d_codes.p, x->n_dev, M, row0, x->d_codesT.p, x->stream);
         VDB_CUDA(cudaGetLastError());
         x->n_codesT = x->n_dev;

@@ -77,7 +77,7 @@ struct vdb_index {
     DevBuf<float> d_base, d_norms, d_cb;
     DevBuf<int32_t> d_ids, d_adj;
     DevBuf<uint8_t> d_codes;
-    DevBuf<uint8_t> d_codesT;       // PQ index: codes transposed in 16-row blocks [ceil(n/16)][M][16] (adc_fast.cu)
+    DevBuf<uint8_t> d_codesT;       // PQ index: codes transposed in 16-row blocks [ceil(n/16)][ceil8(M)][16] (adc_fast.cu)
     int64_t n_codesT = 0;           // rows present in d_codesT
     DevBuf<unsigned char> d_trav;   // traversal rows (bf16 or padded fp32), rebuilt when rows are uploaded
     int64_t n_trav = 0;
