@@ -367,6 +367,31 @@ def test_hnswpq_traversal_vs_oracle(v, po, n, dim, M, rebuilt, mode):
     g.close()
 
 
+@pytest.mark.parametrize("store", [1, 0], ids=["fp32rows", "bf16rows"])
+def test_hnswpq_large_rounds(v, po, store):
+    """64 candidates per round on a beam of 1500: the first rounds accept up to 2048 keys at once, which drives the
+    accepted-key sort through every chunk size (2 / 4 / 8 keys per lane) and the sort-straight-into-the-side-buffer path.
+    The walk order differs from Java's pop order near the beam boundary, so ids are compared loosely; everything else
+    (exact re-scored distances, order, no duplicates, recall) is held to the usual bar."""
+    n, dim, M, nq, k = 10000, 128, 16, 200, 10
+    X, Q = po.synth(42, n, dim), po.synth(43, nq, dim)
+    o = po.OracleHnsw(po.KIND_HNSWPQ, dim, 2 * n, pq_m=M, level_seed=5)
+    o.add_batch(X)
+    g = v.NativeHnswPqIndex(dim, 2 * n, pqM=M, trav_store=store, trav_batch=64)
+    g.addBatch(None, X)
+    _load_oracle_state(g, o, o.codes())
+    ids, d = g.searchBatch(Q, k)
+    jid, jd, _ = o.search(Q, k, nthreads=8)
+    assert (ids >= 0).all() and all(len(set(r)) == k for r in ids.tolist())
+    assert (np.diff(d, axis=1) >= 0).all()
+    assert (ids == jid).mean() >= 0.97
+    same = ids == jid
+    assert np.array_equal(bits(d[same]), bits(jd[same]))
+    gt, _ = po.flat_search(X, Q, k, nthreads=8)
+    assert abs(recall(ids, gt) - recall(jid, gt)) <= 0.005
+    g.close()
+
+
 @pytest.mark.parametrize("mode", [STRICT, FAST], ids=["strict", "fast"])
 def test_hnsw_cosine_traversal_vs_oracle(v, po, mode):
     n, dim, nq, k = 10000, 128, 200, 10
