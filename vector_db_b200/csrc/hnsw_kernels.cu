@@ -20,6 +20,7 @@
 //     bf16 copy (half the bytes; L2-resident at 100k x 512-d). Either way the answer is re-scored from the fp32 rows in
 //     the reference's sequential order (HnswPqIndex.java:646-664), so returned distances are bit-identical to Java's.
 #include <cuda_bf16.h>
+#include <cuda_fp8.h>
 
 #include "kernels.h"
 
@@ -446,6 +447,80 @@ __device__ __forceinline__ U8 ld256_nc(const unsigned char* p) {
                  : "=r"(r.lo.x), "=r"(r.lo.y), "=r"(r.lo.z), "=r"(r.lo.w), "=r"(r.hi.x), "=r"(r.hi.y), "=r"(r.hi.z), "=r"(r.hi.w) : "l"(p));
     return r;
 }
+// ---- fp8 (e4m3) traversal rows, opt-in (trav_store = 2): half the row bytes of the bf16 copy. A row is stored as
+//      e4m3(x * s_row) with a per-row power-of-two scale (exact to undo); the query as e4m3 with a per-query power-of-two
+//      scale, by default in TWO terms (hi + lo / 16: the query side then adds no rounding worth the name; HN_FP8_LO = 0
+//      keeps the hi term only and halves the MMAs); m16n8k32 MMAs accumulate in fp32.
+#ifndef HN_FP8_LO
+#define HN_FP8_LO 1
+#endif
+__device__ __forceinline__ float fp8_pow2_scale(float maxabs) {       // largest element -> [120, 240] (e4m3 max finite: 448)
+    if (!(maxabs > 0.0f)) return 1.0f;
+    const int e = min(100, max(-100, (int)floorf(log2f(240.0f / maxabs))));
+    return exp2f((float)e);
+}
+__device__ __forceinline__ float fp8_to_float(__nv_fp8_storage_t h) {
+    return __half2float(__half(__nv_cvt_fp8_to_halfraw(h, __NV_E4M3)));
+}
+__device__ __forceinline__ void mma_e4m3_16832(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.f32.e4m3.e4m3.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+// sq8: the query's hi term in bytes [0, dim), its lo term (x 16) in [dim, 2 dim). qinv = 1 / query scale.
+// One 32-byte load per lane and row = 32 k-values = four MMAs per query term; NL loads per row in flight.
+template <int NL>
+__device__ __forceinline__ void fresh_distances_fp8(const HnswSearchParams& p, const unsigned char* __restrict__ sq8, float qnorm, float qq, float qinv,
+                                                    const int* __restrict__ fnode, int nf, const FreshOut& o) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int g = lane >> 2, c = lane & 3;
+    const unsigned char* tb = reinterpret_cast<const unsigned char*>(p.tbase);
+    const int tstride = p.tstride;
+    const int nst = tstride / (NL * 128);
+    for (int tile = warp; tile * 16 < nf; tile += HN_WARPS) {
+        const int j0 = tile * 16 + g, j1 = j0 + 8;
+        const int n0 = fnode[min(j0, nf - 1)], n1 = fnode[min(j1, nf - 1)];
+        const unsigned char* r0 = tb + (size_t)n0 * tstride + c * 32;
+        const unsigned char* r1 = tb + (size_t)n1 * tstride + c * 32;
+        float sc0 = 0.0f, sc1 = 0.0f, is0 = 0.0f, is1 = 0.0f;
+        if (c == 0 && j0 < nf) { sc0 = p.metric == 1 ? __ldg(p.norms + n0) : __ldg(p.tnorm + n0); is0 = __ldg(p.tscale + n0); }
+        if (c == 0 && j1 < nf) { sc1 = p.metric == 1 ? __ldg(p.norms + n1) : __ldg(p.tnorm + n1); is1 = __ldg(p.tscale + n1); }
+        float ah[4] = {0.0f, 0.0f, 0.0f, 0.0f}, al[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+        for (int st = 0; st < nst; st++) {
+            U8 A0[NL], A1[NL];
+#pragma unroll
+            for (int i = 0; i < NL; i++) { A0[i] = ld256_nc(r0 + (st * NL + i) * 128); A1[i] = ld256_nc(r1 + (st * NL + i) * 128); }
+#pragma unroll
+            for (int i = 0; i < NL; i++) {
+                const uint4* qh = reinterpret_cast<const uint4*>(sq8 + (st * NL + i) * 128 + c * 32);
+                const uint4 h0 = qh[0], h1 = qh[1];
+                mma_e4m3_16832(ah, A0[i].lo.x, A1[i].lo.x, A0[i].lo.y, A1[i].lo.y, h0.x, h0.y);
+                mma_e4m3_16832(ah, A0[i].lo.z, A1[i].lo.z, A0[i].lo.w, A1[i].lo.w, h0.z, h0.w);
+                mma_e4m3_16832(ah, A0[i].hi.x, A1[i].hi.x, A0[i].hi.y, A1[i].hi.y, h1.x, h1.y);
+                mma_e4m3_16832(ah, A0[i].hi.z, A1[i].hi.z, A0[i].hi.w, A1[i].hi.w, h1.z, h1.w);
+#if HN_FP8_LO
+                const uint4* ql = reinterpret_cast<const uint4*>(sq8 + tstride + (st * NL + i) * 128 + c * 32);
+                const uint4 l0 = ql[0], l1 = ql[1];
+                mma_e4m3_16832(al, A0[i].lo.x, A1[i].lo.x, A0[i].lo.y, A1[i].lo.y, l0.x, l0.y);
+                mma_e4m3_16832(al, A0[i].lo.z, A1[i].lo.z, A0[i].lo.w, A1[i].lo.w, l0.z, l0.w);
+                mma_e4m3_16832(al, A0[i].hi.x, A1[i].hi.x, A0[i].hi.y, A1[i].hi.y, l1.x, l1.y);
+                mma_e4m3_16832(al, A0[i].hi.z, A1[i].hi.z, A0[i].hi.w, A1[i].hi.w, l1.z, l1.w);
+#endif
+            }
+        }
+        if (c == 0) {
+            if (j0 < nf) {
+                const float dot = __fmul_rn(__fmaf_rn(al[0], 0.0625f, ah[0]), __fmul_rn(is0, qinv));
+                accept_key(o, p.metric == 1 ? cosine_dist_from_dot(dot, sc0, qnorm) : fmaxf(__fmaf_rn(-2.0f, dot, __fadd_rn(qq, sc0)), 0.0f), n0);
+            }
+            if (j1 < nf) {
+                const float dot = __fmul_rn(__fmaf_rn(al[2], 0.0625f, ah[2]), __fmul_rn(is1, qinv));
+                accept_key(o, p.metric == 1 ? cosine_dist_from_dot(dot, sc1, qnorm) : fmaxf(__fmaf_rn(-2.0f, dot, __fadd_rn(qq, sc1)), 0.0f), n1);
+            }
+        }
+    }
+}
+
 #ifndef HN_NL
 #define HN_NL 2           // 32-byte loads per lane, row and stage (a stage = HN_NL * 128 bytes of each row)
 #endif
@@ -609,7 +684,7 @@ struct HnswShared {
     int frontP, frontF;   // every entry below these indices carries the expanded bit
     int whichF;           // which of the two side-buffer halves is current
     int evicted;          // Java: first results.poll() has happened (furthest is live)
-    float dentry, qnorm, qq;
+    float dentry, qnorm, qq, qinv;
     long long ph[8];      // profile: per-phase cycles of thread 0
     long long tp;
     long long hist[4];    // profile: rounds with > 256 accepted keys, sum of accepted keys, rounds with 129..256, sort cycles of the first
@@ -704,7 +779,7 @@ __device__ __forceinline__ void fold_side_buffer(uint64_t* P, const uint64_t* F0
 }
 
 // FULL (bf16 rows only): rows are a whole number of 256-byte MMA stages, the distance loop needs no bound checks
-template <bool BF16, bool FULL>
+template <bool BF16, bool FULL, int FP8 = 0>      // FP8: 0 = off, else the number of 32-byte loads per row and stage (1 or 2)
 __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int qpad = (p.dim + 7) & ~7;
@@ -743,7 +818,35 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
             __syncthreads();
             if (tid == 0) S.qnorm = norm_java(sq, p.dim);
         } else if (tid == 0) S.qnorm = 0.0f;
-        if (BF16) {
+        if (FP8) {
+            unsigned char* q8 = reinterpret_cast<unsigned char*>(sqh);      // [dim] hi term, [dim] lo term (x 16)
+            if (warp == 1) {
+                float mx = 0.0f;
+                for (int i = lane; i < p.dim; i += 32) mx = fmaxf(mx, fabsf(sq[i]));
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+                if (lane == 0) S.qinv = __fdiv_rn(1.0f, fp8_pow2_scale(mx));
+            }
+            __syncthreads();
+            const float qinv_ = S.qinv, qs = __fdiv_rn(1.0f, qinv_);
+            for (int i = tid; i < p.dim; i += HN_NT) {
+                const float v = __fmul_rn(sq[i], qs);
+                const __nv_fp8_storage_t h = __nv_cvt_float_to_fp8(v, __NV_SATFINITE, __NV_E4M3);
+                const __nv_fp8_storage_t l = HN_FP8_LO ? __nv_cvt_float_to_fp8(__fmul_rn(__fsub_rn(v, fp8_to_float(h)), 16.0f), __NV_SATFINITE, __NV_E4M3)
+                                                       : (__nv_fp8_storage_t)0;
+                q8[i] = h; q8[p.dim + i] = l;
+            }
+            __syncthreads();
+            if (warp == 1) {                                           // ||q||^2 of the REPRESENTED query (hi + lo / 16) / scale
+                float a = 0.0f;
+                for (int i = lane; i < p.dim; i += 32) {
+                    const float v = __fmul_rn(__fmaf_rn(fp8_to_float(q8[p.dim + i]), 0.0625f, fp8_to_float(q8[i])), qinv_);
+                    a = __fmaf_rn(v, v, a);
+                }
+                a = warp_tree_sum(a);
+                if (lane == 0) S.qq = a;
+            }
+        } else if (BF16) {
             __nv_bfloat16* h = reinterpret_cast<__nv_bfloat16*>(sqh);
             for (int i = tid; i < qpad; i += HN_NT) h[i] = __float2bfloat16_rn(sq[i]);
             __syncthreads();
@@ -770,7 +873,8 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
         __syncthreads();
         {
             FreshOut o{fkey, &S.nacc, false, 0.0f};
-            if (BF16) fresh_distances_mma<FULL>(p, sqh, qnorm, qq, fnode, 1, o);
+            if constexpr (FP8 != 0) fresh_distances_fp8<FP8 ? FP8 : 1>(p, reinterpret_cast<const unsigned char*>(sqh), qnorm, qq, S.qinv, fnode, 1, o);
+            else if (BF16) fresh_distances_mma<FULL>(p, sqh, qnorm, qq, fnode, 1, o);
             else fresh_dispatch<false>(p, sq, qnorm, qq, fnode, 1, o);
         }
         __syncthreads();
@@ -896,7 +1000,8 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
                 float bound = 0.0f;
                 if (full) bound = (variant == 0 || evicted) ? pool_dist(P[ef - 1]) : S.dentry;
                 FreshOut o{fkey, &S.nacc, full, bound};
-                if (BF16) fresh_distances_mma<FULL>(p, sqh, qnorm, qq, fnode, nf, o);
+                if constexpr (FP8 != 0) fresh_distances_fp8<FP8 ? FP8 : 1>(p, reinterpret_cast<const unsigned char*>(sqh), qnorm, qq, S.qinv, fnode, nf, o);
+                else if (BF16) fresh_distances_mma<FULL>(p, sqh, qnorm, qq, fnode, nf, o);
                 else fresh_dispatch<false>(p, sq, qnorm, qq, fnode, nf, o);
             }
             __syncthreads();
@@ -966,7 +1071,7 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
         }
         {
             int rs = 32;
-            while (rs < p.k + 22) rs <<= 1;
+            while (rs < (FP8 ? 4 * p.k + 24 : p.k + 22)) rs <<= 1;      // fp8 rows: a deeper exact re-score absorbs the coarser ranking
             if (rs > HN_FMAX) rs = HN_FMAX;
             const int have = min(S.countP, rs);
             for (int j = tid; j < rs; j += HN_NT) {
@@ -1007,7 +1112,16 @@ int launch_hnsw_search(const HnswSearchParams& p, int grid, cudaStream_t st) {
     if (p.k + 22 > HN_FMAX || p.deg > 64 || p.batch < 1 || p.batch * p.deg > HN_FMAX || p.batch > HN_MAXB) return 1;
     if ((p.tstride & 15) != 0) return 1;
     const size_t smem = hnsw_search_smem_bytes(p);
-    if (p.tstore == 1 && (p.tstride & 255) == 0) {
+    if (p.tstore == 2) {
+        if ((p.tstride & 127) != 0 || 4 * p.k + 24 > HN_FMAX) return 1;
+        if ((p.tstride & 255) == 0) {
+            if (cudaFuncSetAttribute(hnsw_search_kernel<true, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 2;
+            hnsw_search_kernel<true, false, 2><<<grid, HN_NT, smem, st>>>(p);
+        } else {
+            if (cudaFuncSetAttribute(hnsw_search_kernel<true, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 2;
+            hnsw_search_kernel<true, false, 1><<<grid, HN_NT, smem, st>>>(p);
+        }
+    } else if (p.tstore == 1 && (p.tstride & 255) == 0) {
         if (cudaFuncSetAttribute(hnsw_search_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 2;
         hnsw_search_kernel<true, true><<<grid, HN_NT, smem, st>>>(p);
     } else if (p.tstore == 1) {
@@ -1022,17 +1136,34 @@ int launch_hnsw_search(const HnswSearchParams& p, int grid, cudaStream_t st) {
 
 // ---- traversal copy of the base rows: zero-padded to a multiple of 8 elements, fp32 or bf16 (round to nearest even);
 //      tnorm[r] = sum of squares of the STORED (rounded) row, sequential fp32 — used by the bf16 sq-L2 form ----
-__global__ void make_traversal_rows_kernel(const float* __restrict__ base, int64_t n, int dim, int dpad, int bf16, void* __restrict__ out,
-                                           float* __restrict__ tnorm) {
+__global__ void make_traversal_rows_kernel(const float* __restrict__ base, int64_t n, int dim, int dpad, int mode, void* __restrict__ out,
+                                           float* __restrict__ tnorm, float* __restrict__ tscale) {
     const int lane = threadIdx.x & 31;
     const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     for (int64_t r = warp; r < n; r += nwarps) {
         float a = 0.0f;
+        if (mode == 2) {
+            // fp8 e4m3 with a per-row power-of-two scale (largest element lands in [120, 240]); row stride = dim bytes
+            float mx = 0.0f;
+            for (int c = lane; c < dim; c += 32) mx = fmaxf(mx, fabsf(base[r * dim + c]));
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+            const float sc = fp8_pow2_scale(mx), inv = __fdiv_rn(1.0f, sc);
+            for (int c = lane; c < dim; c += 32) {
+                const __nv_fp8_storage_t h = __nv_cvt_float_to_fp8(__fmul_rn(base[r * dim + c], sc), __NV_SATFINITE, __NV_E4M3);
+                reinterpret_cast<unsigned char*>(out)[r * dim + c] = h;
+                const float sv = __fmul_rn(fp8_to_float(h), inv);
+                a = __fmaf_rn(sv, sv, a);
+            }
+            a = warp_tree_sum(a);
+            if (lane == 0) { tnorm[r] = a; tscale[r] = inv; }
+            continue;
+        }
         for (int c = lane; c < dpad; c += 32) {
             const float v = c < dim ? base[r * dim + c] : 0.0f;
             float sv = v;
-            if (bf16) { const __nv_bfloat16 h = __float2bfloat16_rn(v); reinterpret_cast<__nv_bfloat16*>(out)[r * dpad + c] = h; sv = __bfloat162float(h); }
+            if (mode == 1) { const __nv_bfloat16 h = __float2bfloat16_rn(v); reinterpret_cast<__nv_bfloat16*>(out)[r * dpad + c] = h; sv = __bfloat162float(h); }
             else reinterpret_cast<float*>(out)[r * dpad + c] = v;
             a = __fmaf_rn(sv, sv, a);
         }
@@ -1040,8 +1171,9 @@ __global__ void make_traversal_rows_kernel(const float* __restrict__ base, int64
         if (lane == 0 && tnorm) tnorm[r] = a;
     }
 }
-void launch_make_traversal_rows(const float* d_base, int64_t n, int dim, int dpad, int bf16, void* d_out, float* d_tnorm, cudaStream_t st) {
+void launch_make_traversal_rows(const float* d_base, int64_t n, int dim, int dpad, int mode, void* d_out, float* d_tnorm, float* d_tscale,
+                                cudaStream_t st) {
     if (n <= 0) return;
     int blocks = (int)std::min<int64_t>((n + 7) / 8, 148 * 16);
-    make_traversal_rows_kernel<<<blocks, 256, 0, st>>>(d_base, n, dim, dpad, bf16, d_out, d_tnorm);
+    make_traversal_rows_kernel<<<blocks, 256, 0, st>>>(d_base, n, dim, dpad, mode, d_out, d_tnorm, d_tscale);
 }

@@ -33,7 +33,8 @@ void launch_distance(const float* d_a, const float* d_b, int64_t n, int dim, int
 // hnsw_kernels.cu
 struct HnswSearchParams {
     const float* base;        // [n][dim]; normalised rows for cosine (exact re-score, greedy descent)
-    const float* tnorm;       // [n] squared norm of the stored traversal row (bf16 sq-L2 form)
+    const float* tnorm;       // [n] squared norm of the stored traversal row (bf16 / fp8 sq-L2 form)
+    const float* tscale;      // [n] fp8 rows: 1 / (power-of-two scale the row was stored with)
     const void* tbase;        // traversal rows [n][tstride bytes]: fp32 or bf16, zero-padded to a multiple of 8 elements
     const float* norms;       // [n] Java norm of the stored row (cosine), else nullptr
     const int32_t* ids;       // [n] external ids
@@ -50,7 +51,7 @@ struct HnswSearchParams {
     int metric;               // 0 sq-L2 (HnswPqIndex), 1 cosine (HnswIndex)
     int variant;              // 0 searchLayerWithSize, 1 HnswPqIndex.searchLayer, 2 HnswIndex.searchLayer
     int ef, k, nq;
-    int tstride, tstore;      // bytes per traversal row (multiple of 16); 0 = fp32, 1 = bf16
+    int tstride, tstore;      // bytes per traversal row (multiple of 16); 0 = fp32, 1 = bf16, 2 = fp8 e4m3
     int batch;                // candidates expanded per round (1 = the Java order)
     int profile;              // accumulate thread-0 cycle counters per phase into counters[2..9]
     int visited_in_smem;
@@ -59,7 +60,8 @@ struct HnswSearchParams {
 int launch_hnsw_search(const HnswSearchParams& p, int grid, cudaStream_t st);
 size_t hnsw_search_smem_bytes(const HnswSearchParams& p);
 int hnsw_max_batch(int deg);
-void launch_make_traversal_rows(const float* d_base, int64_t n, int dim, int dpad, int bf16, void* d_out, float* d_tnorm, cudaStream_t st);
+void launch_make_traversal_rows(const float* d_base, int64_t n, int dim, int dpad, int mode /* 0 fp32, 1 bf16, 2 fp8 */, void* d_out, float* d_tnorm,
+                                float* d_tscale, cudaStream_t st);
 
 // flat_kernels.cu
 void launch_flat_search_exact(const float* d_base, const float* d_norms, const int32_t* d_ids, int id_offset, int64_t n, int dim,

@@ -75,6 +75,7 @@ extern "C" int vdb_create(const vdb_config* cfg, vdb_index** out) {
     if (uses_pq) c.metric = VDB_METRIC_SQL2;
     if (c.index_type == VDB_INDEX_HNSW || c.index_type == VDB_INDEX_HNSW_PQ) {
         if (c.hnsw_m > 64) { delete x; FAIL(VDB_ERR_INVALID, "hnsw_m > 64 not supported"); }
+        if (c.trav_store == VDB_TRAV_FP8 && (c.dim % 128) != 0) { delete x; FAIL(VDB_ERR_INVALID, "fp8 traversal rows need dim % 128 == 0"); }
         if (c.ef_construction <= 0) c.ef_construction = c.index_type == VDB_INDEX_HNSW ? 400 : 64;
         if (c.ef_search <= 0) c.ef_search = c.index_type == VDB_INDEX_HNSW ? 400 : 64;
         x->g.init(c.dim, c.hnsw_m, c.max_elements, c.metric, c.level_seed);
@@ -93,7 +94,7 @@ extern "C" int vdb_destroy(vdb_index* x) {
     if (x->stream) cudaStreamSynchronize(x->stream);
     x->d_base.release(); x->d_norms.release(); x->d_cb.release(); x->d_ids.release(); x->d_adj.release(); x->d_codes.release();
     x->d_q.release(); x->d_out_d.release(); x->d_lut.release(); x->d_out_ids.release(); x->d_keys.release(); x->d_keys_tmp.release();
-    x->d_rows.release(); x->d_rows_tmp.release(); x->d_visited.release(); x->d_counters.release(); x->d_trav.release(); x->d_tnorm.release(); x->d_codesT.release(); x->d_lutg.release(); x->d_flag.release();
+    x->d_rows.release(); x->d_rows_tmp.release(); x->d_visited.release(); x->d_counters.release(); x->d_trav.release(); x->d_tnorm.release(); x->d_tscale.release(); x->d_codesT.release(); x->d_lutg.release(); x->d_flag.release();
     x->d_fmirror.release(); x->d_fab.release(); x->d_fcolsum.release(); x->d_fq.release(); x->d_fqf.release(); x->d_fscores.release(); x->d_ftau.release();
     x->d_fqstat.release(); x->d_fcnt.release(); x->d_fcand.release(); x->d_fslab_d.release(); x->d_fslab_i.release();
     x->d_train.release(); x->d_sub.release(); x->d_mind.release(); x->d_asg.release();
@@ -130,15 +131,19 @@ static int upload_rows(vdb_index* x) {
 
 // traversal copy of rows [n_trav, n_dev): zero-padded to 8 elements, bf16 (default) or fp32 (strict mode)
 static inline int trav_dpad(const vdb_index* x) { return (x->cfg.dim + 7) & ~7; }
-static inline int trav_stride(const vdb_index* x) { return trav_dpad(x) * (x->cfg.trav_store == VDB_TRAV_F32 ? 4 : 2); }
+static inline int trav_stride(const vdb_index* x) {
+    return x->cfg.trav_store == VDB_TRAV_FP8 ? x->cfg.dim : trav_dpad(x) * (x->cfg.trav_store == VDB_TRAV_F32 ? 4 : 2);    // fp8: dim % 128 == 0
+}
+static inline int trav_mode(const vdb_index* x) { return x->cfg.trav_store == VDB_TRAV_F32 ? 0 : (x->cfg.trav_store == VDB_TRAV_FP8 ? 2 : 1); }
 static int build_traversal_rows(vdb_index* x) {
     if (x->n_trav >= x->n_dev) return VDB_OK;
     const size_t stride = (size_t)trav_stride(x);
     VDB_TRY(x->d_trav.ensure((size_t)x->n_dev * stride, (size_t)x->n_trav * stride, x->stream));
     VDB_TRY(x->d_tnorm.ensure((size_t)x->n_dev, (size_t)x->n_trav, x->stream));
+    VDB_TRY(x->d_tscale.ensure((size_t)x->n_dev, (size_t)x->n_trav, x->stream));
     launch_make_traversal_rows(x->d_base.p + (size_t)x->n_trav * x->cfg.dim, x->n_dev - x->n_trav, x->cfg.dim, trav_dpad(x),
-                               x->cfg.trav_store == VDB_TRAV_F32 ? 0 : 1, x->d_trav.p + (size_t)x->n_trav * stride,
-                               x->d_tnorm.p + x->n_trav, x->stream);
+                               trav_mode(x), x->d_trav.p + (size_t)x->n_trav * stride,
+                               x->d_tnorm.p + x->n_trav, x->d_tscale.p + x->n_trav, x->stream);
     VDB_CUDA(cudaGetLastError());
     VDB_CUDA(cudaStreamSynchronize(x->stream));
     x->n_trav = x->n_dev;
@@ -437,7 +442,7 @@ static int search_graph(vdb_index* x, const float* d_q, int64_t nq, int k, int32
     } else { p.variant = 2; p.ef = std::max(x->cfg.ef_search, k * 4); }        // HnswIndex.java:347
     p.ef = (int)std::min<int64_t>(p.ef, std::max<int64_t>(x->n, 1));
     p.k = k; p.nq = (int)nq;
-    p.tbase = x->d_trav.p; p.tnorm = x->d_tnorm.p; p.tstride = trav_stride(x); p.tstore = x->cfg.trav_store == VDB_TRAV_F32 ? 0 : 1;
+    p.tbase = x->d_trav.p; p.tnorm = x->d_tnorm.p; p.tscale = x->d_tscale.p; p.tstride = trav_stride(x); p.tstore = trav_mode(x);
     p.batch = x->cfg.trav_batch > 0 ? x->cfg.trav_batch : (p.ef >= 4096 ? 64 : std::max(4, std::min(32, p.ef / 128)));
     p.batch = std::max(1, std::min(p.batch, hnsw_max_batch(p.deg)));
     p.profile = getenv("VDB_HNSW_PROFILE") ? 1 : 0;

@@ -82,6 +82,7 @@ struct vdb_index {
     DevBuf<unsigned char> d_trav;   // traversal rows (bf16 or padded fp32), rebuilt when rows are uploaded
     int64_t n_trav = 0;
     DevBuf<float> d_tnorm;          // squared norms of the traversal rows
+    DevBuf<float> d_tscale;         // fp8 traversal rows: inverse of the per-row scale
     DevBuf<uint16_t> d_fmirror;     // flat index: bf16 mirror [n][dpad] for the tensor-core search (flat_gemm.cu)
     DevBuf<float> d_fab;            // per-row additive term a: approximate score = a + b * (q' . x')
     DevBuf<float> d_fcolsum;        // [dim] column sums, [dim] max squared row norm
