@@ -443,7 +443,9 @@ static int search_graph(vdb_index* x, const float* d_q, int64_t nq, int k, int32
     p.ef = (int)std::min<int64_t>(p.ef, std::max<int64_t>(x->n, 1));
     p.k = k; p.nq = (int)nq;
     p.tbase = x->d_trav.p; p.tnorm = x->d_tnorm.p; p.tscale = x->d_tscale.p; p.tstride = trav_stride(x); p.tstore = trav_mode(x);
-    p.batch = x->cfg.trav_batch > 0 ? x->cfg.trav_batch : (p.ef >= 4096 ? 64 : std::max(4, std::min(32, p.ef / 128)));
+    // candidates expanded per round: ~1.5 % of the beam keeps >= 99 % of the ids equal to the Java pop order (tests) and halves the
+    // per-round bookkeeping of small beams (C1, ef = 1500: 11 -> 23 per round, 4.65 -> 2.9 ms per 1000 queries)
+    p.batch = x->cfg.trav_batch > 0 ? x->cfg.trav_batch : (p.ef >= 4096 ? 64 : std::max(4, std::min(32, p.ef / 64)));
     p.batch = std::max(1, std::min(p.batch, hnsw_max_batch(p.deg)));
     p.profile = getenv("VDB_HNSW_PROFILE") ? 1 : 0;
     if (const char* eb = getenv("VDB_HNSW_BATCH")) p.batch = std::max(1, std::min(atoi(eb), hnsw_max_batch(p.deg)));
