@@ -39,7 +39,7 @@ enum {
     VDB_INDEX_HNSW_PQ = 3  /* Java HnswPqIndex: sq-L2, PQ upper layers, exact layer 0 + rerank (index/HnswPqIndex.java) */
 };
 enum { VDB_METRIC_SQL2 = 0, VDB_METRIC_COSINE = 1 };
-enum { VDB_TRAV_BF16 = 0, VDB_TRAV_F32 = 1, VDB_TRAV_FP8 = 2 };
+enum { VDB_TRAV_BF16 = 0, VDB_TRAV_F32 = 1, VDB_TRAV_FP8 = 2, VDB_TRAV_INT8 = 3 };
 /* fp32 reduction order of the reference implementation being reproduced */
 enum {
     VDB_ARITH_JAVA_SEQ = 0,    /* sequential, mul then add (HnswPqIndex.java:741-750, :343-350) */
@@ -70,7 +70,7 @@ typedef struct vdb_config {
     int32_t id_offset;       /* multi-GPU id-range sharding: this shard holds global rows [id_offset, id_offset+n) */
     int32_t search_ef_cap;   /* HNSW_PQ: cap of the layer-0 beam; 0 = 5000, the constant of HnswPqIndex.java:621 */
     uint64_t level_seed;     /* seeded stand-in for ThreadLocalRandom level draws (HnswPqIndex.java:752-759) */
-    int32_t trav_store;      /* HNSW*: rows read during traversal: 0 = bf16 copy (default), 1 = fp32 (strict order), 2 = fp8 e4m3 with a per-row power-of-two scale (opt-in, dim % 128 == 0) */
+    int32_t trav_store;      /* HNSW*: rows read during traversal: 0 = bf16 copy (default), 1 = fp32 (strict order), 2 = fp8 e4m3 with a per-row power-of-two scale, 3 = int8 with a per-row scale (both opt-in, dim % 128 == 0) */
     int32_t trav_batch;      /* HNSW*: candidates expanded per round: 0 = auto (ef/128 in [4,32]; 64 from ef 4096), 1 = the Java pop order */
     int32_t reserved1;
     int32_t reserved2;

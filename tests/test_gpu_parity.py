@@ -367,28 +367,29 @@ def test_hnswpq_traversal_vs_oracle(v, po, n, dim, M, rebuilt, mode):
     g.close()
 
 
+@pytest.mark.parametrize("store,min_match", [(2, 0.98), (3, 0.99)], ids=["fp8", "int8"])
 @pytest.mark.parametrize("n,dim,M", [(10000, 128, 16), (4000, 512, 64)])
-def test_hnswpq_fp8_traversal_rows(v, po, n, dim, M):
-    """Opt-in trav_store = 2: e4m3 traversal rows with a per-row power-of-two scale. Only the WALK is approximate — the
-    answer is re-scored from the fp32 rows in Java's order — so: Recall@10 within 0.5 pt of the reference algorithm,
-    >= 98 % of the ids equal Java's, distances bit-equal wherever the id is."""
+def test_hnswpq_8bit_traversal_rows(v, po, n, dim, M, store, min_match):
+    """Opt-in trav_store = 2 / 3: e4m3 rows with a per-row power-of-two scale / int8 rows with a per-row scale. Only the
+    WALK is approximate — the answer is re-scored from the fp32 rows in Java's order — so: Recall@10 within 0.5 pt of the
+    reference algorithm, >= 98 % (fp8) / 99 % (int8) of the ids equal Java's, distances bit-equal wherever the id is."""
     nq, k = 200, 10
     X, Q = po.synth(42, n, dim), po.synth(43, nq, dim)
     o = po.OracleHnsw(po.KIND_HNSWPQ, dim, 2 * n, pq_m=M, level_seed=5)
     o.add_batch(X)
-    g = v.NativeHnswPqIndex(dim, 2 * n, pqM=M, trav_store=2)
+    g = v.NativeHnswPqIndex(dim, 2 * n, pqM=M, trav_store=store)
     g.addBatch(None, X)
     _load_oracle_state(g, o, o.codes())
     ids, d = g.searchBatch(Q, k)
     jid, jd, _ = o.search(Q, k, nthreads=8)
-    assert (ids == jid).mean() >= 0.98
+    assert (ids == jid).mean() >= min_match
     same = ids == jid
     assert np.array_equal(bits(d[same]), bits(jd[same]))
     gt, _ = po.flat_search(X, Q, k, nthreads=8)
     assert abs(recall(ids, gt) - recall(jid, gt)) <= 0.005
     g.close()
     with pytest.raises(Exception):
-        v.NativeHnswPqIndex(96, 100, pqM=12, trav_store=2)        # dim % 128 != 0 is rejected at creation
+        v.NativeHnswPqIndex(96, 100, pqM=12, trav_store=store)    # dim % 128 != 0 is rejected at creation
 
 
 @pytest.mark.parametrize("store", [1, 0], ids=["fp32rows", "bf16rows"])

@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""tools/fp8_check.py — recall / id agreement / kernel time of the fp8 traversal rows (trav_store = 2) against the bf16
+"""tools/fp8_check.py — recall / id agreement / kernel time of the fp8 and int8 traversal rows (trav_store = 2 / 3) against the bf16
 default and fp32 rows on the SAME graph, codebooks and codes. Ground truth: the exact flat search of the library.
     python tools/fp8_check.py [--n 100000] [--dim 512] [--nq 1184] [--k 10] [--pqm 64]
 Prints one JSON line."""
@@ -39,7 +39,7 @@ def main():
     tq = torch.from_numpy(Q).cuda()
     out = {"n": a.n, "dim": a.dim, "nq": a.nq, "k": a.k, "build_s": build_s}
     res = {}
-    modes = [("bf16", 0), ("fp8", 2)] + ([] if a.skip_fp32 else [("fp32", 1)])
+    modes = [("bf16", 0), ("fp8", 2), ("int8", 3)] + ([] if a.skip_fp32 else [("fp32", 1)])
     for name, store in modes:
         if store == 0:
             g = base
@@ -59,10 +59,11 @@ def main():
         out[name] = {"recall": recall(ids, gt), "kernel_ms": min(ms), "dist_evals_per_query": st["dist_evals"] / st["queries"]}
         if store != 0:
             g.close()
-    out["fp8"]["id_match_vs_bf16"] = float((res["fp8"] == res["bf16"]).mean())
+    for m in ("fp8", "int8"):
+        out[m]["id_match_vs_bf16"] = float((res[m] == res["bf16"]).mean())
     if "fp32" in res:
-        out["fp8"]["id_match_vs_fp32"] = float((res["fp8"] == res["fp32"]).mean())
-        out["bf16"]["id_match_vs_fp32"] = float((res["bf16"] == res["fp32"]).mean())
+        for m in ("fp8", "int8", "bf16"):
+            out[m]["id_match_vs_fp32"] = float((res[m] == res["fp32"]).mean())
     base.close()
     print(json.dumps(out))
 

@@ -521,6 +521,58 @@ __device__ __forceinline__ void fresh_distances_fp8(const HnswSearchParams& p, c
     }
 }
 
+// ---- int8 traversal rows, opt-in (trav_store = 3): half the row bytes of the bf16 copy, NATIVE tensor op on sm_100a
+//      (IMMA.16832.S8.S8; the e4m3 mma.sync above is lowered to F2FP unpacks + two HMMA per MMA, which doubles the ALU work of
+//      the phase). Row = round(x * 127 / max|x_row|), query likewise; int32 accumulation is exact, dot = acc * s_row * s_query.
+__device__ __forceinline__ void mma_s8_16832(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
+                 : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+template <int NL>
+__device__ __forceinline__ void fresh_distances_i8(const HnswSearchParams& p, const unsigned char* __restrict__ sq8, float qnorm, float qq, float qinv,
+                                                   const int* __restrict__ fnode, int nf, const FreshOut& o) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int g = lane >> 2, c = lane & 3;
+    const unsigned char* tb = reinterpret_cast<const unsigned char*>(p.tbase);
+    const int tstride = p.tstride;
+    const int nst = tstride / (NL * 128);
+    for (int tile = warp; tile * 16 < nf; tile += HN_WARPS) {
+        const int j0 = tile * 16 + g, j1 = j0 + 8;
+        const int n0 = fnode[min(j0, nf - 1)], n1 = fnode[min(j1, nf - 1)];
+        const unsigned char* r0 = tb + (size_t)n0 * tstride + c * 32;
+        const unsigned char* r1 = tb + (size_t)n1 * tstride + c * 32;
+        float sc0 = 0.0f, sc1 = 0.0f, is0 = 0.0f, is1 = 0.0f;
+        if (c == 0 && j0 < nf) { sc0 = p.metric == 1 ? __ldg(p.norms + n0) : __ldg(p.tnorm + n0); is0 = __ldg(p.tscale + n0); }
+        if (c == 0 && j1 < nf) { sc1 = p.metric == 1 ? __ldg(p.norms + n1) : __ldg(p.tnorm + n1); is1 = __ldg(p.tscale + n1); }
+        int a0[4] = {0, 0, 0, 0}, a1[4] = {0, 0, 0, 0};
+        for (int st = 0; st < nst; st++) {
+            U8 A0[NL], A1[NL];
+#pragma unroll
+            for (int i = 0; i < NL; i++) { A0[i] = ld256_nc(r0 + (st * NL + i) * 128); A1[i] = ld256_nc(r1 + (st * NL + i) * 128); }
+#pragma unroll
+            for (int i = 0; i < NL; i++) {
+                const uint4* qh = reinterpret_cast<const uint4*>(sq8 + (st * NL + i) * 128 + c * 32);
+                const uint4 h0 = qh[0], h1 = qh[1];
+                mma_s8_16832(a0, A0[i].lo.x, A1[i].lo.x, A0[i].lo.y, A1[i].lo.y, h0.x, h0.y);
+                mma_s8_16832(a1, A0[i].lo.z, A1[i].lo.z, A0[i].lo.w, A1[i].lo.w, h0.z, h0.w);
+                mma_s8_16832(a0, A0[i].hi.x, A1[i].hi.x, A0[i].hi.y, A1[i].hi.y, h1.x, h1.y);
+                mma_s8_16832(a1, A0[i].hi.z, A1[i].hi.z, A0[i].hi.w, A1[i].hi.w, h1.z, h1.w);
+            }
+        }
+        if (c == 0) {
+            if (j0 < nf) {
+                const float dot = __fmul_rn((float)(a0[0] + a1[0]), __fmul_rn(is0, qinv));
+                accept_key(o, p.metric == 1 ? cosine_dist_from_dot(dot, sc0, qnorm) : fmaxf(__fmaf_rn(-2.0f, dot, __fadd_rn(qq, sc0)), 0.0f), n0);
+            }
+            if (j1 < nf) {
+                const float dot = __fmul_rn((float)(a0[2] + a1[2]), __fmul_rn(is1, qinv));
+                accept_key(o, p.metric == 1 ? cosine_dist_from_dot(dot, sc1, qnorm) : fmaxf(__fmaf_rn(-2.0f, dot, __fadd_rn(qq, sc1)), 0.0f), n1);
+            }
+        }
+    }
+}
+
 #ifndef HN_NL
 #define HN_NL 2           // 32-byte loads per lane, row and stage (a stage = HN_NL * 128 bytes of each row)
 #endif
@@ -779,7 +831,7 @@ __device__ __forceinline__ void fold_side_buffer(uint64_t* P, const uint64_t* F0
 }
 
 // FULL (bf16 rows only): rows are a whole number of 256-byte MMA stages, the distance loop needs no bound checks
-template <bool BF16, bool FULL, int FP8 = 0>      // FP8: 0 = off, else the number of 32-byte loads per row and stage (1 or 2)
+template <bool BF16, bool FULL, int FP8 = 0, bool I8 = false>   // FP8: 0 = off, else 32-byte loads per row and stage (1 or 2) of the 8-bit rows; I8: int8 instead of e4m3
 __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int qpad = (p.dim + 7) & ~7;
@@ -818,7 +870,26 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
             __syncthreads();
             if (tid == 0) S.qnorm = norm_java(sq, p.dim);
         } else if (tid == 0) S.qnorm = 0.0f;
-        if (FP8) {
+        if (FP8 && I8) {
+            signed char* q8 = reinterpret_cast<signed char*>(sqh);          // [dim] int8 query
+            if (warp == 1) {
+                float mx = 0.0f;
+                for (int i = lane; i < p.dim; i += 32) mx = fmaxf(mx, fabsf(sq[i]));
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+                if (lane == 0) S.qinv = mx > 0.0f ? __fdiv_rn(mx, 127.0f) : 1.0f;
+            }
+            __syncthreads();
+            const float qinv_ = S.qinv, qs = __fdiv_rn(1.0f, qinv_);
+            for (int i = tid; i < p.dim; i += HN_NT) q8[i] = (signed char)max(-127, min(127, __float2int_rn(__fmul_rn(sq[i], qs))));
+            __syncthreads();
+            if (warp == 1) {                                           // ||q||^2 of the REPRESENTED query
+                float a = 0.0f;
+                for (int i = lane; i < p.dim; i += 32) { const float v = __fmul_rn((float)q8[i], qinv_); a = __fmaf_rn(v, v, a); }
+                a = warp_tree_sum(a);
+                if (lane == 0) S.qq = a;
+            }
+        } else if (FP8) {
             unsigned char* q8 = reinterpret_cast<unsigned char*>(sqh);      // [dim] hi term, [dim] lo term (x 16)
             if (warp == 1) {
                 float mx = 0.0f;
@@ -873,7 +944,8 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
         __syncthreads();
         {
             FreshOut o{fkey, &S.nacc, false, 0.0f};
-            if constexpr (FP8 != 0) fresh_distances_fp8<FP8 ? FP8 : 1>(p, reinterpret_cast<const unsigned char*>(sqh), qnorm, qq, S.qinv, fnode, 1, o);
+            if constexpr (FP8 != 0 && I8) fresh_distances_i8<FP8 ? FP8 : 1>(p, reinterpret_cast<const unsigned char*>(sqh), qnorm, qq, S.qinv, fnode, 1, o);
+            else if constexpr (FP8 != 0) fresh_distances_fp8<FP8 ? FP8 : 1>(p, reinterpret_cast<const unsigned char*>(sqh), qnorm, qq, S.qinv, fnode, 1, o);
             else if (BF16) fresh_distances_mma<FULL>(p, sqh, qnorm, qq, fnode, 1, o);
             else fresh_dispatch<false>(p, sq, qnorm, qq, fnode, 1, o);
         }
@@ -1000,7 +1072,8 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
                 float bound = 0.0f;
                 if (full) bound = (variant == 0 || evicted) ? pool_dist(P[ef - 1]) : S.dentry;
                 FreshOut o{fkey, &S.nacc, full, bound};
-                if constexpr (FP8 != 0) fresh_distances_fp8<FP8 ? FP8 : 1>(p, reinterpret_cast<const unsigned char*>(sqh), qnorm, qq, S.qinv, fnode, nf, o);
+                if constexpr (FP8 != 0 && I8) fresh_distances_i8<FP8 ? FP8 : 1>(p, reinterpret_cast<const unsigned char*>(sqh), qnorm, qq, S.qinv, fnode, nf, o);
+                else if constexpr (FP8 != 0) fresh_distances_fp8<FP8 ? FP8 : 1>(p, reinterpret_cast<const unsigned char*>(sqh), qnorm, qq, S.qinv, fnode, nf, o);
                 else if (BF16) fresh_distances_mma<FULL>(p, sqh, qnorm, qq, fnode, nf, o);
                 else fresh_dispatch<false>(p, sq, qnorm, qq, fnode, nf, o);
             }
@@ -1112,7 +1185,16 @@ int launch_hnsw_search(const HnswSearchParams& p, int grid, cudaStream_t st) {
     if (p.k + 22 > HN_FMAX || p.deg > 64 || p.batch < 1 || p.batch * p.deg > HN_FMAX || p.batch > HN_MAXB) return 1;
     if ((p.tstride & 15) != 0) return 1;
     const size_t smem = hnsw_search_smem_bytes(p);
-    if (p.tstore == 2) {
+    if (p.tstore == 3) {
+        if ((p.tstride & 127) != 0 || 4 * p.k + 24 > HN_FMAX) return 1;
+        if ((p.tstride & 255) == 0) {
+            if (cudaFuncSetAttribute(hnsw_search_kernel<true, false, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 2;
+            hnsw_search_kernel<true, false, 2, true><<<grid, HN_NT, smem, st>>>(p);
+        } else {
+            if (cudaFuncSetAttribute(hnsw_search_kernel<true, false, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 2;
+            hnsw_search_kernel<true, false, 1, true><<<grid, HN_NT, smem, st>>>(p);
+        }
+    } else if (p.tstore == 2) {
         if ((p.tstride & 127) != 0 || 4 * p.k + 24 > HN_FMAX) return 1;
         if ((p.tstride & 255) == 0) {
             if (cudaFuncSetAttribute(hnsw_search_kernel<true, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 2;
@@ -1143,6 +1225,23 @@ __global__ void make_traversal_rows_kernel(const float* __restrict__ base, int64
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     for (int64_t r = warp; r < n; r += nwarps) {
         float a = 0.0f;
+        if (mode == 3) {
+            // int8 with a per-row scale (largest element -> 127); row stride = dim bytes
+            float mx = 0.0f;
+            for (int c = lane; c < dim; c += 32) mx = fmaxf(mx, fabsf(base[r * dim + c]));
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+            const float inv = mx > 0.0f ? __fdiv_rn(mx, 127.0f) : 1.0f, sc = __fdiv_rn(1.0f, inv);
+            for (int c = lane; c < dim; c += 32) {
+                const int qv = max(-127, min(127, __float2int_rn(__fmul_rn(base[r * dim + c], sc))));
+                reinterpret_cast<signed char*>(out)[r * dim + c] = (signed char)qv;
+                const float sv = __fmul_rn((float)qv, inv);
+                a = __fmaf_rn(sv, sv, a);
+            }
+            a = warp_tree_sum(a);
+            if (lane == 0) { tnorm[r] = a; tscale[r] = inv; }
+            continue;
+        }
         if (mode == 2) {
             // fp8 e4m3 with a per-row power-of-two scale (largest element lands in [120, 240]); row stride = dim bytes
             float mx = 0.0f;

@@ -51,7 +51,7 @@ struct HnswSearchParams {
     int metric;               // 0 sq-L2 (HnswPqIndex), 1 cosine (HnswIndex)
     int variant;              // 0 searchLayerWithSize, 1 HnswPqIndex.searchLayer, 2 HnswIndex.searchLayer
     int ef, k, nq;
-    int tstride, tstore;      // bytes per traversal row (multiple of 16); 0 = fp32, 1 = bf16, 2 = fp8 e4m3
+    int tstride, tstore;      // bytes per traversal row (multiple of 16); 0 = fp32, 1 = bf16, 2 = fp8 e4m3, 3 = int8
     int batch;                // candidates expanded per round (1 = the Java order)
     int profile;              // accumulate thread-0 cycle counters per phase into counters[2..9]
     int visited_in_smem;
@@ -60,7 +60,7 @@ struct HnswSearchParams {
 int launch_hnsw_search(const HnswSearchParams& p, int grid, cudaStream_t st);
 size_t hnsw_search_smem_bytes(const HnswSearchParams& p);
 int hnsw_max_batch(int deg);
-void launch_make_traversal_rows(const float* d_base, int64_t n, int dim, int dpad, int mode /* 0 fp32, 1 bf16, 2 fp8 */, void* d_out, float* d_tnorm,
+void launch_make_traversal_rows(const float* d_base, int64_t n, int dim, int dpad, int mode /* 0 fp32, 1 bf16, 2 fp8, 3 int8 */, void* d_out, float* d_tnorm,
                                 float* d_tscale, cudaStream_t st);
 
 // flat_kernels.cu

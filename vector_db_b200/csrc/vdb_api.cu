@@ -75,7 +75,7 @@ extern "C" int vdb_create(const vdb_config* cfg, vdb_index** out) {
     if (uses_pq) c.metric = VDB_METRIC_SQL2;
     if (c.index_type == VDB_INDEX_HNSW || c.index_type == VDB_INDEX_HNSW_PQ) {
         if (c.hnsw_m > 64) { delete x; FAIL(VDB_ERR_INVALID, "hnsw_m > 64 not supported"); }
-        if (c.trav_store == VDB_TRAV_FP8 && (c.dim % 128) != 0) { delete x; FAIL(VDB_ERR_INVALID, "fp8 traversal rows need dim % 128 == 0"); }
+        if ((c.trav_store == VDB_TRAV_FP8 || c.trav_store == VDB_TRAV_INT8) && (c.dim % 128) != 0) { delete x; FAIL(VDB_ERR_INVALID, "fp8 / int8 traversal rows need dim % 128 == 0"); }
         if (c.ef_construction <= 0) c.ef_construction = c.index_type == VDB_INDEX_HNSW ? 400 : 64;
         if (c.ef_search <= 0) c.ef_search = c.index_type == VDB_INDEX_HNSW ? 400 : 64;
         x->g.init(c.dim, c.hnsw_m, c.max_elements, c.metric, c.level_seed);
@@ -132,9 +132,11 @@ static int upload_rows(vdb_index* x) {
 // traversal copy of rows [n_trav, n_dev): zero-padded to 8 elements, bf16 (default) or fp32 (strict mode)
 static inline int trav_dpad(const vdb_index* x) { return (x->cfg.dim + 7) & ~7; }
 static inline int trav_stride(const vdb_index* x) {
-    return x->cfg.trav_store == VDB_TRAV_FP8 ? x->cfg.dim : trav_dpad(x) * (x->cfg.trav_store == VDB_TRAV_F32 ? 4 : 2);    // fp8: dim % 128 == 0
+    return (x->cfg.trav_store == VDB_TRAV_FP8 || x->cfg.trav_store == VDB_TRAV_INT8) ? x->cfg.dim : trav_dpad(x) * (x->cfg.trav_store == VDB_TRAV_F32 ? 4 : 2);    // fp8: dim % 128 == 0
 }
-static inline int trav_mode(const vdb_index* x) { return x->cfg.trav_store == VDB_TRAV_F32 ? 0 : (x->cfg.trav_store == VDB_TRAV_FP8 ? 2 : 1); }
+static inline int trav_mode(const vdb_index* x) {
+    return x->cfg.trav_store == VDB_TRAV_F32 ? 0 : (x->cfg.trav_store == VDB_TRAV_FP8 ? 2 : (x->cfg.trav_store == VDB_TRAV_INT8 ? 3 : 1));
+}
 static int build_traversal_rows(vdb_index* x) {
     if (x->n_trav >= x->n_dev) return VDB_OK;
     const size_t stride = (size_t)trav_stride(x);
