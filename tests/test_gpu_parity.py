@@ -392,6 +392,25 @@ def test_hnswpq_8bit_traversal_rows(v, po, n, dim, M, store, min_match):
         v.NativeHnswPqIndex(96, 100, pqM=12, trav_store=store)    # dim % 128 != 0 is rejected at creation
 
 
+@pytest.mark.parametrize("store", [2, 3], ids=["fp8", "int8"])
+def test_hnsw_cosine_8bit_traversal_rows(v, po, store):
+    """The 8-bit traversal rows behind the uncompressed cosine index (HnswIndex semantics): same bar as the bf16 walk."""
+    n, dim, nq, k = 10000, 128, 200, 10
+    X, Q = po.synth(42, n, dim), po.synth(43, nq, dim)
+    o = po.OracleHnsw(po.KIND_HNSW, dim, n, level_seed=5)
+    o.add_batch(X)
+    g = v.NativeHnswIndex(dim, n, trav_store=store)
+    g.addBatch(None, X)
+    levels, adj, entry = o.export_graph()
+    g.set_graph(levels, adj, entry)
+    ids, d = g.searchBatch(Q, k)
+    jid, jd, _ = o.search(Q, k, nthreads=8)
+    gt, _ = po.flat_search(po.java_normalize(X), po.java_normalize(Q), k, metric=1, nthreads=8)
+    assert (ids == jid).mean() >= 0.97
+    assert abs(recall(ids, gt) - recall(jid, gt)) <= 0.005
+    g.close()
+
+
 @pytest.mark.parametrize("store", [1, 0], ids=["fp32rows", "bf16rows"])
 def test_hnswpq_large_rounds(v, po, store):
     """64 candidates per round on a beam of 1500: the first rounds accept up to 2048 keys at once, which drives the
