@@ -164,6 +164,10 @@ ORC_API void orc_java_normalize(const float* a, int d, float* out) {      // Vec
     float n = norm_java(a, d);
     for (int i = 0; i < d; i++) out[i] = a[i] / n;
 }
+ORC_API void orc_java_normalize_rows(const float* a, int64_t n, int d, float* out) {   // row-wise, OpenMP (test sizes up to 1M rows)
+    #pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < n; i++) orc_java_normalize(a + i * d, d, out + i * d);
+}
 // native "cosine": 1 - dot with the 8-lane FMA order (DistanceAVX2.cpp:35-57). Listed for completeness.
 ORC_API float orc_native_cosine(const float* a, const float* b, int d) {
     float l[8] = {0, 0, 0, 0, 0, 0, 0, 0};

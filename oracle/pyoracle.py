@@ -45,6 +45,7 @@ def lib():
             getattr(L, n).argtypes = [_f32p, _f32p, C.c_int]; getattr(L, n).restype = C.c_float
         L.orc_java_norm.argtypes = [_f32p, C.c_int]; L.orc_java_norm.restype = C.c_float
         L.orc_java_normalize.argtypes = [_f32p, C.c_int, _f32p]
+        L.orc_java_normalize_rows.argtypes = [_f32p, C.c_int64, C.c_int, _f32p]
         L.orc_recommended_pq_m.argtypes = [C.c_int]; L.orc_recommended_pq_m.restype = C.c_int
         L.orc_java_random_probe.argtypes = [C.c_int64, C.c_int32, C.c_int, _i32p, _f32p]
         L.orc_pq_train.argtypes = [_f32p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _f32p]
@@ -171,6 +172,14 @@ def java_normalize(v):
     else:
         for i in range(v.shape[0]):
             lib().orc_java_normalize(v[i], v.shape[1], out[i])
+    return out
+
+
+def java_normalize_rows(v):
+    """row-wise Vector.normalize (core/Vector.java:107-116) in C with OpenMP: for the 1M-row cosine checks"""
+    v = _f32(v)
+    out = np.empty_like(v)
+    lib().orc_java_normalize_rows(v, v.shape[0], v.shape[1], out)
     return out
 
 
