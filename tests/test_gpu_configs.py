@@ -101,9 +101,22 @@ def test_c3_headline_shape_sample(v, po):
     gt, _ = po.flat_search(X, Q, k, nthreads=CORES)
     rg, rj = recall(ids, gt), recall(jid, gt)
     assert abs(rg - rj) <= 0.005, (rg, rj)
+    # id agreement with the Java pop order. Measured on the B200 (tools/c3_idmatch.py -> profiles/r2_c3_idmatch.log): with ONE
+    # candidate per round the ids are 100 % the oracle's for bf16 AND fp32 rows; with the default 64 candidates per round 8 of
+    # 256 queries differ, and in every one of them the GPU's k-th exact distance is strictly SMALLER (the batched round expands
+    # a few candidates the sequential loop would have skipped, +0.8 % distance evaluations). So the bar for the batched mode is:
+    # >= 98 % equal ids, and wherever they differ the GPU answer must not be worse (<= 1 query of the sample may be).
     match = float((ids == jid).mean())
     rep = _diff_report(ids, jid, d, jd, k)
-    assert match >= 0.99, (match, rep)
+    assert match >= 0.98, (match, rep)
+    assert rep["gpu_worse_kth"] <= 1 and rg >= rj - 1e-9, (match, rep, rg, rj)
+    # one candidate per round on the bf16 rows (half the bytes of the strict fp32 mode): the Java pop order, ids identical
+    b1 = v.NativeHnswPqIndex(dim, 2 * n, pqM=M, level_seed=1234, trav_batch=1)
+    b1.addBatch(np.arange(n, dtype=np.int32), X)
+    b1.set_codebooks(state[3]); b1.set_graph(state[0], list(state[1]), state[2]); b1.set_codes(state[4])
+    bid, bd = b1.searchBatch(Q[:64], k)
+    b1.close()
+    assert (bid == jid[:64]).mean() >= 0.995
     same = ids == jid
     assert np.array_equal(bits(d[same]), bits(jd[same]))
     st = g.stats()
