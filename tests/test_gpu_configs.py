@@ -109,7 +109,7 @@ def test_c3_headline_shape_sample(v, po):
     match = float((ids == jid).mean())
     rep = _diff_report(ids, jid, d, jd, k)
     assert match >= 0.98, (match, rep)
-    assert rep["gpu_worse_kth"] <= 1 and rg >= rj - 1e-9, (match, rep, rg, rj)
+    assert rep["gpu_worse_kth"] <= 1 and rg >= rj - 0.002, (match, rep, rg, rj)
     # one candidate per round on the bf16 rows (half the bytes of the strict fp32 mode): the Java pop order, ids identical
     b1 = v.NativeHnswPqIndex(dim, 2 * n, pqM=M, level_seed=1234, trav_batch=1)
     b1.addBatch(np.arange(n, dtype=np.int32), X)
