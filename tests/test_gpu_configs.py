@@ -164,7 +164,7 @@ def test_c5_adc_scan_rerank_1m_1000(v, po):
     X = po.synth(42, n, dim)
     sample = np.concatenate([np.arange(0, 8192), np.arange(n - 8192, n)])
     assert np.array_equal(codes[sample], po.pq_encode(X[sample], cb, po.ARITH_NATIVE_AVX2))   # codes bit-exact (row sample)
-    oi, od = po.pq_flat_search(Q, cb, codes, k, po.ARITH_NATIVE_AVX2, rerank=R, base=X, nthreads=CORES)
+    oi, od = po.pq_flat_search(Q, cb, codes, k, po.ARITH_NATIVE_AVX2, rerank=R, base=X, exact_order=1, nthreads=CORES)   # re-score in order R1 (euclideanDistanceAVX2)
     assert np.array_equal(ids, oi)
     assert np.array_equal(bits(d), bits(od))
     # no-rerank form == PQIndex::search itself (ADC distances, (dist,id) order) on a smaller query set
