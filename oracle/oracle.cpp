@@ -207,6 +207,15 @@ struct JavaRandom {
     }
     float nextFloat() { return (float)next(24) / (float)(1 << 24); }
 };
+// kind 0: nextInt() = next(32); 1: nextInt(bound); 2: nextFloat() — one stream per call (java.util.Random javadoc)
+ORC_API void orc_java_random_stream(int64_t seed, int kind, int32_t bound, int n, int32_t* ints, float* floats) {
+    JavaRandom r(seed);
+    for (int i = 0; i < n; i++) {
+        if (kind == 0) ints[i] = r.next(32);
+        else if (kind == 1) ints[i] = r.nextInt(bound);
+        else floats[i] = r.nextFloat();
+    }
+}
 ORC_API void orc_java_random_probe(int64_t seed, int32_t bound, int n, int32_t* ints, float* floats) {
     JavaRandom r(seed);
     for (int i = 0; i < n; i++) { ints[i] = r.nextInt(bound); floats[i] = r.nextFloat(); }
@@ -553,6 +562,13 @@ struct Hnsw {
     std::vector<std::vector<std::vector<int>>> graph;   // [level][index] -> neighbour indices
     std::vector<std::vector<uint8_t>> present;           // [level][index] node has a list at that level
     int entry = -1;
+    // removeVector (HnswPqIndex.java:542-596): a removed node stays as a dead index (Java: id gone from `vectors`)
+    std::vector<uint8_t> dead;
+    int nlive = 0;
+    // Java `currentSize` / idToIndex: code row = currentSize at insert time, currentSize-- on removal (:393,:467,:591), so an
+    // insert after a removal overwrites the code row of an earlier vector. jindex[index] = that row; codes are indexed by it.
+    std::vector<int> jindex;
+    int javaSize = 0;
     // scratch for the insert path (searches use a per-thread Scratch)
     struct Scratch { std::vector<uint32_t> visit; uint32_t epoch = 0; } own;
 
@@ -566,8 +582,9 @@ struct Hnsw {
         return 1.0f - dot / (norms[i] * qnorm);                   // HnswIndex.java:126-133
     }
     float pqdist(const float* q, int i) const {
-        if (arith == 2) return pq_direct_parts(q, &codes[(size_t)i * pqM], codebooks.data(), pqM, ncent, sd);
-        return pq_direct(q, &codes[(size_t)i * pqM], codebooks.data(), pqM, ncent, sd);
+        const size_t row = (size_t)jindex[i];                       // idToIndex.get(id) (:804,:814)
+        if (arith == 2) return pq_direct_parts(q, &codes[row * pqM], codebooks.data(), pqM, ncent, sd);
+        return pq_direct(q, &codes[row * pqM], codebooks.data(), pqM, ncent, sd);
     }
 
     int assignLevel() {                                            // HnswPqIndex.java:752-759 (seeded)
@@ -597,6 +614,7 @@ static int search_closest(const Hnsw& h, const float* q, float qn, int ep, int l
         const std::vector<int>& nb = h.graph[lvl][cur];
         if (nb.empty()) return cur;
         for (int n : nb) {
+            if (h.dead[n]) continue;                                // `!vectors.containsKey(neighborId)` (:778,:811)
             float d = compressed ? h.pqdist(q, n) : h.dist(q, qn, n, st);
             if (d < curd) { curd = d; cur = n; changed = true; break; }
         }
@@ -631,7 +649,7 @@ static void search_layer(const Hnsw& h, Hnsw::Scratch& sc, const float* q, float
         if (nb.empty()) continue;
         if (st) st->expansions++;
         for (int n : nb) {
-            if (sc.visit[n] == sc.epoch) continue;
+            if (sc.visit[n] == sc.epoch || h.dead[n]) continue;     // visited, or no longer stored (:869,:944): not marked
             sc.visit[n] = sc.epoch;
             float d = h.dist(q, qn, n, st);
             if ((int)results.size() < ef || d < furthest) {
@@ -669,11 +687,14 @@ static void hnsw_insert(Hnsw& h, int id, const float* v, bool compressed_phase) 
     h.ids.push_back(id);
     h.vecs.insert(h.vecs.end(), v, v + h.dim);
     h.norms.push_back(h.kind == 1 ? norm_java(v, h.dim) : 0.0f);
+    h.dead.push_back(0); h.nlive++;
+    const int jrow = h.javaSize++;                                    // index = currentSize++ (:393,:467)
+    h.jindex.push_back(jrow);
     if (h.kind == 0) {
-        h.codes.resize((size_t)(index + 1) * h.pqM, 0);              // Java codes[][] start zeroed (:104)
+        if (h.codes.size() < (size_t)(jrow + 1) * h.pqM) h.codes.resize((size_t)(jrow + 1) * h.pqM, 0);   // Java codes[][] start zeroed (:104)
         if (compressed_phase)
             for (int m = 0; m < h.pqM; m++)
-                h.codes[(size_t)index * h.pqM + m] = (uint8_t)nearest_centroid(&h.codebooks[(size_t)m * h.ncent * h.sd], v + m * h.sd, h.sd, h.ncent, ARITH_JAVA_SEQ);
+                h.codes[(size_t)jrow * h.pqM + m] = (uint8_t)nearest_centroid(&h.codebooks[(size_t)m * h.ncent * h.sd], v + m * h.sd, h.sd, h.ncent, ARITH_JAVA_SEQ);
     }
     int lv = h.assignLevel();
     h.level.push_back(lv);
@@ -701,6 +722,7 @@ static void hnsw_insert(Hnsw& h, int id, const float* v, bool compressed_phase) 
             if ((int)conn.size() > h.M) {
                 tmp.clear();
                 for (int nn : conn) {
+                    if (h.dead[nn]) continue;                       // `nnVector != null` (:435): dangling links drop out here
                     // calculateDistance(neighborVector, nnVector): distance of stored vectors
                     float d;
                     if (h.kind == 0) d = l2sq_seq(h.vec(nb), h.vec(nn), h.dim);
@@ -740,7 +762,8 @@ ORC_API void orc_hnsw_set_arith(void* p, int arith) { ((Hnsw*)p)->arith = arith;
 // HnswIndex.java:139-248 (normalise on insert :154).
 ORC_API int orc_hnsw_add(void* p, int id, const float* v) {
     Hnsw& h = *(Hnsw*)p;
-    if (h.size() >= h.maxElements) return 0;
+    for (int i = 0; i < h.size(); i++) if (!h.dead[i] && h.ids[i] == id) return 0;    // vectors.containsKey(id) (:157-159)
+    if (h.nlive >= h.maxElements) return 0;                                          // vectors.size() >= maxElements (:161-163)
     if (h.kind == 1) {
         std::vector<float> nv(h.dim);
         orc_java_normalize(v, h.dim, nv.data());
@@ -764,17 +787,73 @@ ORC_API void orc_hnsw_rebuild(void* p) {
     if (h.kind == 0 && !h.trained && h.ntrain > 0) hnsw_train(h);
     std::vector<float> sv; sv.swap(h.vecs);
     std::vector<int32_t> sid; sid.swap(h.ids);
+    std::vector<uint8_t> sdead; sdead.swap(h.dead);
     int n = (int)sid.size();
-    std::vector<int> order(n);
-    for (int i = 0; i < n; i++) order[i] = i;
+    std::vector<int> order;
+    for (int i = 0; i < n; i++) if (!sdead[i]) order.push_back(i);     // new HashMap<>(vectors) (:687): live vectors only
     std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return sid[a] < sid[b]; });
-    h.norms.clear(); h.level.clear(); h.codes.clear(); h.entry = -1;
+    h.norms.clear(); h.level.clear(); h.codes.clear(); h.entry = -1; h.jindex.clear(); h.javaSize = 0; h.nlive = 0;
     for (int l = 0; l < h.maxLevel; l++) { h.graph[l].clear(); h.present[l].clear(); }
     for (int i : order) {
         // HnswIndex re-normalises already-normalised vectors on re-add (addVector :154) — restated as is.
         orc_hnsw_add(p, sid[i], &sv[(size_t)i * h.dim]);
     }
 }
+// removeVector: HnswPqIndex.java:542-596 / HnswIndex.java:254-317. Returns 1 when the id was stored.
+ORC_API int orc_hnsw_remove(void* p, int id) {
+    Hnsw& h = *(Hnsw*)p;
+    int idx = -1;
+    for (int i = 0; i < h.size(); i++) if (!h.dead[i] && h.ids[i] == id) { idx = i; break; }
+    if (idx < 0) return 0;
+    for (int l = 0; l <= h.level[idx] && l < h.maxLevel; l++) {
+        std::vector<int> copy = h.graph[l][idx];                      // neighborsCopy (:562)
+        for (int nb : copy) {
+            std::vector<int>& conn = h.graph[l][nb];
+            auto it = std::find(conn.begin(), conn.end(), idx);       // remove(Integer.valueOf(id)): first occurrence
+            if (it != conn.end()) conn.erase(it);
+        }
+        h.graph[l][idx].clear(); h.present[l][idx] = 0;               // currentGraph.remove(id)
+    }
+    if (idx == h.entry) {
+        if (h.nlive == 1) h.entry = -1;
+        else {
+            // first key of the ConcurrentHashMap<>(maxElements) in iteration order, skipping id (:577-584): ascending bin
+            // ((h ^ h>>>16) & 0x7fffffff) & (table-1), table = tableSizeFor(1.5*maxElements+1); insertion order inside a bin
+            uint64_t want = (uint64_t)h.maxElements + ((uint64_t)h.maxElements >> 1) + 1, table = 1;
+            while (table < want && table < (1ull << 30)) table <<= 1;
+            int best = -1; uint64_t bestbin = ~0ull;
+            for (int i = 0; i < h.size(); i++) {
+                if (h.dead[i] || i == idx) continue;
+                uint32_t hc = (uint32_t)h.ids[i];
+                uint64_t bin = ((hc ^ (hc >> 16)) & 0x7fffffffu) & (table - 1);
+                if (bin < bestbin) { bestbin = bin; best = i; }
+            }
+            h.entry = best;
+        }
+    }
+    h.dead[idx] = 1; h.nlive--;
+    if (h.kind == 0) h.javaSize--;                                    // currentSize-- (:591)
+    return 1;
+}
+ORC_API int orc_hnsw_live(void* p) { return ((Hnsw*)p)->nlive; }
+ORC_API void orc_hnsw_get_dead(void* p, uint8_t* out) { Hnsw& h = *(Hnsw*)p; std::memcpy(out, h.dead.data(), h.dead.size()); }
+// state of a snapshot that carries removals: dead[n], code-row table jindex[n] (int64), Java currentSize, level counter
+ORC_API void orc_hnsw_set_dead(void* p, const uint8_t* dead, const int64_t* jindex, int64_t javaSize, uint64_t level_ctr) {
+    Hnsw& h = *(Hnsw*)p;
+    const int n = h.size();
+    h.nlive = 0;
+    for (int i = 0; i < n; i++) { h.dead[i] = dead[i]; if (!dead[i]) h.nlive++; h.jindex[i] = (int)jindex[i]; }
+    h.javaSize = (int)javaSize; h.level_ctr = level_ctr;
+    // codes arrive per vector (row i = code of vector i); rows sharing a Java code row hold identical codes by construction
+    if (h.kind == 0 && !h.codes.empty()) {
+        std::vector<uint8_t> byrow(h.codes);
+        for (int i = 0; i < n; i++) std::memcpy(&h.codes[(size_t)h.jindex[i] * h.pqM], &byrow[(size_t)i * h.pqM], (size_t)h.pqM);
+    }
+}
+ORC_API void orc_hnsw_get_jindex(void* p, int64_t* out) { Hnsw& h = *(Hnsw*)p; for (int i = 0; i < h.size(); i++) out[i] = h.jindex[i]; }
+ORC_API uint64_t orc_hnsw_level_ctr(void* p) { return ((Hnsw*)p)->level_ctr; }
+ORC_API int64_t orc_hnsw_java_size(void* p) { return ((Hnsw*)p)->javaSize; }
+ORC_API void orc_hnsw_get_ids(void* p, int32_t* out) { Hnsw& h = *(Hnsw*)p; for (int i = 0; i < h.size(); i++) out[i] = h.ids[i]; }
 ORC_API int orc_hnsw_size(void* p) { return ((Hnsw*)p)->size(); }
 ORC_API int orc_hnsw_trained(void* p) { return ((Hnsw*)p)->trained ? 1 : 0; }
 ORC_API int orc_hnsw_max_level(void* p) { return ((Hnsw*)p)->maxLevel; }
@@ -783,7 +862,11 @@ ORC_API void orc_hnsw_get_codebooks(void* p, float* out) { Hnsw& h = *(Hnsw*)p; 
 ORC_API void orc_hnsw_set_codebooks(void* p, const float* cb) {
     Hnsw& h = *(Hnsw*)p; h.codebooks.assign(cb, cb + (size_t)h.pqM * h.ncent * h.sd); h.trained = true;
 }
-ORC_API void orc_hnsw_get_codes(void* p, uint8_t* out) { Hnsw& h = *(Hnsw*)p; std::memcpy(out, h.codes.data(), h.codes.size()); }
+// codes as the walk sees them: row i = the code row of vector i (codes[idToIndex[id]])
+ORC_API void orc_hnsw_get_codes(void* p, uint8_t* out) {
+    Hnsw& h = *(Hnsw*)p;
+    for (int i = 0; i < h.size(); i++) std::memcpy(out + (size_t)i * h.pqM, &h.codes[(size_t)h.jindex[i] * h.pqM], (size_t)h.pqM);
+}
 ORC_API void orc_hnsw_get_vectors(void* p, float* out) { Hnsw& h = *(Hnsw*)p; std::memcpy(out, h.vecs.data(), h.vecs.size() * sizeof(float)); }
 ORC_API void orc_hnsw_get_norms(void* p, float* out) { Hnsw& h = *(Hnsw*)p; std::memcpy(out, h.norms.data(), h.norms.size() * sizeof(float)); }
 ORC_API void orc_hnsw_get_levels(void* p, int32_t* out) { Hnsw& h = *(Hnsw*)p; for (int i = 0; i < h.size(); i++) out[i] = h.level[i]; }
@@ -811,14 +894,14 @@ ORC_API void orc_hnsw_set_ef_cap(void* p, int cap) { ((Hnsw*)p)->efCap = cap > 0
 // searchNearest: HnswPqIndex.java:599-669 / HnswIndex.java:328-365. stats[0]=distance evals, [1]=expansions.
 static void hnsw_search_one(const Hnsw& h, Hnsw::Scratch& sc, const float* qin, int k, int32_t* out_ids, float* out_d, int64_t* stats) {
     for (int j = 0; j < k; j++) { out_ids[j] = -1; out_d[j] = std::numeric_limits<float>::infinity(); }
-    if (h.size() == 0 || h.entry < 0) return;
+    if (h.nlive == 0 || h.entry < 0) return;
     Stats st;
     std::vector<float> qbuf; const float* q = qin; float qn = 0.0f;
     if (h.kind == 1) { qbuf.resize(h.dim); orc_java_normalize(qin, h.dim, qbuf.data()); q = qbuf.data(); qn = norm_java(q, h.dim); }
     int cur = h.entry;
     std::vector<Cand> cands;
     if (h.kind == 0) {
-        int searchEf = java_search_ef(h.size(), k, h.ef, h.efCap);
+        int searchEf = java_search_ef(h.nlive, k, h.ef, h.efCap);          // dataSize = vectors.size() (:615)
         for (int l = h.maxLevel - 1; l > 0; l--) cur = search_closest(h, q, qn, cur, l, h.trained, &st);
         if (h.trained) search_layer(h, sc, q, qn, cur, std::max(searchEf, k * 100), 0, 0, cands, &st);
         else search_layer(h, sc, q, qn, cur, searchEf, 0, 1, cands, &st);
@@ -858,6 +941,29 @@ ORC_API void orc_hnsw_search(void* p, const float* queries, int nq, int k, int32
     }
 }
 
+// ---- test hooks: ONE layer search / ONE greedy descent with explicit parameters (the micro-fixtures of
+//      tests/golden/micro_fixtures.json drive the termination rules on hand-derived 5..8-node graphs) ----
+ORC_API int orc_hnsw_search_layer(void* p, const float* qin, int ep, int ef, int level, int variant, int32_t* out_idx, float* out_d,
+                                  int64_t* stats) {
+    Hnsw& h = *(Hnsw*)p;
+    std::vector<float> qbuf; const float* q = qin; float qn = 0.0f;
+    if (h.kind == 1) { qbuf.resize(h.dim); orc_java_normalize(qin, h.dim, qbuf.data()); q = qbuf.data(); qn = norm_java(q, h.dim); }
+    std::vector<Cand> out; Stats st;
+    search_layer(h, h.own, q, qn, ep, ef, level, variant, out, &st);
+    for (size_t i = 0; i < out.size(); i++) { out_idx[i] = out[i].idx; out_d[i] = out[i].d; }
+    if (stats) { stats[0] = st.dist_evals; stats[1] = st.expansions; }
+    return (int)out.size();
+}
+ORC_API int orc_hnsw_search_closest(void* p, const float* qin, int ep, int level, int compressed, int64_t* stats) {
+    Hnsw& h = *(Hnsw*)p;
+    std::vector<float> qbuf; const float* q = qin; float qn = 0.0f;
+    if (h.kind == 1) { qbuf.resize(h.dim); orc_java_normalize(qin, h.dim, qbuf.data()); q = qbuf.data(); qn = norm_java(q, h.dim); }
+    Stats st;
+    int r = search_closest(h, q, qn, ep, level, compressed != 0, &st);
+    if (stats) { stats[0] = st.dist_evals; stats[1] = st.expansions; }
+    return r;
+}
+
 // Import a graph built elsewhere (the product's builder / a snapshot) so the CPU search runs on the SAME graph,
 // codebooks and codes as the GPU ("same persisted graph and codebooks", BASELINE.json north_star).
 // vecs[n][dim] are stored as is (already normalised for kind 1); adj[max_level][n][M] is -1 padded.
@@ -880,6 +986,9 @@ ORC_API void orc_hnsw_import(void* p, int n, const float* vecs, const int32_t* i
         }
     }
     h.entry = entry;
+    h.dead.assign(n, 0); h.nlive = n; h.javaSize = n;
+    h.jindex.resize(n);
+    for (int i = 0; i < n; i++) h.jindex[i] = i;
     if (h.kind == 0 && codebooks && codes) {
         h.codebooks.assign(codebooks, codebooks + (size_t)h.pqM * h.ncent * h.sd);
         h.codes.assign(codes, codes + (size_t)n * h.pqM);

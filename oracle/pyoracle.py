@@ -75,6 +75,19 @@ def lib():
         L.orc_hnsw_get_level_adj.argtypes = [C.c_void_p, C.c_int, _i32p, _u8p]
         L.orc_hnsw_import.argtypes = [C.c_void_p, C.c_int, _f32p, C.c_void_p, _i32p, _i32p, C.c_int, C.c_void_p, C.c_void_p]
         L.orc_java_search_ef.argtypes = [C.c_int] * 3; L.orc_java_search_ef.restype = C.c_int
+        L.orc_java_random_stream.argtypes = [C.c_int64, C.c_int, C.c_int32, C.c_int, _i32p, _f32p]
+        L.orc_hnsw_search_layer.argtypes = [C.c_void_p, _f32p, C.c_int, C.c_int, C.c_int, C.c_int, _i32p, _f32p, _i64p]
+        L.orc_hnsw_search_layer.restype = C.c_int
+        L.orc_hnsw_search_closest.argtypes = [C.c_void_p, _f32p, C.c_int, C.c_int, C.c_int, _i64p]
+        L.orc_hnsw_search_closest.restype = C.c_int
+        L.orc_hnsw_remove.argtypes = [C.c_void_p, C.c_int]; L.orc_hnsw_remove.restype = C.c_int
+        L.orc_hnsw_live.argtypes = [C.c_void_p]; L.orc_hnsw_live.restype = C.c_int
+        L.orc_hnsw_get_dead.argtypes = [C.c_void_p, _u8p]
+        L.orc_hnsw_set_dead.argtypes = [C.c_void_p, _u8p, _i64p, C.c_int64, C.c_uint64]
+        L.orc_hnsw_get_jindex.argtypes = [C.c_void_p, _i64p]
+        L.orc_hnsw_get_ids.argtypes = [C.c_void_p, _i32p]
+        L.orc_hnsw_level_ctr.argtypes = [C.c_void_p]; L.orc_hnsw_level_ctr.restype = C.c_uint64
+        L.orc_hnsw_java_size.argtypes = [C.c_void_p]; L.orc_hnsw_java_size.restype = C.c_int64
         L.orc_hnsw_search.argtypes = [C.c_void_p, _f32p, C.c_int, C.c_int, _i32p, _f32p, _i64p, C.c_int]
         _lib = L
     return _lib
@@ -216,6 +229,39 @@ class OracleHnsw:
         v = _f32(vecs)
         idp = None if ids is None else np.ascontiguousarray(ids, dtype=np.int32).ctypes.data
         lib().orc_hnsw_add_batch(self.h, idp, v, v.shape[0])
+
+    def search_layer(self, q, ep, ef, level, variant):
+        """test hook: one searchLayer* call (variant 0 searchLayerWithSize, 1 HnswPqIndex.searchLayer, 2 HnswIndex.searchLayer)
+        -> (node indices ascending by distance, distances, (dist_evals, expansions))"""
+        idx = np.empty(self.size, dtype=np.int32); d = np.empty(self.size, dtype=np.float32); st = np.zeros(2, dtype=np.int64)
+        c = lib().orc_hnsw_search_layer(self.h, _f32(q), int(ep), int(ef), int(level), int(variant), idx, d, st)
+        return idx[:c], d[:c], st
+
+    def search_closest(self, q, ep, level, compressed=False):
+        st = np.zeros(2, dtype=np.int64)
+        return lib().orc_hnsw_search_closest(self.h, _f32(q), int(ep), int(level), int(bool(compressed)), st), st
+
+    def add(self, id_, vec):
+        """addVector: False for a duplicate id or a full index (HnswPqIndex.java:157-163)"""
+        return bool(lib().orc_hnsw_add(self.h, int(id_), _f32(vec)))
+
+    def remove(self, id_):
+        """removeVector (HnswPqIndex.java:542-596 / HnswIndex.java:254-317)"""
+        return bool(lib().orc_hnsw_remove(self.h, int(id_)))
+
+    @property
+    def live(self):
+        return lib().orc_hnsw_live(self.h)
+
+    def dead(self):
+        out = np.zeros(self.size, dtype=np.uint8)
+        lib().orc_hnsw_get_dead(self.h, out)
+        return out
+
+    def ext_ids(self):
+        out = np.empty(self.size, dtype=np.int32)
+        lib().orc_hnsw_get_ids(self.h, out)
+        return out
 
     def rebuild(self):
         lib().orc_hnsw_rebuild(self.h)
