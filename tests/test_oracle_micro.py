@@ -89,3 +89,132 @@ def _adj_table(o, adj, level=0):
     for i, nb in enumerate(adj):
         A[level, i, :len(nb)] = nb
     return A
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# 2. independent Python restatement of the Java methods (written from the Java source; float32 arithmetic through numpy)
+# ---------------------------------------------------------------------------------------------------------------------
+F = np.float32
+
+
+def _l2sq_java(a, b):                      # HnswPqIndex.java:741-750: sequential sum += diff * diff
+    s = F(0)
+    for x, y in zip(a, b):
+        df = F(x) - F(y)
+        s = F(s + F(df * df))
+    return s
+
+
+class PyJavaHnswPq:
+    """searchLayer / searchLayerWithSize / searchLayerClosest / searchNearest of index/HnswPqIndex.java on a given graph
+    (untrained index = exact distances everywhere). Heap ties by (distance, id) like the C++ oracle states it does."""
+
+    def __init__(self, X, adj_levels, entry, ef=64):
+        self.X, self.adj, self.entry, self.ef = X, adj_levels, entry, ef
+        self.max_level = len(adj_levels)
+        self.evals = 0
+
+    def dist(self, i, q):
+        self.evals += 1
+        return _l2sq_java(self.X[i], q)
+
+    def closest(self, q, ep, level):       # :761-792
+        cur, curd = ep, self.dist(ep, q)
+        changed = True
+        while changed:
+            changed = False
+            nb = self.adj[level].get(cur)
+            if not nb:
+                return cur
+            for n in nb:
+                d = self.dist(n, q)
+                if d < curd:
+                    curd, cur, changed = d, n, True
+                    break
+        return cur
+
+    def layer(self, q, ep, ef, level, with_size):      # :829-895 (with_size False) / :905-974 (True)
+        d0 = self.dist(ep, q)
+        results = [(-d0, -ep)]             # max-heap through negation; ties: larger id is "further"
+        cands = [(d0, ep)]
+        visited = {ep}
+        furthest = d0
+        while cands:
+            cd, c = heapq.heappop(cands)
+            if cd > furthest and len(results) >= ef:
+                if with_size:
+                    break
+                continue
+            nb = self.adj[level].get(c)
+            if not nb:
+                continue
+            for n in nb:
+                if n in visited:
+                    continue
+                visited.add(n)
+                d = self.dist(n, q)
+                if len(results) < ef or d < furthest:
+                    heapq.heappush(cands, (d, n))
+                    heapq.heappush(results, (-d, -n))
+                    if with_size:
+                        if len(results) > ef:
+                            heapq.heappop(results)
+                        furthest = -results[0][0]
+                    elif len(results) > ef:
+                        heapq.heappop(results)
+                        furthest = -results[0][0]
+        return sorted((-a, -b) for a, b in results)
+
+    def search(self, q, k):                # :599-669, untrained branch
+        n = len(self.X)
+        ef = min(min(max(max(int(n * 0.15), k * 100), self.ef), n), 5000)
+        cur = self.entry
+        for level in range(self.max_level - 1, 0, -1):
+            cur = self.closest(q, cur, level)
+        c = self.layer(q, cur, ef, 0, False)
+        c = sorted((_l2sq_java(self.X[i], q), i) for _, i in c)
+        return c[:k]
+
+
+def _random_graph(rng, n, L, deg):
+    levels = np.minimum(rng.geometric(0.6, n) - 1, L - 1)
+    levels[0] = L - 1
+    adj = []
+    for l in range(L):
+        members = [i for i in range(n) if levels[i] >= l]
+        d = {}
+        for i in members:
+            others = [j for j in members if j != i]
+            d[i] = list(rng.choice(others, size=min(deg, len(others)), replace=False)) if others else []
+        adj.append(d)
+    return levels.astype(np.int32), adj
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_cpp_oracle_equals_independent_python_restatement(po, seed):
+    rng = np.random.default_rng(seed)
+    n, dim, deg = 90 + 10 * seed, 6, 4 + seed % 3
+    X = rng.uniform(-1, 1, (n, dim)).astype(np.float32)
+    o = po.OracleHnsw(po.KIND_HNSWPQ, dim, 1100, pq_m=2)
+    L = o.max_level
+    levels, adj = _random_graph(rng, n, L, deg)
+    A = np.full((L, n, 32), -1, dtype=np.int32)
+    for l in range(L):
+        for i, nb in adj[l].items():
+            A[l, i, :len(nb)] = nb
+    o.import_state(X, levels, A, 0)
+    py = PyJavaHnswPq(X, adj, 0)
+    Q = rng.uniform(-1, 1, (8, dim)).astype(np.float32)
+    for q in Q:
+        for ef in (3, 10, 200):
+            for variant, with_size in ((0, True), (1, False)):
+                py.evals = 0
+                want = py.layer(q, 5, ef, 0, with_size)
+                idx, d, st = o.search_layer(q, 5, ef, 0, variant)
+                assert [i for _, i in want] == list(idx) and [float(x) for x, _ in want] == [float(x) for x in d]
+                assert py.evals == int(st[0])
+        py.evals = 0
+        want = py.search(q, 5)
+        ids, d, st = o.search(q.reshape(1, -1), 5)
+        assert [i for _, i in want] == [int(i) for i in ids[0] if i >= 0]
+        assert [float(x) for x, _ in want] == [float(x) for x, i in zip(d[0], ids[0]) if i >= 0]
