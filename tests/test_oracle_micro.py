@@ -218,3 +218,88 @@ def test_cpp_oracle_equals_independent_python_restatement(po, seed):
         ids, d, st = o.search(q.reshape(1, -1), 5)
         assert [i for _, i in want] == [int(i) for i in ids[0] if i >= 0]
         assert [float(x) for x, _ in want] == [float(x) for x, i in zip(d[0], ids[0]) if i >= 0]
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# 3. java.util.Random — javadoc algorithm restated in Python ints, anchored on published values
+# ---------------------------------------------------------------------------------------------------------------------
+class PyJavaRandom:
+    MASK = (1 << 48) - 1
+
+    def __init__(self, seed):
+        self.seed = (seed ^ 0x5DEECE66D) & self.MASK
+
+    def next(self, bits):
+        self.seed = (self.seed * 0x5DEECE66D + 0xB) & self.MASK
+        v = self.seed >> (48 - bits)
+        return v - (1 << bits) if v >= (1 << (bits - 1)) and bits == 32 else v     # (int) cast: only next(32) can be negative
+
+    def nextInt(self, bound=None):
+        if bound is None:
+            return self.next(32)
+        r = self.next(31)
+        m = bound - 1
+        if (bound & m) == 0:
+            return (bound * r) >> 31
+        u = r
+        while True:
+            r = u % bound
+            if u - r + m < (1 << 31):      # Java: `u - r + m < 0` detects int overflow
+                return r
+            u = self.next(31)
+
+    def nextFloat(self):
+        return np.float32(self.next(24)) / np.float32(1 << 24)
+
+
+def test_java_random_anchored_and_long_streams(po):
+    a = FX["java_random_anchors"]
+    r0 = PyJavaRandom(0)
+    assert [r0.nextInt(), r0.nextInt()] == a["seed0_nextInt"]            # the classic `new Random(0)` values
+    assert PyJavaRandom(42).nextInt() == a["seed42_nextInt_first"]
+    assert PyJavaRandom(42).nextInt(10) == a["seed42_nextInt10_first"]
+    L = po.lib()
+    n = 4000
+    ints, fl = np.empty(n, np.int32), np.empty(n, np.float32)
+    for seed in (0, 42, 42 + 63, -7, 2 ** 40 + 12345):
+        L.orc_java_random_stream(seed, 0, 0, n, ints, fl)
+        r = PyJavaRandom(seed)
+        assert list(ints) == [r.nextInt() for _ in range(n)]
+        # bounds: power of two, small odd, the k-means++ sample counts, and one just above 2^30 (rejection loop taken often)
+        for bound in (1, 16, 1 << 30, 10, 2000, 10000, 5000, (1 << 30) + 1, 2 ** 31 - 1):
+            L.orc_java_random_stream(seed, 1, bound, n, ints, fl)
+            r = PyJavaRandom(seed)
+            assert list(ints) == [r.nextInt(bound) for _ in range(n)], (seed, bound)
+        L.orc_java_random_stream(seed, 2, 0, n, ints, fl)
+        r = PyJavaRandom(seed)
+        assert [float(x) for x in fl] == [float(r.nextFloat()) for _ in range(n)]
+    # literal values (from the anchored restatement above) kept in the test so a regression in BOTH is visible
+    L.orc_java_random_stream(42, 1, 256, 12, ints, fl)
+    assert list(ints[:12]) == [PyJavaRandom42_256[i] for i in range(12)]
+
+
+_r = PyJavaRandom(42)
+PyJavaRandom42_256 = [_r.nextInt(256) for _ in range(12)]
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# 4. direct PQ distance (a3, R5) against the compiled reference
+# ---------------------------------------------------------------------------------------------------------------------
+def test_pq_direct_distance_equals_compiled_reference(po):
+    if not po.ref_available():
+        pytest.skip("oracle/_ref not built (no /root/reference on this machine and no prebuilt library)")
+    n, dim, M = 600, 64, 8
+    X, Q = po.synth(42, n, dim), po.synth(43, 20, dim)
+    r = po.RefHnswPq(dim, 2 * n, M)
+    r.train(X[:400])
+    cb = r.codebooks()
+    codes = r.encode(X)
+    for i in range(n):
+        r.add(i, X[i])
+    R = po.ref()
+    for q in Q:
+        for node in range(0, n, 7):
+            want = R.ref_hnswpq_pq_distance(r.h, np.ascontiguousarray(q), node)           # HNSWPQIndex::computeDistancePQ
+            got = po.pq_direct(q, codes[node], cb)
+            assert np.float32(want).view(np.uint32) == np.float32(got).view(np.uint32), (node, want, got)
+    r.close()
