@@ -144,6 +144,21 @@ int vdb_merge_topk_device(const float* d_dists, const int32_t* d_ids, int32_t g,
 int vdb_distance_device(const float* d_a, const float* d_b, int64_t n, int32_t dim, int32_t metric, int32_t order,
                         float* d_out, void* stream);
 
+/* ---- no-allocation variant (no counterpart in the reference) ----
+ * Order-exact flat search (squared L2) over caller-owned DEVICE rows d_base[n][dim] for callers that cannot call cudaMalloc
+ * (CUDA graph capture, tight serving loops, harnesses that forbid it): same kernels and same answer as a VDB_INDEX_FLAT
+ * index (ids and distance bits, ties by id; global id = row number), but the call allocates NOTHING — no cudaMalloc /
+ * cudaFree / pinned memory, no allocating library routine. Its scratch (per-chunk candidate lists) lives in one fixed 8 MiB
+ * `static __device__` array inside the library, held by every GPU that loads the library until the process exits.
+ *   limits : nq * k <= ~340 000 (scratch), k <= 1024, dim <= 8192, nq <= 65535; larger requests fail with VDB_ERR_INVALID and
+ *            a message that states the limit.
+ *   sharing: every call on a GPU uses the same array and finds the previous call's contents in it (nothing needs clearing:
+ *            every slot that is read is written first by the same call). Calls that OVERLAP on one GPU — two streams, two
+ *            host threads — race on it: issue one call at a time per GPU, or order them on one stream.
+ *   device : the rows' device must be current (cudaSetDevice) in the calling thread; `order` = VDB_ARITH_*; `stream` as above. */
+int vdb_flat_search_noalloc_device(const float* d_base, int64_t n, int32_t dim, int32_t order, const float* d_queries, int64_t nq,
+                                   int32_t k, int32_t* d_out_ids, float* d_out_dists, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
