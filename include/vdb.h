@@ -72,7 +72,9 @@ typedef struct vdb_config {
     uint64_t level_seed;     /* seeded stand-in for ThreadLocalRandom level draws (HnswPqIndex.java:752-759) */
     int32_t trav_store;      /* HNSW*: rows read during traversal: 0 = bf16 copy (default), 1 = fp32 (strict order), 2 = fp8 e4m3 with a per-row power-of-two scale, 3 = int8 with a per-row scale (both opt-in, dim % 128 == 0) */
     int32_t trav_batch;      /* HNSW*: candidates expanded per round: 0 = auto (ef/128 in [4,32]; 64 from ef 4096), 1 = the Java pop order */
-    int32_t reserved1;
+    int32_t n_devices;       /* FLAT / PQ: GPUs of this box the rows are spread over by contiguous id range (0 or 1 = one GPU,
+                                `device`); devices device..device+n_devices-1 are used from ONE process: one vdb_search_batch
+                                fans the batch out to every shard and merges the lists (a JVM cannot run torchrun) */
     int32_t reserved2;
 } vdb_config;
 
@@ -110,6 +112,14 @@ int vdb_search_batch(vdb_index* idx, const float* queries, int64_t nq, int32_t k
  * also torch's default stream): no host copies, nothing is synchronised */
 int vdb_search_batch_device(vdb_index* idx, const float* d_queries, int64_t nq, int32_t k, int32_t* d_ids,
                             float* d_dists, void* stream);
+/* VectorIndex.removeVector (index/HnswPqIndex.java:542-596, HnswIndex.java:254-317): HNSW / HNSW_PQ only — the node's own
+ * lists are dropped, it is deleted from the lists of the nodes it links to, links pointing at it from elsewhere stay and are
+ * skipped by every walk (`!vectors.containsKey`), the entry point moves to the first live key in ConcurrentHashMap order.
+ * *removed = 1 when the id was present. FLAT / PQ: *removed = 0 (NativeIndex.removeVector answers false, NativeIndex.java:47-51) */
+int vdb_remove(vdb_index* idx, int32_t id, int32_t* removed);
+/* 1 when the id is stored and live (graph indexes; `vectors.containsKey(id)`, HnswPqIndex.java:157) */
+int vdb_contains(vdb_index* idx, int32_t id);
+/* live vectors (Java: vectors.size()) */
 int64_t vdb_size(const vdb_index* idx);
 int vdb_is_trained(const vdb_index* idx);
 int vdb_get_stats(vdb_index* idx, vdb_stats* out);

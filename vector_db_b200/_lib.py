@@ -19,7 +19,7 @@ SYMBOLS = [
     "vdb_build", "vdb_search_batch", "vdb_search_batch_device", "vdb_size", "vdb_is_trained", "vdb_get_stats",
     "vdb_set_codebooks", "vdb_get_codebooks", "vdb_get_codes", "vdb_set_codes", "vdb_set_graph", "vdb_get_graph",
     "vdb_max_level", "vdb_save", "vdb_load", "vdb_fill_synthetic", "vdb_encode_all", "vdb_pq_lut_device",
-    "vdb_adc_scan_device", "vdb_merge_topk_device", "vdb_distance_device", "vdb_flat_search_noalloc_device",
+    "vdb_adc_scan_device", "vdb_merge_topk_device", "vdb_distance_device", "vdb_flat_search_noalloc_device", "vdb_remove", "vdb_contains",
 ]
 
 
@@ -27,7 +27,7 @@ class VdbConfig(C.Structure):
     _fields_ = [(n, C.c_int32) for n in (
         "dim", "max_elements", "index_type", "metric", "arith", "hnsw_m", "ef_construction", "ef_search", "pq_m", "pq_bits",
         "pq_iters", "train_flavour", "rerank", "device", "id_offset", "search_ef_cap")] + [("level_seed", C.c_uint64)] + [
-        (n, C.c_int32) for n in ("trav_store", "trav_batch", "reserved1", "reserved2")]
+        (n, C.c_int32) for n in ("trav_store", "trav_batch", "n_devices", "reserved2")]
 
 
 class VdbStats(C.Structure):
@@ -64,6 +64,8 @@ def lib():
     L.vdb_search_batch.argtypes = [vp, vp, i64, i32, vp, vp]
     L.vdb_search_batch_device.argtypes = [vp, vp, i64, i32, vp, vp, vp]
     L.vdb_size.argtypes = [vp]; L.vdb_size.restype = i64
+    L.vdb_remove.argtypes = [vp, i32, C.POINTER(i32)]
+    L.vdb_contains.argtypes = [vp, i32]
     L.vdb_is_trained.argtypes = [vp]
     L.vdb_get_stats.argtypes = [vp, C.POINTER(VdbStats)]
     L.vdb_set_codebooks.argtypes = [vp, vp]

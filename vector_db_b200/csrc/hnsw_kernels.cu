@@ -104,10 +104,12 @@ __device__ __forceinline__ float pq_direct_dist(const HnswSearchParams& p, const
 
 // searchLayerClosest / searchLayerClosestCompressed (HnswPqIndex.java:761-827, HnswIndex.java:511-552): executed by
 // warp 0; lane j evaluates neighbour j, the first improving neighbour in list order wins (ballot + ffs == `break`).
+// `vis` holds only the removed-node bits at this point: a dead neighbour is skipped (`!vectors.containsKey`, HnswPqIndex.java:778)
+__device__ __forceinline__ bool node_dead(const uint32_t* vis, int nb) { return (vis[nb >> 5] >> (nb & 31)) & 1u; }
 __device__ int greedy_level(const HnswSearchParams& p, const float* sq, float qnorm, int cur, int level, bool compressed,
-                            unsigned long long& evals) {
+                            unsigned long long& evals, const uint32_t* vis) {
     const int lane = threadIdx.x & 31;
-    const int32_t* adjl = p.adj + (size_t)level * p.n * p.deg;
+    const int32_t* adjl = p.adj + (size_t)level * p.adj_stride * p.deg;
     float curd = 0.0f;
     if (lane == 0) curd = compressed ? pq_direct_dist(p, sq, cur) : exact_seq_dist(p, sq, qnorm, cur);
     curd = __shfl_sync(0xffffffffu, curd, 0);
@@ -117,6 +119,7 @@ __device__ int greedy_level(const HnswSearchParams& p, const float* sq, float qn
         for (int j0 = 0; j0 < p.deg && !moved; j0 += 32) {
             int j = j0 + lane;
             int nb = j < p.deg ? adjl[(size_t)cur * p.deg + j] : -1;
+            if (nb >= 0 && p.dead && node_dead(vis, nb)) nb = -1;
             float d = 0.0f;
             bool better = false;
             if (nb >= 0) {
@@ -177,9 +180,9 @@ __device__ __forceinline__ float pq_combine8(float ps, int lane) {      // parti
     for (int i = 1; i < 8; i++) total = __fadd_rn(total, __shfl_sync(0xffffffffu, ps, base + i));
     return total;
 }
-__device__ int greedy_level_pq(const HnswSearchParams& p, const float* sq, int cur, int level, GreedyShared& G) {
+__device__ int greedy_level_pq(const HnswSearchParams& p, const float* sq, int cur, int level, GreedyShared& G, const uint32_t* vis) {
     const int tid = threadIdx.x, lane = tid & 31;
-    const int32_t* adjl = p.adj + (size_t)level * p.n * p.deg;
+    const int32_t* adjl = p.adj + (size_t)level * p.adj_stride * p.deg;
     const int nbr = tid >> 3, part = tid & 7;
     {
         const float d = pq_combine8(pq_partial(p, sq, cur, part), lane);
@@ -193,7 +196,8 @@ __device__ int greedy_level_pq(const HnswSearchParams& p, const float* sq, int c
         __syncthreads();
         for (int j0 = 0; j0 < p.deg; j0 += HN_NT / 8) {
             const int j = j0 + nbr;
-            const int nb = j < p.deg ? __ldg(adjl + (size_t)cur * p.deg + j) : -1;
+            int nb = j < p.deg ? __ldg(adjl + (size_t)cur * p.deg + j) : -1;
+            if (nb >= 0 && p.dead && node_dead(vis, nb)) nb = -1;
             const float ps = nb >= 0 ? pq_partial(p, sq, nb, part) : 0.0f;
             const float d = pq_combine8(ps, lane);
             if (part == 0 && nb >= 0) { G.d[j] = d; if (d < curd) atomicMin(&G.best, j); }
@@ -859,7 +863,7 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
         __syncthreads();
         if (p.profile && tid == 0) S.tp = clock64();
         for (int i = tid; i < qpad; i += HN_NT) sq[i] = i < p.dim ? p.queries[(size_t)q * p.dim + i] : 0.0f;
-        for (int i = tid; i < vwords; i += HN_NT) vis[i] = 0u;
+        for (int i = tid; i < vwords; i += HN_NT) vis[i] = p.dead ? __ldg(p.dead + i) : 0u;
         __syncthreads();
         if (p.metric == 1) {
             if (tid == 0) S.qnorm = norm_java(sq, p.dim);
@@ -934,11 +938,11 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
         // ---- B. greedy descent on levels max_level-1 .. 1 (warp 0), then the entry point's layer-0 distance ----
         if ((p.metric == 0) && p.trained) {
             int cur = p.entry;
-            for (int l = p.max_level - 1; l > 0; l--) cur = greedy_level_pq(p, sq, cur, l, GS);
+            for (int l = p.max_level - 1; l > 0; l--) cur = greedy_level_pq(p, sq, cur, l, GS, vis);
             if (tid == 0) { fnode[0] = cur; S.nacc = 0; vis[cur >> 5] |= 1u << (cur & 31); }
         } else if (warp == 0) {
             int cur = p.entry;
-            for (int l = p.max_level - 1; l > 0; l--) cur = greedy_level(p, sq, qnorm, cur, l, false, evals);
+            for (int l = p.max_level - 1; l > 0; l--) cur = greedy_level(p, sq, qnorm, cur, l, false, evals, vis);
             if (lane == 0) { fnode[0] = cur; S.nacc = 0; vis[cur >> 5] |= 1u << (cur & 31); }
         }
         __syncthreads();
@@ -1269,6 +1273,20 @@ __global__ void make_traversal_rows_kernel(const float* __restrict__ base, int64
         a = warp_tree_sum(a);
         if (lane == 0 && tnorm) tnorm[r] = a;
     }
+}
+__global__ void scatter_adj_rows_kernel(int32_t* __restrict__ adj, const int32_t* __restrict__ payload, const uint64_t* __restrict__ targets,
+                                        int cnt, int deg, int64_t stride) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (int64_t)cnt * deg) return;
+    const int r = (int)(i / deg), j = (int)(i - (int64_t)r * deg);
+    const uint64_t t = targets[r];
+    adj[((size_t)(t >> 32) * stride + (uint32_t)t) * deg + j] = payload[i];
+}
+void launch_scatter_adj_rows(int32_t* d_adj, const int32_t* d_payload, const uint64_t* d_targets, int cnt, int deg, int64_t adj_stride,
+                             cudaStream_t st) {
+    if (cnt <= 0) return;
+    const int64_t tot = (int64_t)cnt * deg;
+    scatter_adj_rows_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(d_adj, d_payload, d_targets, cnt, deg, adj_stride);
 }
 void launch_make_traversal_rows(const float* d_base, int64_t n, int dim, int dpad, int mode, void* d_out, float* d_tnorm, float* d_tscale,
                                 cudaStream_t st) {

@@ -40,11 +40,13 @@ void HostGraph::init(int dim_, int M_, int max_elements, int metric_, uint64_t s
     // maxLevel = (int)(ln(maxElements)/ln(m)) + 1   (HnswPqIndex.java:89, HnswIndex.java:49)
     max_level = (int)(std::log((double)max_elements) / std::log((double)M)) + 1;
     if (max_level < 1) max_level = 1;
-    adj.assign(max_level, {}); deg.assign(max_level, {}); adjd.assign(max_level, {});
+    adj.assign(max_level, {}); deg.assign(max_level, {}); adjd.assign(max_level, {}); dirty_flag.assign(max_level, {});
     clear();
 }
 void HostGraph::clear() {
-    level.clear(); entry = -1; level_ctr = 0;
+    level.clear(); dead.clear(); entry = -1; level_ctr = 0;
+    dirty.clear(); all_dirty = true;
+    for (auto& f : dirty_flag) f.clear();
     for (auto& a : adj) a.clear();
     for (auto& d : deg) d.clear();
     for (auto& d : adjd) d.clear();
@@ -63,6 +65,7 @@ int HostGraph::draw_level() {
 void HostGraph::import_graph(const int32_t* levels, const int32_t* adj_in, int n, int entry_) {
     clear();
     level.assign(levels, levels + n);
+    dead.assign(n, 0);
     for (int l = 0; l < max_level; l++) {
         adj[l].assign(adj_in + (size_t)l * n * M, adj_in + (size_t)(l + 1) * n * M);
         deg[l].resize(n);
@@ -84,6 +87,7 @@ void HostGraph::insert(int index, int ef, int variant) {
     };
     const int lv = draw_level();
     level.push_back(lv);
+    dead.push_back(0);
     for (int l = 0; l < max_level; l++) { adj[l].resize((size_t)(index + 1) * M, -1); adjd[l].resize((size_t)(index + 1) * M, -1.0f); deg[l].push_back(0); }
     if ((int)visit.size() <= index) visit.resize(std::max<size_t>(1024, (size_t)(index + 1) * 2), 0);
     if (entry < 0) { entry = index; return; }
@@ -98,6 +102,7 @@ void HostGraph::insert(int index, int ef, int variant) {
             const int c = deg[l][cur];
             for (int j = 0; j < c; j++) {
                 int nb = adj[l][(size_t)cur * M + j];
+                if (dead[nb]) continue;                             // `!vectors.containsKey(neighborId)` (:778)
                 float d = dist(nb, index);
                 if (d < curd) { curd = d; cur = nb; changed = true; break; }
             }
@@ -122,14 +127,14 @@ void HostGraph::insert(int index, int ef, int variant) {
             // pull the unvisited neighbours' rows towards the core before the distance loop walks them one by one
             for (int j = 0; j < cn; j++) {
                 const int nb = adj[l][(size_t)c.idx * M + j];
-                if (visit[nb] != epoch) {
+                if (visit[nb] != epoch && !dead[nb]) {
                     const char* row = reinterpret_cast<const char*>(vecs + (size_t)nb * dim);
                     __builtin_prefetch(row); __builtin_prefetch(row + 64); __builtin_prefetch(row + 128); __builtin_prefetch(row + 192);
                 }
             }
             for (int j = 0; j < cn; j++) {
                 int nb = adj[l][(size_t)c.idx * M + j];
-                if (visit[nb] == epoch) continue;
+                if (visit[nb] == epoch || dead[nb]) continue;      // :869 visited or no longer stored
                 visit[nb] = epoch;
                 float d = dist(nb, index);
                 if ((int)results.size() < ef || d < furthest) {
@@ -145,8 +150,10 @@ void HostGraph::insert(int index, int ef, int variant) {
         for (int i = 0; i < (int)found.size() && i < M; i++) sel.push_back(found[i].idx);
         for (int j = 0; j < (int)sel.size(); j++) { adj[l][(size_t)index * M + j] = sel[j]; adjd[l][(size_t)index * M + j] = found[j].d; }
         deg[l][index] = (uint8_t)sel.size();
+        mark_dirty(l, index);
         for (int j = 0; j < (int)sel.size(); j++) {
             const int nb = sel[j];
+            mark_dirty(l, nb);
             const float dnew = found[j].d;                      // dist(nb, index) == dist(index, nb) bit for bit
             int c = deg[l][nb];
             if (c < M) { adj[l][(size_t)nb * M + c] = index; adjd[l][(size_t)nb * M + c] = dnew; deg[l][nb] = (uint8_t)(c + 1); continue; }
@@ -154,15 +161,50 @@ void HostGraph::insert(int index, int ef, int variant) {
             tmp.clear();
             for (int t = 0; t < c; t++) {
                 const int nn = adj[l][(size_t)nb * M + t];
+                if (dead[nn]) continue;                             // `nnVector != null` (:435-438): dangling links drop out here (the
+                                                                    // compressed path :514-517 has no null check and would abort the
+                                                                    // insert with an NPE — not reproduced)
                 float dd = adjd[l][(size_t)nb * M + t];
                 if (dd < 0.0f) dd = dist(nb, nn);               // imported graph: edge distance not cached yet
                 tmp.push_back({dd, nn});
             }
             tmp.push_back({dnew, index});
-            std::stable_sort(tmp.begin(), tmp.end(), [](const Nb& a, const Nb& b) { return a.d < b.d; });
-            for (int t = 0; t < M; t++) { adj[l][(size_t)nb * M + t] = tmp[t].idx; adjd[l][(size_t)nb * M + t] = tmp[t].d; }
+            // selectNeighbors (:1043-1064): at most M candidates are returned in the given order, more are stable-sorted
+            if ((int)tmp.size() > M) std::stable_sort(tmp.begin(), tmp.end(), [](const Nb& a, const Nb& b) { return a.d < b.d; });
+            const int keep = std::min<int>(M, (int)tmp.size());
+            for (int t = 0; t < M; t++) {
+                adj[l][(size_t)nb * M + t] = t < keep ? tmp[t].idx : -1;
+                adjd[l][(size_t)nb * M + t] = t < keep ? tmp[t].d : -1.0f;
+            }
+            deg[l][nb] = (uint8_t)keep;
         }
         cur = sel.empty() ? index : sel[0];
     }
     if (lv > level[entry]) entry = index;
+}
+
+void HostGraph::remove(int row, int new_entry) {
+    const int lv = level[row];
+    for (int l = 0; l <= lv && l < max_level; l++) {
+        const int c = deg[l][row];
+        for (int j = 0; j < c; j++) {
+            const int nb = adj[l][(size_t)row * M + j];
+            if (nb < 0 || nb == row) continue;
+            // neighborConnections.remove(Integer.valueOf(id)): first occurrence, later entries shift down
+            const int cn = deg[l][nb];
+            for (int t = 0; t < cn; t++) {
+                if (adj[l][(size_t)nb * M + t] != row) continue;
+                for (int u = t; u + 1 < cn; u++) { adj[l][(size_t)nb * M + u] = adj[l][(size_t)nb * M + u + 1]; adjd[l][(size_t)nb * M + u] = adjd[l][(size_t)nb * M + u + 1]; }
+                adj[l][(size_t)nb * M + cn - 1] = -1; adjd[l][(size_t)nb * M + cn - 1] = -1.0f;
+                deg[l][nb] = (uint8_t)(cn - 1);
+                mark_dirty(l, nb);
+                break;
+            }
+        }
+        for (int j = 0; j < M; j++) { adj[l][(size_t)row * M + j] = -1; adjd[l][(size_t)row * M + j] = -1.0f; }   // currentGraph.remove(id)
+        deg[l][row] = 0;
+        mark_dirty(l, row);
+    }
+    dead[row] = 1;
+    if (row == entry) entry = new_entry;
 }

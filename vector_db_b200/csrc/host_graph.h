@@ -16,6 +16,11 @@ struct HostGraph {
     std::vector<std::vector<uint8_t>> deg;   // [max_level][n]
     std::vector<std::vector<float>> adjd;    // [max_level] flat [n][M]: distance of each stored edge (< 0 = not known yet);
                                              // distances are symmetric bit for bit, so back-link pruning re-uses them
+    std::vector<uint8_t> dead;       // [n] 1 = removed (removeVector, HnswPqIndex.java:542-596): skipped like `!vectors.containsKey`
+    // rows whose adjacency changed since the last upload: (level << 32 | row), deduplicated through dirty_flag
+    std::vector<uint64_t> dirty;
+    std::vector<std::vector<uint8_t>> dirty_flag;   // [max_level][n]
+    bool all_dirty = true;           // everything must be uploaded (after clear / import / bulk build)
     // scratch
     std::vector<uint32_t> visit; uint32_t epoch = 0;
 
@@ -27,4 +32,18 @@ struct HostGraph {
     void insert(int index, int ef, int variant);
     // import an externally built graph: levels[n], adj_in[max_level][n][M]
     void import_graph(const int32_t* levels, const int32_t* adj_in, int n, int entry_);
+    // removeVector (HnswPqIndex.java:542-596 / HnswIndex.java:254-317): drop the node's own lists, delete it from the lists of
+    // the nodes IT links to (links pointing at it from elsewhere stay and are skipped by every walk), mark it dead.
+    // new_entry = the replacement entry point the caller computed (first live key in ConcurrentHashMap order), used when
+    // `row` is the entry point; -1 when no live node is left.
+    void remove(int row, int new_entry);
+    void mark_dirty(int l, int row) {
+        if (all_dirty) return;
+        if ((int)dirty_flag[l].size() <= row) dirty_flag[l].resize(level.size(), 0);
+        if (!dirty_flag[l][row]) { dirty_flag[l][row] = 1; dirty.push_back(((uint64_t)l << 32) | (uint32_t)row); }
+    }
+    void clear_dirty() {
+        for (uint64_t d : dirty) dirty_flag[(int)(d >> 32)][(uint32_t)d] = 0;
+        dirty.clear(); all_dirty = false;
+    }
 };

@@ -38,7 +38,9 @@ struct HnswSearchParams {
     const void* tbase;        // traversal rows [n][tstride bytes]: fp32 or bf16, zero-padded to a multiple of 8 elements
     const float* norms;       // [n] Java norm of the stored row (cosine), else nullptr
     const int32_t* ids;       // [n] external ids
-    const int32_t* adj;       // [max_level][n][deg], -1 padded
+    const int32_t* adj;       // [max_level][adj_stride][deg], -1 padded
+    const uint32_t* dead;     // [ceil(n/32)] bitmap of removed nodes (removeVector), or nullptr: pre-loaded into the visited bitset
+    int64_t adj_stride;       // rows per level of adj (>= n: capacity, so incremental adds do not move the levels)
     const uint8_t* codes;     // [n][pq_m] or nullptr
     const float* codebooks;   // [pq_m][256][sd] or nullptr
     const float* queries;     // [nq][dim]
@@ -60,6 +62,9 @@ struct HnswSearchParams {
 int launch_hnsw_search(const HnswSearchParams& p, int grid, cudaStream_t st);
 size_t hnsw_search_smem_bytes(const HnswSearchParams& p);
 int hnsw_max_batch(int deg);
+// write `cnt` changed adjacency rows (payload[cnt][deg]) to their (level, row) targets: target = level << 32 | row
+void launch_scatter_adj_rows(int32_t* d_adj, const int32_t* d_payload, const uint64_t* d_targets, int cnt, int deg, int64_t adj_stride,
+                             cudaStream_t st);
 void launch_make_traversal_rows(const float* d_base, int64_t n, int dim, int dpad, int mode /* 0 fp32, 1 bf16, 2 fp8, 3 int8 */, void* d_out, float* d_tnorm,
                                 float* d_tscale, cudaStream_t st);
 

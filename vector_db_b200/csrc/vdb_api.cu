@@ -10,6 +10,8 @@
 #include "kernels.h"
 #include "vdb_index.h"
 
+int vdb_validate_graph(const int32_t* levels, const int32_t* adj, int64_t n, int max_level, int M, int32_t entry);
+
 static thread_local std::string g_err;
 void vdb_set_error(const std::string& msg) { g_err = msg; }
 #define FAIL(code, msg) do { vdb_set_error(msg); return (code); } while (0)
@@ -98,6 +100,7 @@ extern "C" int vdb_destroy(vdb_index* x) {
     x->d_fmirror.release(); x->d_fab.release(); x->d_fcolsum.release(); x->d_fq.release(); x->d_fqf.release(); x->d_fscores.release(); x->d_ftau.release();
     x->d_fqstat.release(); x->d_fcnt.release(); x->d_fcand.release(); x->d_fslab_d.release(); x->d_fslab_i.release();
     x->d_train.release(); x->d_sub.release(); x->d_mind.release(); x->d_asg.release();
+    x->d_dead.release(); x->d_adj_payload.release(); x->d_adj_targets.release();
     x->p_q.release(); x->p_d.release(); x->p_ids.release();
     if (x->ev_total0) { cudaEventDestroy(x->ev_total0); cudaEventDestroy(x->ev_total1); cudaEventDestroy(x->ev_k0); cudaEventDestroy(x->ev_k1); }
     if (x->stream) cudaStreamDestroy(x->stream);
@@ -105,7 +108,8 @@ extern "C" int vdb_destroy(vdb_index* x) {
     return VDB_OK;
 }
 
-extern "C" int64_t vdb_size(const vdb_index* x) { return x ? x->n : -1; }
+static inline bool is_graph(const vdb_index* x) { return x->cfg.index_type == VDB_INDEX_HNSW || x->cfg.index_type == VDB_INDEX_HNSW_PQ; }
+extern "C" int64_t vdb_size(const vdb_index* x) { return x ? (is_graph(x) ? x->n_live : x->n) : -1; }   // Java: vectors.size()
 extern "C" int vdb_is_trained(const vdb_index* x) { return x && x->trained ? 1 : 0; }
 extern "C" int32_t vdb_max_level(const vdb_index* x) { return x ? x->g.max_level : 0; }
 
@@ -208,11 +212,59 @@ static int encode_pending(vdb_index* x) {
 static int upload_graph(vdb_index* x) {
     const int64_t n = x->g.size();
     const int L = x->g.max_level, M = x->g.M;
-    VDB_TRY(x->d_adj.ensure((size_t)L * n * M, 0, x->stream));
-    for (int l = 0; l < L; l++)
-        VDB_CUDA(cudaMemcpyAsync(x->d_adj.p + (size_t)l * n * M, x->g.adj[l].data(), (size_t)n * M * 4, cudaMemcpyHostToDevice, x->stream));
+    const bool grow = n > x->adj_cap;
+    if (grow || x->g.all_dirty || (int64_t)x->g.dirty.size() * 8 > n) {
+        // full upload; capacity grows geometrically so the level offsets stay put across incremental adds
+        if (grow) x->adj_cap = std::min<int64_t>(std::max<int64_t>(x->cfg.max_elements, n), std::max<int64_t>(1024, n + n / 2));
+        VDB_TRY(x->d_adj.ensure((size_t)L * x->adj_cap * M, 0, x->stream));
+        for (int l = 0; l < L; l++)
+            VDB_CUDA(cudaMemcpyAsync(x->d_adj.p + (size_t)l * x->adj_cap * M, x->g.adj[l].data(), (size_t)n * M * 4, cudaMemcpyHostToDevice, x->stream));
+    } else if (!x->g.dirty.empty()) {
+        // only the rows an insert / remove touched (the new node's lists + <= M back-links per level): one payload, one scatter
+        const size_t cnt = x->g.dirty.size();
+        std::vector<int32_t> payload(cnt * M);
+        for (size_t i = 0; i < cnt; i++) {
+            const int l = (int)(x->g.dirty[i] >> 32); const uint32_t row = (uint32_t)x->g.dirty[i];
+            std::memcpy(&payload[i * M], &x->g.adj[l][(size_t)row * M], (size_t)M * 4);
+        }
+        VDB_TRY(x->d_adj_payload.ensure(cnt * M, 0, x->stream));
+        VDB_TRY(x->d_adj_targets.ensure(cnt, 0, x->stream));
+        VDB_CUDA(cudaMemcpyAsync(x->d_adj_payload.p, payload.data(), payload.size() * 4, cudaMemcpyHostToDevice, x->stream));
+        VDB_CUDA(cudaMemcpyAsync(x->d_adj_targets.p, x->g.dirty.data(), cnt * 8, cudaMemcpyHostToDevice, x->stream));
+        launch_scatter_adj_rows(x->d_adj.p, x->d_adj_payload.p, x->d_adj_targets.p, (int)cnt, M, x->adj_cap, x->stream);
+        VDB_CUDA(cudaGetLastError());
+    }
     VDB_CUDA(cudaStreamSynchronize(x->stream));
+    x->g.clear_dirty();
     x->graph_uploaded = true;
+    return VDB_OK;
+}
+static int upload_dead(vdb_index* x) {
+    if (!x->dead_dirty) return VDB_OK;
+    const int64_t n = x->g.size();
+    std::vector<uint32_t> w((size_t)(n + 31) / 32, 0u);
+    for (int64_t i = 0; i < n; i++) if (x->g.dead[i]) w[i >> 5] |= 1u << (i & 31);
+    VDB_TRY(x->d_dead.ensure(w.size(), 0, x->stream));
+    VDB_CUDA(cudaMemcpyAsync(x->d_dead.p, w.data(), w.size() * 4, cudaMemcpyHostToDevice, x->stream));
+    VDB_CUDA(cudaStreamSynchronize(x->stream));
+    x->dead_dirty = false;
+    return VDB_OK;
+}
+// rows that share a Java code-row index with a newly inserted (trained-phase) row get that row's code (vdb_index.h: h_jindex)
+static int propagate_shared_codes(vdb_index* x, int64_t from_row) {
+    if (!x->any_dead || !x->trained) return VDB_OK;
+    const int M = x->pq_m;
+    for (int64_t r = from_row; r < x->n; r++) {
+        const int64_t j = x->h_jindex[r];
+        if (r >= x->raw_rows) {
+            auto range = x->jindex_rows.equal_range(j);
+            for (auto it = range.first; it != range.second; ++it)
+                if (it->second != r)
+                    VDB_CUDA(cudaMemcpyAsync(x->d_codes.p + (size_t)it->second * M, x->d_codes.p + (size_t)r * M, (size_t)M, cudaMemcpyDeviceToDevice, x->stream));
+        }
+        x->jindex_rows.emplace(j, r);
+    }
+    VDB_CUDA(cudaStreamSynchronize(x->stream));
     return VDB_OK;
 }
 
@@ -222,10 +274,12 @@ static int sync_index(vdb_index* x) {
     const int t = x->cfg.index_type;
     if (t == VDB_INDEX_HNSW || t == VDB_INDEX_HNSW_PQ) {
         if (x->device_only) FAIL(VDB_ERR_INVALID, "graph indexes need host rows (vdb_fill_synthetic is for FLAT/PQ)");
+        const int64_t first_new = x->n_indexed;
         if (x->n_indexed < x->n) {
             x->g.vecs = x->h_vecs.data(); x->g.norms = x->h_norms.data();
             const int dim = x->cfg.dim;
             for (int64_t i = x->n_indexed; i < x->n; i++) {
+                if ((int64_t)x->h_jindex.size() <= i) x->h_jindex.push_back(x->java_size++);     // index = currentSize++ (:393,:467)
                 int ef = x->cfg.ef_construction, variant = 2;
                 if (t == VDB_INDEX_HNSW_PQ) {
                     variant = 1;
@@ -248,8 +302,9 @@ static int sync_index(vdb_index* x) {
         }
         VDB_TRY(upload_rows(x));
         VDB_TRY(build_traversal_rows(x));
-        if (t == VDB_INDEX_HNSW_PQ) VDB_TRY(encode_pending(x));
+        if (t == VDB_INDEX_HNSW_PQ) { VDB_TRY(encode_pending(x)); VDB_TRY(propagate_shared_codes(x, first_new)); }
         if (!x->graph_uploaded) VDB_TRY(upload_graph(x));
+        VDB_TRY(upload_dead(x));
     } else {
         VDB_TRY(upload_rows(x));
         if (t == VDB_INDEX_PQ) VDB_TRY(encode_pending(x));
@@ -264,9 +319,32 @@ extern "C" int vdb_add_batch(vdb_index* x, const int32_t* ids, const float* vecs
     if (x->device_only) FAIL(VDB_ERR_INVALID, "index holds device-generated rows; host adds are not allowed");
     if (x->cfg.index_type == VDB_INDEX_PQ && !x->trained)
         FAIL(VDB_ERR_UNTRAINED, "PQ index must be trained before adding vectors");    // PQIndex.cpp:124-126
-    if (x->n + cnt > x->cfg.max_elements) FAIL(VDB_ERR_FULL, "max_elements exceeded");   // VectorStore.cpp:40-43
     VDB_CUDA(cudaSetDevice(x->cfg.device));
     const int dim = x->cfg.dim;
+    std::vector<float> kept_v; std::vector<int32_t> kept_i;
+    if (is_graph(x)) {
+        // addVector answers false for an id that is already stored (HnswPqIndex.java:157-159, HnswIndex.java:144-146): skipped
+        std::vector<int64_t> keep;
+        for (int64_t i = 0; i < cnt; i++) {
+            const int32_t id = ids ? ids[i] : (int32_t)(x->cfg.id_offset + x->n + i);
+            if (x->id2row.count(id)) continue;
+            x->id2row[id] = x->n + (int64_t)keep.size();
+            keep.push_back(i);
+        }
+        if (x->n_live + (int64_t)keep.size() > x->cfg.max_elements) {      // `vectors.size() >= maxElements` (:161-163)
+            for (int64_t i : keep) x->id2row.erase(ids ? ids[i] : (int32_t)(x->cfg.id_offset + x->n + i));
+            FAIL(VDB_ERR_FULL, "max_elements exceeded");
+        }
+        if ((int64_t)keep.size() != cnt || !ids) {
+            kept_v.resize(keep.size() * (size_t)dim); kept_i.resize(keep.size());
+            for (size_t t = 0; t < keep.size(); t++) {
+                std::memcpy(&kept_v[t * dim], vecs + (size_t)keep[t] * dim, (size_t)dim * 4);
+                kept_i[t] = ids ? ids[keep[t]] : (int32_t)(x->cfg.id_offset + x->n + keep[t]);
+            }
+            vecs = kept_v.data(); ids = kept_i.data(); cnt = (int64_t)keep.size();
+        }
+        x->n_live += cnt;
+    } else if (x->n + cnt > x->cfg.max_elements) FAIL(VDB_ERR_FULL, "max_elements exceeded");   // VectorStore.cpp:40-43
     const size_t old = x->h_vecs.size();
     x->h_vecs.insert(x->h_vecs.end(), vecs, vecs + (size_t)cnt * dim);
     for (int64_t i = 0; i < cnt; i++) x->h_ids.push_back(ids ? ids[i] : (int32_t)(x->cfg.id_offset + x->n + i));
@@ -282,6 +360,55 @@ extern "C" int vdb_add_batch(vdb_index* x, const int32_t* ids, const float* vecs
         VDB_CUDA(cudaStreamSynchronize(x->stream));
     }
     x->n += cnt;
+    return VDB_OK;
+}
+
+// first live key of Java's `vectors` map in iteration order, skipping `skip_id` (HnswPqIndex.java:577-584). The map is a
+// ConcurrentHashMap<>(maxElements): table = tableSizeFor(1.5 * maxElements + 1) bins and never resizes (<= maxElements entries
+// stay below the 0.75 load factor); bin = spread(hash) & (table - 1) with spread(h) = (h ^ (h >>> 16)) & 0x7fffffff and
+// Integer.hashCode() = the value; bins are walked in ascending order, entries of one bin in insertion order.
+static int64_t java_first_live_row(const vdb_index* x, int32_t skip_id) {
+    uint64_t want = (uint64_t)x->cfg.max_elements + ((uint64_t)x->cfg.max_elements >> 1) + 1, table = 1;
+    while (table < want && table < (1ull << 30)) table <<= 1;
+    int64_t best_row = -1; uint64_t best_bin = ~0ull;
+    for (const auto& kv : x->id2row) {
+        if (kv.first == skip_id) continue;
+        const uint32_t h = (uint32_t)kv.first;
+        const uint64_t bin = ((h ^ (h >> 16)) & 0x7fffffffu) & (table - 1);
+        if (bin < best_bin || (bin == best_bin && kv.second < best_row)) { best_bin = bin; best_row = kv.second; }
+    }
+    return best_row;
+}
+
+extern "C" int vdb_contains(vdb_index* x, int32_t id) {
+    if (!x) return 0;
+    std::lock_guard<std::mutex> lk(x->mu);
+    if (is_graph(x)) return x->id2row.count(id) ? 1 : 0;
+    for (int64_t i = 0; i < (int64_t)x->h_ids.size(); i++) if (x->h_ids[i] == id) return 1;
+    return 0;
+}
+
+extern "C" int vdb_remove(vdb_index* x, int32_t id, int32_t* removed) {
+    if (!x) FAIL(VDB_ERR_INVALID, "vdb_remove: null index");
+    if (removed) *removed = 0;
+    std::lock_guard<std::mutex> lk(x->mu);
+    if (!is_graph(x)) return VDB_OK;                                  // NativeIndex.removeVector -> false (NativeIndex.java:47-51)
+    auto it = x->id2row.find(id);
+    if (it == x->id2row.end()) return VDB_OK;                         // `!vectors.containsKey(id)` -> false (:545-547)
+    VDB_TRY(sync_index(x));                                           // everything added before this call is in the graph
+    const int64_t row = it->second;
+    if (!x->any_dead) {                                               // first removal: index the Java code rows handed out so far
+        x->jindex_rows.clear();
+        for (int64_t r = 0; r < (int64_t)x->h_jindex.size(); r++) x->jindex_rows.emplace(x->h_jindex[r], r);
+    }
+    int64_t new_entry = -1;
+    if (row == x->g.entry && x->n_live > 1) new_entry = java_first_live_row(x, id);
+    x->g.remove((int)row, (int)new_entry);
+    x->id2row.erase(it);
+    x->n_live--;
+    if (x->cfg.index_type == VDB_INDEX_HNSW_PQ) x->java_size--;       // currentSize-- (:591); HnswIndex keeps no such counter
+    x->any_dead = true; x->dead_dirty = true; x->graph_uploaded = false;
+    if (removed) *removed = 1;
     return VDB_OK;
 }
 
@@ -338,12 +465,30 @@ extern "C" int vdb_encode_all(vdb_index* x) {
     return encode_pending(x);
 }
 
+// every level in [0, max_level), every neighbour and the entry point inside [-1, n): a bad id would become an out-of-bounds
+// shared-memory atomic in the beam kernel (sticky CUDA fault), so imported graphs are checked on the host first
+int vdb_validate_graph(const int32_t* levels, const int32_t* adj, int64_t n, int max_level, int M, int32_t entry) {
+    if (n < 0 || entry < -1 || entry >= n) FAIL(VDB_ERR_INVALID, "graph: entry point out of range");
+    for (int64_t i = 0; i < n; i++)
+        if (levels[i] < 0 || levels[i] >= max_level) FAIL(VDB_ERR_INVALID, "graph: node level out of range");
+    const size_t tot = (size_t)max_level * n * M;
+    for (size_t i = 0; i < tot; i++)
+        if (adj[i] < -1 || adj[i] >= n) FAIL(VDB_ERR_INVALID, "graph: neighbour id out of range");
+    return VDB_OK;
+}
+
 extern "C" int vdb_set_graph(vdb_index* x, const int32_t* levels, const int32_t* adj, int32_t max_level, int32_t entry) {
     if (!x || !levels || !adj) FAIL(VDB_ERR_INVALID, "vdb_set_graph: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
+    if (!is_graph(x)) FAIL(VDB_ERR_INVALID, "vdb_set_graph: not a graph index");
     if (max_level != x->g.max_level) FAIL(VDB_ERR_INVALID, "max_level mismatch");
-    x->g.import_graph(levels, adj, (int)x->n, entry);
+    VDB_TRY(vdb_validate_graph(levels, adj, x->n, max_level, x->g.M, entry));
+    try { x->g.import_graph(levels, adj, (int)x->n, entry); }
+    catch (const std::exception& e) { FAIL(VDB_ERR_INVALID, std::string("vdb_set_graph: ") + e.what()); }
     x->n_indexed = x->n; x->graph_uploaded = false;
+    x->h_jindex.resize(x->n);
+    for (int64_t r = 0; r < x->n; r++) x->h_jindex[r] = r;
+    x->java_size = x->n; x->any_dead = false; x->dead_dirty = false; x->jindex_rows.clear();
     return VDB_OK;
 }
 extern "C" int vdb_get_graph(vdb_index* x, int32_t* levels, int32_t* adj, int32_t* entry) {
@@ -376,6 +521,21 @@ extern "C" int vdb_build(vdb_index* x) {
         }
         if (x->n_train > 0) VDB_TRY(train_on_device(x, x->h_train.data(), x->n_train));
     }
+    // buildIndex re-adds `new HashMap<>(vectors)` (:687): removed vectors are gone for good — compact the store first
+    if (x->any_dead) {
+        int64_t w = 0;
+        for (int64_t r = 0; r < x->n; r++) {
+            if (x->g.dead[r]) continue;
+            if (w != r) {
+                std::memmove(&x->h_vecs[(size_t)w * dim], &x->h_vecs[(size_t)r * dim], (size_t)dim * 4);
+                x->h_ids[w] = x->h_ids[r];
+                if (!x->h_norms.empty()) x->h_norms[w] = x->h_norms[r];
+            }
+            w++;
+        }
+        x->n = w; x->h_vecs.resize((size_t)w * dim); x->h_ids.resize(w);
+        if (!x->h_norms.empty()) x->h_norms.resize(w);
+    }
     // reorder the store by id (stable), as buildIndex sorts the saved vectors by id before re-adding
     std::vector<int64_t> order(x->n);
     std::iota(order.begin(), order.end(), 0);
@@ -395,6 +555,9 @@ extern "C" int vdb_build(vdb_index* x) {
     }
     x->g.clear();
     x->n_indexed = 0; x->n_dev = 0; x->n_trav = 0; x->n_fmirror = 0; x->n_coded = 0; x->raw_rows = 0; x->codes_overridden = false;
+    x->id2row.clear();
+    for (int64_t r = 0; r < x->n; r++) x->id2row[x->h_ids[r]] = r;
+    x->n_live = x->n; x->any_dead = false; x->dead_dirty = false; x->h_jindex.clear(); x->java_size = 0; x->jindex_rows.clear();
     return sync_index(x);
 }
 
@@ -435,14 +598,16 @@ static int search_graph(vdb_index* x, const float* d_q, int64_t nq, int k, int32
     p.codes = pq && x->trained ? x->d_codes.p : nullptr; p.codebooks = pq && x->trained ? x->d_cb.p : nullptr;
     p.queries = d_q; p.out_ids = d_ids; p.out_dists = d_dists; p.counters = x->d_counters.p;
     p.n = (int)x->n; p.dim = x->cfg.dim; p.deg = x->g.M; p.max_level = x->g.max_level; p.entry = x->g.entry;
+    p.adj_stride = x->adj_cap; p.dead = x->any_dead ? x->d_dead.p : nullptr;
+    const int64_t live = x->n_live;                                             // Java: dataSize = vectors.size() (:615)
     p.pq_m = x->pq_m; p.trained = pq && x->trained ? 1 : 0;
     p.metric = pq ? 0 : 1;
     if (pq) {
-        const int sef = java_search_ef(x->n, k, x->cfg.ef_search, x->cfg.search_ef_cap);
+        const int sef = java_search_ef(live, k, x->cfg.ef_search, x->cfg.search_ef_cap);
         if (x->trained) { p.variant = 0; p.ef = std::max(sef, k * 100); }     // :638-640 searchLayerWithSize
         else { p.variant = 1; p.ef = sef; }                                    // :643 searchLayer
     } else { p.variant = 2; p.ef = std::max(x->cfg.ef_search, k * 4); }        // HnswIndex.java:347
-    p.ef = (int)std::min<int64_t>(p.ef, std::max<int64_t>(x->n, 1));
+    p.ef = (int)std::min<int64_t>(p.ef, std::max<int64_t>(live, 1));
     p.k = k; p.nq = (int)nq;
     p.tbase = x->d_trav.p; p.tnorm = x->d_tnorm.p; p.tscale = x->d_tscale.p; p.tstride = trav_stride(x); p.tstore = trav_mode(x);
     // candidates expanded per round: ~1.5 % of the beam keeps >= 99 % of the ids equal to the Java pop order (tests) and halves the
@@ -615,7 +780,7 @@ static int search_device_locked(vdb_index* x, const float* d_q, int64_t nq, int 
     x->timed = true;
     cudaEventRecord(x->ev_total0, st);
     int rc;
-    if (x->n == 0 || (x->g.entry < 0 && (x->cfg.index_type == VDB_INDEX_HNSW || x->cfg.index_type == VDB_INDEX_HNSW_PQ))) {
+    if (x->n == 0 || (is_graph(x) && (x->g.entry < 0 || x->n_live == 0))) {
         launch_keys_to_results(nullptr, 0, k, nq, d_ids, d_dists, st);     // empty index -> empty lists (HnswIndexTest.java:120-129)
         cudaEventRecord(x->ev_k0, st); cudaEventRecord(x->ev_k1, st);
         rc = VDB_OK;

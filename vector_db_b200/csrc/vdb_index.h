@@ -5,6 +5,7 @@
 #include <cstdint>
 #include <mutex>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "../../include/vdb.h"
@@ -102,6 +103,21 @@ struct vdb_index {
     HostGraph g;
     int64_t n_indexed = 0;          // rows inserted into the graph
     bool graph_uploaded = false;
+    int64_t adj_cap = 0;            // rows per level of d_adj (capacity: grows geometrically, levels keep their offsets in between)
+    // live set of a graph index (Java: the `vectors` map). Rows are never reused; a removed row stays as a dead node.
+    std::unordered_map<int32_t, int64_t> id2row;
+    int64_t n_live = 0;
+    bool dead_dirty = false;        // g.dead changed since d_dead was uploaded
+    bool any_dead = false;
+    DevBuf<uint32_t> d_dead;        // [ceil(n/32)] bitmap
+    // Java `currentSize` / idToIndex (HnswPqIndex.java:393,467,589-591): the code row of a vector is currentSize at insert
+    // time and currentSize is DEcremented by removeVector, so an insert after a removal overwrites the code row of an earlier
+    // vector. Reproduced: h_jindex[row] = that index, rows sharing one index share the latest code.
+    std::vector<int64_t> h_jindex;
+    int64_t java_size = 0;
+    std::unordered_multimap<int64_t, int64_t> jindex_rows;   // built at the first removal
+    DevBuf<int32_t> d_adj_payload;  // incremental adjacency upload: changed rows + their (level,row) targets
+    DevBuf<uint64_t> d_adj_targets;
 
     // search scratch
     DevBuf<float> d_q, d_out_d, d_lut, d_lutg;

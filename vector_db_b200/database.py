@@ -170,8 +170,11 @@ class VectorDatabase:
         return self._vectors.get(id_)
 
     def deleteVector(self, id_):
-        # the GPU index mirrors NativeIndex.removeVector -> false (NativeIndex.java:47-51)
-        return False
+        """core/VectorDatabase.java:192-205: remove from the storage first (false when absent), then from the index."""
+        if id_ not in self._vectors:
+            return False
+        del self._vectors[id_]
+        return self.index.removeVector(int(id_))
 
     def search(self, query, k):
         q = np.asarray(query, dtype=np.float32)

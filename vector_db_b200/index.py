@@ -86,6 +86,8 @@ class GpuIndex:
         v = _f32(values)
         if v.ndim != 1 or v.size != self.dimension:
             raise ValueError("Vector dimension mismatch: expected %d, got %d" % (self.dimension, v.size))
+        if self.index_type in (INDEX_HNSW, INDEX_HNSW_PQ) and self.contains(vid):
+            return False                                                     # HnswPqIndex.java:157-159
         try:
             self.addBatch(np.array([vid], dtype=np.int32), v.reshape(1, -1))
         except VdbError as e:
@@ -107,7 +109,14 @@ class GpuIndex:
         check(_lib.lib().vdb_add_batch(self._h, idp, v.ctypes.data, v.shape[0]))
 
     def removeVector(self, id_):
-        return False                                                         # NativeIndex.java:47-51
+        """VectorIndex.removeVector: graph indexes follow HnswPqIndex.java:542-596; FLAT / PQ answer False like
+        NativeIndex.removeVector (NativeIndex.java:47-51)."""
+        removed = C.c_int32(0)
+        check(_lib.lib().vdb_remove(self._h, int(id_), C.byref(removed)))
+        return bool(removed.value)
+
+    def contains(self, id_):
+        return bool(_lib.lib().vdb_contains(self._h, int(id_)))
 
     def train(self, samples):
         s = _f32(samples)
