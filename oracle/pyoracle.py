@@ -343,6 +343,99 @@ class OracleHnsw:
 
 
 # ------------------------------------------------------------------------------------------------
+# VDBSNAP2 — the snapshot format of vdb_save / vdb_load (vector_db_b200/csrc/snapshot.cu), read and written here so that
+# the CPU oracle and the GPU library load "the same persisted graph and codebooks" from ONE file (SURVEY.md §8f rank 2;
+# the reference's own save()/load() are empty: native/index/HNSWPQIndex.cpp:774-780, VectorIndex.h:21-25).
+# ------------------------------------------------------------------------------------------------
+_CFG_FIELDS = ["dim", "max_elements", "index_type", "metric", "arith", "hnsw_m", "ef_construction", "ef_search", "pq_m", "pq_bits",
+               "pq_iters", "train_flavour", "rerank", "device", "id_offset", "search_ef_cap"]
+_CFG_DTYPE = np.dtype([(n, "<i4") for n in _CFG_FIELDS] + [("level_seed", "<u8")] +
+                      [(n, "<i4") for n in ("trav_store", "trav_batch", "n_devices", "reserved2")])
+_HDR_DTYPE = np.dtype([("n", "<i8"), ("trained", "<i4"), ("max_level", "<i4"), ("entry", "<i4"), ("any_dead", "<i4"), ("raw_rows", "<i8"),
+                       ("level_ctr", "<u8"), ("n_train", "<i8"), ("java_size", "<i8"), ("n_coded", "<i8")])
+
+
+def snapshot_read(path):
+    """-> dict(cfg, hdr, ids, vectors, norms, codebooks, codes, samples, levels, adj[max_level][n][deg], dead, jindex)"""
+    with open(path, "rb") as f:
+        if f.read(8) != b"VDBSNAP2":
+            raise ValueError("not a VDBSNAP2 snapshot")
+        cfg_bytes = int(np.frombuffer(f.read(4), "<u4")[0])
+        if cfg_bytes != _CFG_DTYPE.itemsize:
+            raise ValueError("vdb_config size mismatch: %d != %d" % (cfg_bytes, _CFG_DTYPE.itemsize))
+        cfg = np.frombuffer(f.read(cfg_bytes), _CFG_DTYPE)[0]
+        hdr = np.frombuffer(f.read(_HDR_DTYPE.itemsize), _HDR_DTYPE)[0]
+        n, dim, M = int(hdr["n"]), int(cfg["dim"]), int(cfg["pq_m"])
+        rd = lambda dt, cnt: np.frombuffer(f.read(np.dtype(dt).itemsize * cnt), dt, cnt).copy()
+        out = {"cfg": cfg, "hdr": hdr, "ids": rd("<i4", n), "vectors": rd("<f4", n * dim).reshape(n, dim)}
+        out["norms"] = rd("<f4", n) if int(cfg["metric"]) == 1 else None
+        uses_pq = int(cfg["index_type"]) in (1, 3) and M > 0
+        out["codebooks"] = out["codes"] = out["samples"] = None
+        if uses_pq and int(hdr["trained"]):
+            out["codebooks"] = rd("<f4", M * 256 * (dim // M)).reshape(M, 256, dim // M)
+            out["codes"] = rd("u1", n * M).reshape(n, M)
+        elif uses_pq:
+            out["samples"] = rd("<f4", int(hdr["n_train"]) * dim).reshape(-1, dim)
+        if int(cfg["index_type"]) in (2, 3):
+            L, deg = int(hdr["max_level"]), int(cfg["hnsw_m"])
+            out["levels"] = rd("<i4", n)
+            out["adj"] = rd("<i4", L * n * deg).reshape(L, n, deg)
+            out["dead"] = rd("u1", n)
+            out["jindex"] = rd("<i8", n)
+        if f.read(1):
+            raise ValueError("trailing bytes in snapshot")
+    return out
+
+
+def snapshot_write(path, snap):
+    with open(path, "wb") as f:
+        f.write(b"VDBSNAP2")
+        f.write(np.array([_CFG_DTYPE.itemsize], "<u4").tobytes())
+        f.write(np.array([snap["cfg"]], _CFG_DTYPE).tobytes())
+        f.write(np.array([snap["hdr"]], _HDR_DTYPE).tobytes())
+        for key, dt in (("ids", "<i4"), ("vectors", "<f4"), ("norms", "<f4"), ("codebooks", "<f4"), ("codes", "u1"), ("samples", "<f4"),
+                        ("levels", "<i4"), ("adj", "<i4"), ("dead", "u1"), ("jindex", "<i8")):
+            if snap.get(key) is not None:
+                f.write(np.ascontiguousarray(snap[key], dtype=dt).tobytes())
+
+
+def oracle_from_snapshot(path):
+    """build an OracleHnsw holding exactly the state a vdb_save file describes (graph indexes)"""
+    s = snapshot_read(path)
+    cfg, hdr = s["cfg"], s["hdr"]
+    kind = KIND_HNSWPQ if int(cfg["index_type"]) == 3 else KIND_HNSW
+    o = OracleHnsw(kind, int(cfg["dim"]), int(cfg["max_elements"]), M=int(cfg["hnsw_m"]), efC=int(cfg["ef_construction"]),
+                   ef=int(cfg["ef_search"]), pq_m=int(cfg["pq_m"]) if kind == KIND_HNSWPQ else 0, pq_iters=int(cfg["pq_iters"]),
+                   level_seed=int(cfg["level_seed"]))
+    o.import_state(s["vectors"], s["levels"], s["adj"], int(hdr["entry"]), ids=s["ids"], codebooks=s["codebooks"], codes=s["codes"])
+    lib().orc_hnsw_set_dead(o.h, np.ascontiguousarray(s["dead"]), np.ascontiguousarray(s["jindex"]), int(hdr["java_size"]), int(hdr["level_ctr"]))
+    return o
+
+
+def oracle_to_snapshot(o, path, max_elements, ef_construction, ef_search, pq_iters=25, level_seed=1234):
+    """write the oracle's state as a VDBSNAP2 file vdb_load accepts (graph indexes, trained or compression off)"""
+    n = o.size
+    hnswpq = o.kind == KIND_HNSWPQ
+    cfg = np.zeros((), _CFG_DTYPE)
+    cfg["dim"], cfg["max_elements"], cfg["index_type"], cfg["metric"] = o.dim, max_elements, 3 if hnswpq else 2, 0 if hnswpq else 1
+    cfg["hnsw_m"], cfg["ef_construction"], cfg["ef_search"] = o.M, ef_construction, ef_search
+    cfg["pq_m"], cfg["pq_bits"], cfg["pq_iters"], cfg["level_seed"] = (o.pq_m if hnswpq else 0), 8, pq_iters, level_seed
+    dead = o.dead()
+    jindex = np.zeros(n, dtype=np.int64)
+    lib().orc_hnsw_get_jindex(o.h, jindex)
+    hdr = np.zeros((), _HDR_DTYPE)
+    trained = hnswpq and o.trained
+    hdr["n"], hdr["trained"], hdr["max_level"], hdr["entry"], hdr["any_dead"] = n, int(trained), o.max_level, o.entry, int(dead.any())
+    hdr["level_ctr"], hdr["java_size"], hdr["n_coded"] = lib().orc_hnsw_level_ctr(o.h), lib().orc_hnsw_java_size(o.h), n if trained else 0
+    levels, adj, _ = o.export_graph()
+    snap = {"cfg": cfg, "hdr": hdr, "ids": o.ext_ids(), "vectors": o.vectors(), "norms": o.norms() if not hnswpq else None,
+            "codebooks": o.codebooks() if trained else None, "codes": o.codes() if trained else None,
+            "samples": np.zeros((0, o.dim), np.float32) if (hnswpq and not trained) else None,
+            "levels": levels, "adj": np.stack(adj, 0), "dead": dead, "jindex": jindex}
+    snapshot_write(path, snap)
+
+
+# ------------------------------------------------------------------------------------------------
 # compiled reference (oracle/_ref) — present only where `make -C oracle ref` has run
 # ------------------------------------------------------------------------------------------------
 _ref = None
