@@ -121,6 +121,9 @@ int vdb_remove(vdb_index* idx, int32_t id, int32_t* removed);
 int vdb_contains(vdb_index* idx, int32_t id);
 /* live vectors (Java: vectors.size()) */
 int64_t vdb_size(const vdb_index* idx);
+/* stored rows including removed ones: the row count of vdb_get_codes / vdb_get_graph / vdb_set_graph buffers (== vdb_size
+ * until the first vdb_remove; back to it after vdb_build) */
+int64_t vdb_rows(const vdb_index* idx);
 int vdb_is_trained(const vdb_index* idx);
 int vdb_get_stats(vdb_index* idx, vdb_stats* out);
 

@@ -30,6 +30,17 @@ inline float dot_fast(const float* a, const float* b, int d) {
     for (; i < d; i++) s += a[i] * b[i];
     return s;
 }
+// Java's order: sum = sum + round(diff * diff), one accumulator, no fused multiply-add (javac never contracts)
+__attribute__((optimize("-ffp-contract=off"))) float l2sq_java(const float* a, const float* b, int d) {
+    float s = 0.0f;
+    for (int i = 0; i < d; i++) { const float t = a[i] - b[i]; const float m = t * t; s = s + m; }
+    return s;
+}
+__attribute__((optimize("-ffp-contract=off"))) float dot_java(const float* a, const float* b, int d) {
+    float s = 0.0f;
+    for (int i = 0; i < d; i++) { const float m = a[i] * b[i]; s = s + m; }
+    return s;
+}
 struct Nb { float d; int idx; };
 struct NbLess { bool operator()(const Nb& a, const Nb& b) const { return a.d < b.d || (a.d == b.d && a.idx < b.idx); } };
 struct NbGreater { bool operator()(const Nb& a, const Nb& b) const { return NbLess()(b, a); } };
@@ -82,6 +93,7 @@ void HostGraph::import_graph(const int32_t* levels, const int32_t* adj_in, int n
 void HostGraph::insert(int index, int ef, int variant) {
     auto dist = [&](int a, int b) -> float {
         const float* x = vecs + (size_t)a * dim; const float* y = vecs + (size_t)b * dim;
+        if (exact_order) return metric == 0 ? l2sq_java(x, y, dim) : 1.0f - dot_java(x, y, dim) / (norms[a] * norms[b]);
         if (metric == 0) return l2sq_fast(x, y, dim);
         return 1.0f - dot_fast(x, y, dim) / (norms[a] * norms[b]);
     };

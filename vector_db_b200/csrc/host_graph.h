@@ -9,6 +9,8 @@ struct HostGraph {
     int dim = 0, M = 32, max_level = 1, metric = 0;
     uint64_t level_seed = 0, level_ctr = 0;
     int entry = -1;
+    bool exact_order = false;        // build-time distances in Java's sequential fp32 order (HnswPqIndex.java:741-750, Vector.java:77-102):
+                                     // the graph is then the oracle's graph link for link (strict mode); default = 8-lane sums (fast)
     const float* vecs = nullptr;     // [n][dim] (normalised rows for cosine), owned by the index
     const float* norms = nullptr;    // [n] for cosine
     std::vector<int32_t> level;      // [n]

@@ -81,6 +81,7 @@ extern "C" int vdb_create(const vdb_config* cfg, vdb_index** out) {
         if (c.ef_construction <= 0) c.ef_construction = c.index_type == VDB_INDEX_HNSW ? 400 : 64;
         if (c.ef_search <= 0) c.ef_search = c.index_type == VDB_INDEX_HNSW ? 400 : 64;
         x->g.init(c.dim, c.hnsw_m, c.max_elements, c.metric, c.level_seed);
+        x->g.exact_order = c.trav_store == VDB_TRAV_F32 && c.trav_batch == 1;      // strict mode: bit parity for the graph too
     }
     if (cudaStreamCreateWithFlags(&x->stream, cudaStreamNonBlocking) != cudaSuccess) { delete x; FAIL(VDB_ERR_CUDA, "stream create failed"); }
     cudaEventCreate(&x->ev_total0); cudaEventCreate(&x->ev_total1); cudaEventCreate(&x->ev_k0); cudaEventCreate(&x->ev_k1);
@@ -110,6 +111,7 @@ extern "C" int vdb_destroy(vdb_index* x) {
 
 static inline bool is_graph(const vdb_index* x) { return x->cfg.index_type == VDB_INDEX_HNSW || x->cfg.index_type == VDB_INDEX_HNSW_PQ; }
 extern "C" int64_t vdb_size(const vdb_index* x) { return x ? (is_graph(x) ? x->n_live : x->n) : -1; }   // Java: vectors.size()
+extern "C" int64_t vdb_rows(const vdb_index* x) { return x ? x->n : -1; }
 extern "C" int vdb_is_trained(const vdb_index* x) { return x && x->trained ? 1 : 0; }
 extern "C" int32_t vdb_max_level(const vdb_index* x) { return x ? x->g.max_level : 0; }
 

@@ -131,6 +131,10 @@ class GpuIndex:
     def size(self):
         return int(_lib.lib().vdb_size(self._h))
 
+    def rows(self):
+        """stored rows including removed ones (row count of codes() / graph() / set_graph buffers)"""
+        return int(_lib.lib().vdb_rows(self._h))
+
     @property
     def trained(self):
         return bool(_lib.lib().vdb_is_trained(self._h))
@@ -187,13 +191,13 @@ class GpuIndex:
         return cb
 
     def codes(self):
-        c = np.empty((self.size(), self.pq_m), dtype=np.uint8)
+        c = np.empty((self.rows(), self.pq_m), dtype=np.uint8)
         check(_lib.lib().vdb_get_codes(self._h, c.ctypes.data))
         return c
 
     def set_codes(self, codes):
         c = np.ascontiguousarray(codes, dtype=np.uint8)
-        assert c.shape == (self.size(), self.pq_m)
+        assert c.shape == (self.rows(), self.pq_m)
         check(_lib.lib().vdb_set_codes(self._h, c.ctypes.data))
 
     def encode_all(self):
@@ -206,11 +210,11 @@ class GpuIndex:
     def set_graph(self, levels, adj_levels, entry):
         levels = np.ascontiguousarray(levels, dtype=np.int32)
         adj = np.ascontiguousarray(np.stack(adj_levels, axis=0), dtype=np.int32)
-        assert adj.shape == (self.max_level, self.size(), self.hnsw_m), adj.shape
+        assert adj.shape == (self.max_level, self.rows(), self.hnsw_m), adj.shape
         check(_lib.lib().vdb_set_graph(self._h, levels.ctypes.data, adj.ctypes.data, self.max_level, int(entry)))
 
     def graph(self):
-        n = self.size()
+        n = self.rows()
         levels = np.empty(n, dtype=np.int32)
         adj = np.empty((self.max_level, n, self.hnsw_m), dtype=np.int32)
         entry = C.c_int32(-1)
