@@ -109,7 +109,10 @@ int vdb_build(vdb_index* idx);
  * out_ids[nq][k], out_dists[nq][k] */
 int vdb_search_batch(vdb_index* idx, const float* queries, int64_t nq, int32_t k, int32_t* out_ids, float* out_dists);
 /* same with DEVICE buffers on `stream` (a cudaStream_t taken verbatim: NULL = CUDA's legacy default stream, which is
- * also torch's default stream): no host copies, nothing is synchronised */
+ * also torch's default stream): no host copies of queries or results. One handle serves one search at a time: the scratch
+ * buffers belong to the index, so calls are serialised by the handle's mutex on the host and, when consecutive calls use
+ * different streams, ordered on the device by an event (they do not overlap). The first call after rows were added uploads
+ * them and may grow scratch buffers, which synchronises the handle's own stream. */
 int vdb_search_batch_device(vdb_index* idx, const float* d_queries, int64_t nq, int32_t k, int32_t* d_ids,
                             float* d_dists, void* stream);
 /* VectorIndex.removeVector (index/HnswPqIndex.java:542-596, HnswIndex.java:254-317): HNSW / HNSW_PQ only — the node's own
@@ -141,6 +144,8 @@ int vdb_save(vdb_index* idx, const char* path);
 int vdb_load(vdb_index* idx, const char* path);
 
 /* ---- device-side building blocks (benchmarks, multi-GPU merge, parity tests of single kernels) ---- */
+/* vdb_merge_topk_device and vdb_distance_device take no index handle: they launch on the calling thread's CURRENT device,
+ * which must be the device the pointers live on (cudaSetDevice before the call). */
 /* fill rows [row0,row0+n) of the index with the counter-based synthetic generator (seed, (row)*dim+j) directly
  * in HBM (no PCIe traffic); ids = id_offset+row. Oracle twin: orc_fill_uniform. */
 int vdb_fill_synthetic(vdb_index* idx, uint64_t seed, int64_t n);

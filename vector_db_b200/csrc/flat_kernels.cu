@@ -53,8 +53,9 @@ flat_exact_kernel(const float* __restrict__ base, const float* __restrict__ norm
                 bkey[slot] = key; brow[slot] = (uint32_t)i;
             }
         }
-        __syncthreads();
-        if (s_cnt > cap - NT) {
+        // one uniform decision for the whole CTA: a warp that raced ahead to the next iteration's atomicAdd must not be able to
+        // change what a slower warp reads here (a divergent barrier inside the sort would follow)
+        if (__syncthreads_or(s_cnt > cap - NT)) {
             block_bitonic_sort<true>(bkey, brow, cap);
             if (threadIdx.x == 0) { int c = min(s_cnt, k); s_cnt = c; if (c >= k) s_tau = bkey[k - 1]; }
             __syncthreads();

@@ -85,6 +85,7 @@ extern "C" int vdb_create(const vdb_config* cfg, vdb_index** out) {
     }
     if (cudaStreamCreateWithFlags(&x->stream, cudaStreamNonBlocking) != cudaSuccess) { delete x; FAIL(VDB_ERR_CUDA, "stream create failed"); }
     cudaEventCreate(&x->ev_total0); cudaEventCreate(&x->ev_total1); cudaEventCreate(&x->ev_k0); cudaEventCreate(&x->ev_k1);
+    cudaEventCreateWithFlags(&x->ev_done, cudaEventDisableTiming);
     if (x->d_counters.ensure(16, 0, x->stream) != VDB_OK) { delete x; return VDB_ERR_CUDA; }
     cudaMemsetAsync(x->d_counters.p, 0, 16 * sizeof(unsigned long long), x->stream);
     *out = x;
@@ -103,6 +104,7 @@ extern "C" int vdb_destroy(vdb_index* x) {
     x->d_train.release(); x->d_sub.release(); x->d_mind.release(); x->d_asg.release();
     x->d_dead.release(); x->d_adj_payload.release(); x->d_adj_targets.release();
     x->p_q.release(); x->p_d.release(); x->p_ids.release();
+    if (x->ev_done) cudaEventDestroy(x->ev_done);
     if (x->ev_total0) { cudaEventDestroy(x->ev_total0); cudaEventDestroy(x->ev_total1); cudaEventDestroy(x->ev_k0); cudaEventDestroy(x->ev_k1); }
     if (x->stream) cudaStreamDestroy(x->stream);
     delete x;
@@ -779,6 +781,9 @@ static int search_flat(vdb_index* x, const float* d_q, int64_t nq, int k, int32_
 static int search_device_locked(vdb_index* x, const float* d_q, int64_t nq, int k, int32_t* d_ids, float* d_dists, cudaStream_t st) {
     VDB_TRY(sync_index(x));
     if (nq == 0) return VDB_OK;
+    // all scratch (keys, LUTs, visited sets, flags, timing events) belongs to the index: a search issued on a different stream
+    // than the previous one is ordered after it on the device instead of overlapping with it
+    if (x->have_done && x->last_stream != st) VDB_CUDA(cudaStreamWaitEvent(st, x->ev_done, 0));
     x->timed = true;
     cudaEventRecord(x->ev_total0, st);
     int rc;
@@ -794,6 +799,8 @@ static int search_device_locked(vdb_index* x, const float* d_q, int64_t nq, int 
         }
     }
     cudaEventRecord(x->ev_total1, st);
+    cudaEventRecord(x->ev_done, st);
+    x->have_done = true; x->last_stream = st;
     x->stats.queries += nq;
     return rc;
 }

@@ -64,6 +64,9 @@ struct vdb_index {
     int pq_m = 0, sd = 0, num_sms = 148;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev_total0 = nullptr, ev_total1 = nullptr, ev_k0 = nullptr, ev_k1 = nullptr;
+    cudaEvent_t ev_done = nullptr;  // end of the last search: the scratch buffers are shared, so a search on ANOTHER stream waits on it
+    cudaStream_t last_stream = nullptr;
+    bool have_done = false;
     bool timed = false;
     std::mutex mu;
 
