@@ -162,6 +162,12 @@ int vdb_merge_topk_device(const float* d_dists, const int32_t* d_ids, int32_t g,
 int vdb_distance_device(const float* d_a, const float* d_b, int64_t n, int32_t dim, int32_t metric, int32_t order,
                         float* d_out, void* stream);
 
+/* measured ceilings of the access patterns the gather-bound kernels use (csrc/microbench.cu; bench.py quotes roofline fractions
+ * against them): kind 0 = random row gathers with the beam kernel's load shape, 1 = the same with 8 lines per row in flight,
+ * 2 = the ADC scan's conflict-free shared-memory gather. out[0] = ms per launch (median of reps), out[1] = bytes (kinds 0, 1) or
+ * gathers (kind 2) per launch. Allocates and frees its own buffers on the current device. */
+int vdb_microbench_device(int32_t kind, int64_t rows, int32_t row_bytes, int32_t work, int32_t reps, double* out);
+
 /* ---- no-allocation variant (no counterpart in the reference) ----
  * Order-exact flat search (squared L2) over caller-owned DEVICE rows d_base[n][dim] for callers that cannot call cudaMalloc
  * (CUDA graph capture, tight serving loops, harnesses that forbid it): same kernels and same answer as a VDB_INDEX_FLAT

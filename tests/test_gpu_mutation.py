@@ -52,7 +52,6 @@ def test_remove_vector_matches_java_semantics(v, po, kind):
         o = po.OracleHnsw(po.KIND_HNSW, dim, maxel, level_seed=11)
     g.addBatch(np.arange(n, dtype=np.int32), X[:n])
     o.add_batch(X[:n], np.arange(n, dtype=np.int32))
-    o.set_arith(po.ARITH_GPU_TREE)                         # strict mode: the oracle twin reproduces every bit
     ids0, d0 = g.searchBatch(Q, k)
     entry = g.graph()[2]
     rng = np.random.default_rng(5)
@@ -63,7 +62,8 @@ def test_remove_vector_matches_java_semantics(v, po, kind):
     script += [("rm", victims[0]), ("add", 5 if 5 not in victims else 6), ("add", n + 31), ("rm", n + 2), ("add", n + 2)]
     _mutate(po, g, o, X, script)
     assert g.size() == o.live
-    assert _same_graph(g, o)
+    assert _same_graph(g, o)                               # inserts / removals use Java's arithmetic on both sides
+    o.set_arith(po.ARITH_GPU_TREE)                         # searches: strict mode's lane order, which the oracle twin reproduces bit for bit
     ids, d = g.searchBatch(Q, k)
     oi, od, _ = o.search(Q, k)
     assert np.array_equal(ids, oi) and np.array_equal(bits(d), bits(od))
@@ -71,7 +71,9 @@ def test_remove_vector_matches_java_semantics(v, po, kind):
     if kind == "hnswpq":
         assert np.array_equal(g.codes(), o.codes())        # incl. the rows whose Java code row was overwritten after a removal
     # rebuildIndex drops the removed vectors for good and rebuilds by ascending id
+    o.set_arith(po.ARITH_JAVA_SEQ)
     g.buildIndex(); o.rebuild()
+    o.set_arith(po.ARITH_GPU_TREE)
     assert g.size() == o.live == o.size
     assert _same_graph(g, o)
     ids, d = g.searchBatch(Q, k)
@@ -118,7 +120,9 @@ def test_snapshot_is_a_shared_format(v, po, tmp_path):
     oi, od, _ = o.search(Q, k)
     assert np.array_equal(ids, oi) and np.array_equal(bits(d), bits(od))
     # oracle -> library (the oracle mutates the state first, so the file is genuinely its own)
+    o.set_arith(po.ARITH_JAVA_SEQ)                         # mutations in Java's arithmetic, searches in the strict twin's
     assert o.remove(10) and o.add(5000, X[10])
+    o.set_arith(po.ARITH_GPU_TREE)
     p2 = str(tmp_path / "oracle.vdb")
     po.oracle_to_snapshot(o, p2, 3000, 64, 64, level_seed=21)
     h = v.NativeHnswPqIndex(dim, 3000, pqM=M, level_seed=21, **STRICT)
@@ -128,7 +132,9 @@ def test_snapshot_is_a_shared_format(v, po, tmp_path):
     oi, od, _ = o.search(Q, k)
     assert np.array_equal(hi, oi) and np.array_equal(bits(hd), bits(od))
     # the loaded index keeps working like the saved one: same level stream, same training state
+    o.set_arith(po.ARITH_JAVA_SEQ)
     assert h.addVector(6000, X[20]) and o.add(6000, X[20])
+    o.set_arith(po.ARITH_GPU_TREE)
     hi, hd = h.searchBatch(Q, k)
     oi, od, _ = o.search(Q, k)
     assert np.array_equal(hi, oi) and np.array_equal(bits(hd), bits(od))

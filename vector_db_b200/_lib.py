@@ -19,7 +19,7 @@ SYMBOLS = [
     "vdb_build", "vdb_search_batch", "vdb_search_batch_device", "vdb_size", "vdb_is_trained", "vdb_get_stats",
     "vdb_set_codebooks", "vdb_get_codebooks", "vdb_get_codes", "vdb_set_codes", "vdb_set_graph", "vdb_get_graph",
     "vdb_max_level", "vdb_save", "vdb_load", "vdb_fill_synthetic", "vdb_encode_all", "vdb_pq_lut_device",
-    "vdb_adc_scan_device", "vdb_merge_topk_device", "vdb_distance_device", "vdb_flat_search_noalloc_device", "vdb_remove", "vdb_contains", "vdb_rows",
+    "vdb_adc_scan_device", "vdb_merge_topk_device", "vdb_distance_device", "vdb_flat_search_noalloc_device", "vdb_remove", "vdb_contains", "vdb_rows", "vdb_microbench_device",
 ]
 
 
@@ -65,6 +65,7 @@ def lib():
     L.vdb_search_batch_device.argtypes = [vp, vp, i64, i32, vp, vp, vp]
     L.vdb_size.argtypes = [vp]; L.vdb_size.restype = i64
     L.vdb_rows.argtypes = [vp]; L.vdb_rows.restype = i64
+    L.vdb_microbench_device.argtypes = [i32, i64, i32, i32, i32, C.POINTER(C.c_double)]
     L.vdb_remove.argtypes = [vp, i32, C.POINTER(i32)]
     L.vdb_contains.argtypes = [vp, i32]
     L.vdb_is_trained.argtypes = [vp]

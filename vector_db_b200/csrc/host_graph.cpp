@@ -55,7 +55,8 @@ void HostGraph::init(int dim_, int M_, int max_elements, int metric_, uint64_t s
     clear();
 }
 void HostGraph::clear() {
-    level.clear(); dead.clear(); entry = -1; level_ctr = 0;
+    level.clear(); dead.clear(); entry = -1;      // level_ctr is NOT reset: the seeded level stream continues across a rebuild
+                                                  // (ThreadLocalRandom has no reset either, HnswPqIndex.java:752-759)
     dirty.clear(); all_dirty = true;
     for (auto& f : dirty_flag) f.clear();
     for (auto& a : adj) a.clear();

@@ -557,6 +557,18 @@ extern "C" int vdb_build(vdb_index* x) {
         }
         x->h_vecs.swap(nv); x->h_ids.swap(ni); x->h_norms.swap(nn);
     }
+    if (x->cfg.metric == VDB_METRIC_COSINE && x->n > 0) {
+        // buildIndex re-adds the STORED (already normalised) vectors through addVector, which normalises again
+        // (HnswIndex.java:437-460 -> :154): not an exact no-op in fp32, so it is done here too (same device kernel as the add path)
+        VDB_TRY(x->d_q.ensure((size_t)x->n * dim, 0, x->stream));
+        VDB_TRY(x->d_out_d.ensure((size_t)x->n, 0, x->stream));
+        VDB_CUDA(cudaMemcpyAsync(x->d_q.p, x->h_vecs.data(), (size_t)x->n * dim * 4, cudaMemcpyHostToDevice, x->stream));
+        launch_normalize_rows(x->d_q.p, x->n, dim, x->d_out_d.p, x->stream);
+        x->h_norms.resize(x->n);
+        VDB_CUDA(cudaMemcpyAsync(x->h_vecs.data(), x->d_q.p, (size_t)x->n * dim * 4, cudaMemcpyDeviceToHost, x->stream));
+        VDB_CUDA(cudaMemcpyAsync(x->h_norms.data(), x->d_out_d.p, (size_t)x->n * 4, cudaMemcpyDeviceToHost, x->stream));
+        VDB_CUDA(cudaStreamSynchronize(x->stream));
+    }
     x->g.clear();
     x->n_indexed = 0; x->n_dev = 0; x->n_trav = 0; x->n_fmirror = 0; x->n_coded = 0; x->raw_rows = 0; x->codes_overridden = false;
     x->id2row.clear();
