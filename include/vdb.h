@@ -39,7 +39,7 @@ enum {
     VDB_INDEX_HNSW_PQ = 3  /* Java HnswPqIndex: sq-L2, PQ upper layers, exact layer 0 + rerank (index/HnswPqIndex.java) */
 };
 enum { VDB_METRIC_SQL2 = 0, VDB_METRIC_COSINE = 1 };
-enum { VDB_TRAV_BF16 = 0, VDB_TRAV_F32 = 1, VDB_TRAV_FP8 = 2, VDB_TRAV_INT8 = 3 };
+enum { VDB_TRAV_AUTO = 0, VDB_TRAV_F32 = 1, VDB_TRAV_FP8 = 2, VDB_TRAV_INT8 = 3, VDB_TRAV_BF16 = 4 };
 /* fp32 reduction order of the reference implementation being reproduced */
 enum {
     VDB_ARITH_JAVA_SEQ = 0,    /* sequential, mul then add (HnswPqIndex.java:741-750, :343-350) */
@@ -70,7 +70,11 @@ typedef struct vdb_config {
     int32_t id_offset;       /* multi-GPU id-range sharding: this shard holds global rows [id_offset, id_offset+n) */
     int32_t search_ef_cap;   /* HNSW_PQ: cap of the layer-0 beam; 0 = 5000, the constant of HnswPqIndex.java:621 */
     uint64_t level_seed;     /* seeded stand-in for ThreadLocalRandom level draws (HnswPqIndex.java:752-759) */
-    int32_t trav_store;      /* HNSW*: rows read during traversal: 0 = bf16 copy (default), 1 = fp32 (strict order), 2 = fp8 e4m3 with a per-row power-of-two scale, 3 = int8 with a per-row scale (both opt-in, dim % 128 == 0) */
+    int32_t trav_store;      /* HNSW*: rows read during traversal (VDB_TRAV_*): 0 = auto: int8 with a per-row scale when dim % 128 == 0
+                                and (all but 0.1 % of) the rows pass the outlier check max|x| <= 6 rms(x), else the bf16 copy;
+                                1 = fp32 (strict order); 2 = fp8 e4m3 with a per-row power-of-two scale (dim % 128 == 0);
+                                3 = int8 always (dim % 128 == 0); 4 = bf16 always. Whatever the rows, the answer is re-scored
+                                from the fp32 rows in the reference's order, so returned distances are exact */
     int32_t trav_batch;      /* HNSW*: candidates expanded per round: 0 = auto (ef/128 in [4,32]; 64 from ef 4096), 1 = the Java pop order */
     int32_t n_devices;       /* FLAT / PQ: GPUs of this box the rows are spread over by contiguous id range (0 or 1 = one GPU,
                                 `device`); devices device..device+n_devices-1 are used from ONE process: one vdb_search_batch
@@ -87,6 +91,8 @@ typedef struct vdb_stats {
     float last_total_ms;     /* device time of the whole last search */
     int64_t flat_certified;  /* flat search: queries answered by the tensor-core shortlist and certified exact */
     int64_t flat_fallback;   /* flat search: queries that failed certification and were re-run by the order-exact scan */
+    int32_t trav_format;     /* HNSW*: row format the traversal copy currently has (VDB_TRAV_F32 / FP8 / INT8 / BF16; what AUTO picked) */
+    int32_t reserved;
 } vdb_stats;
 
 const char* vdb_last_error(void);

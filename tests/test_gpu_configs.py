@@ -102,16 +102,26 @@ def test_c3_headline_shape_sample(v, po):
     rg, rj = recall(ids, gt), recall(jid, gt)
     assert abs(rg - rj) <= 0.005, (rg, rj)
     # id agreement with the Java pop order. Measured on the B200 (tools/c3_idmatch.py -> profiles/r2_c3_idmatch.log): with ONE
-    # candidate per round the ids are 100 % the oracle's for bf16 AND fp32 rows; with the default 64 candidates per round 8 of
-    # 256 queries differ, and in every one of them the GPU's k-th exact distance is strictly SMALLER (the batched round expands
-    # a few candidates the sequential loop would have skipped, +0.8 % distance evaluations). So the bar for the batched mode is:
-    # >= 98 % equal ids, and wherever they differ the GPU answer must not be worse (<= 1 query of the sample may be).
+    # candidate per round the ids are 100 % the oracle's for bf16 AND fp32 rows; with 64 candidates per round 8 of 256 queries
+    # differ on bf16 rows (98.6 %) and 10 on int8 rows (97.7 %; the default here: dim % 128 == 0 and uniform rows pass the outlier
+    # check), and in all but one of them the GPU's k-th exact distance is strictly SMALLER (the batched round expands a few
+    # candidates the sequential loop would have skipped, +0.8 % distance evaluations). So the bar for the default mode is:
+    # >= 97 % equal ids, at most 2 queries of the sample worse than Java's, recall not below Java's (0.2 pt slack).
+    assert g.stats()["trav_format"] == 3                   # VDB_TRAV_AUTO picked int8
     match = float((ids == jid).mean())
     rep = _diff_report(ids, jid, d, jd, k)
-    assert match >= 0.98, (match, rep)
-    assert rep["gpu_worse_kth"] <= 1 and rg >= rj - 0.002, (match, rep, rg, rj)
+    assert match >= 0.97, (match, rep)
+    assert rep["gpu_worse_kth"] <= 2 and rg >= rj - 0.002, (match, rep, rg, rj)
+    # forced bf16 rows: >= 98 % and at most one worse
+    b16 = v.NativeHnswPqIndex(dim, 2 * n, pqM=M, level_seed=1234, trav_store=4)
+    b16.addBatch(np.arange(n, dtype=np.int32), X)
+    b16.set_codebooks(state[3]); b16.set_graph(state[0], list(state[1]), state[2]); b16.set_codes(state[4])
+    fid, fd = b16.searchBatch(Q, k)
+    b16.close()
+    rep16 = _diff_report(fid, jid, fd, jd, k)
+    assert float((fid == jid).mean()) >= 0.98 and rep16["gpu_worse_kth"] <= 1, rep16
     # one candidate per round on the bf16 rows (half the bytes of the strict fp32 mode): the Java pop order, ids identical
-    b1 = v.NativeHnswPqIndex(dim, 2 * n, pqM=M, level_seed=1234, trav_batch=1)
+    b1 = v.NativeHnswPqIndex(dim, 2 * n, pqM=M, level_seed=1234, trav_batch=1, trav_store=4)
     b1.addBatch(np.arange(n, dtype=np.int32), X)
     b1.set_codebooks(state[3]); b1.set_graph(state[0], list(state[1]), state[2]); b1.set_codes(state[4])
     bid, bd = b1.searchBatch(Q[:64], k)
@@ -176,3 +186,37 @@ def test_c5_adc_scan_rerank_1m_1000(v, po):
     p2.close()
     oi2, od2 = po.pq_flat_search(Q[:16], cb, codes, k, po.ARITH_NATIVE_AVX2, nthreads=CORES)
     assert np.array_equal(ids2, oi2) and np.array_equal(bits(d2), bits(od2))
+
+
+@pytest.mark.parametrize("shape", ["rowscale", "spiky"])
+def test_auto_traversal_format_on_heavy_tailed_rows(v, po, shape):
+    """VDB_TRAV_AUTO (the default) on non-uniform data. `rowscale`: Gaussian rows times a log-normal per-row scale (norms spread
+    over two orders of magnitude) — a per-row int8 scale absorbs it, the outlier check passes, int8 rows are used and recall must
+    stay within 0.5 pt of the Java-order walk. `spiky`: every row carries a few components 40 x larger than the rest — int8 would
+    spend its 8 bits on the spikes, the check must reject it and fall back to bf16."""
+    n, dim, M, nq, k = 20000, 128, 16, 200, 10
+    rng = np.random.default_rng(7)
+    X = rng.standard_normal((n, dim)).astype(np.float32)
+    Q = rng.standard_normal((nq, dim)).astype(np.float32)
+    if shape == "rowscale":
+        X *= np.exp(rng.normal(0.0, 1.0, (n, 1))).astype(np.float32)
+        Q *= np.exp(rng.normal(0.0, 1.0, (nq, 1))).astype(np.float32)
+    else:
+        spikes = rng.integers(0, dim, (n, 3))
+        X[np.arange(n)[:, None], spikes] *= 40.0
+    g = v.NativeHnswPqIndex(dim, 2 * n, pqM=M, level_seed=1234)
+    g.addBatch(np.arange(n, dtype=np.int32), X)
+    g.buildIndex()
+    ids, d = g.searchBatch(Q, k)
+    assert g.stats()["trav_format"] == (3 if shape == "rowscale" else 4)
+    levels, adj, entry = g.graph()
+    o = po.OracleHnsw(po.KIND_HNSWPQ, dim, 2 * n, pq_m=M, level_seed=1234)
+    o.import_state(X, levels, adj, entry, codebooks=g.codebooks(), codes=g.codes())
+    jid, jd, _ = o.search(Q, k, nthreads=CORES)
+    gt, _ = po.flat_search(X, Q, k, nthreads=CORES)
+    rg, rj = recall(ids, gt), recall(jid, gt)
+    assert abs(rg - rj) <= 0.005, (rg, rj)
+    assert (ids == jid).mean() >= 0.97
+    same = ids == jid
+    assert np.array_equal(bits(d[same]), bits(jd[same]))                # exact re-score: distances are Java's bit for bit
+    g.close()

@@ -411,7 +411,7 @@ def test_hnsw_cosine_8bit_traversal_rows(v, po, store):
     g.close()
 
 
-@pytest.mark.parametrize("store", [1, 0], ids=["fp32rows", "bf16rows"])
+@pytest.mark.parametrize("store", [1, 4], ids=["fp32rows", "bf16rows"])
 def test_hnswpq_large_rounds(v, po, store):
     """64 candidates per round on a beam of 1500: the first rounds accept up to 2048 keys at once, which drives the
     accepted-key sort through every chunk size (2 / 4 / 8 keys per lane) and the sort-straight-into-the-side-buffer path.

@@ -11,7 +11,7 @@ INDEX_FLAT, INDEX_PQ, INDEX_HNSW, INDEX_HNSW_PQ = 0, 1, 2, 3
 METRIC_SQL2, METRIC_COSINE = 0, 1
 ARITH_JAVA_SEQ, ARITH_NATIVE_AVX2 = 0, 1
 TRAIN_JAVA, TRAIN_NATIVE_HNSWPQ, TRAIN_NATIVE_PQ = 0, 1, 2
-TRAV_BF16, TRAV_F32 = 0, 1
+TRAV_AUTO, TRAV_F32, TRAV_FP8, TRAV_INT8, TRAV_BF16 = 0, 1, 2, 3, 4
 
 # every symbol include/vdb.h declares (checked by tests/test_abi.py)
 SYMBOLS = [
@@ -32,7 +32,8 @@ class VdbConfig(C.Structure):
 
 class VdbStats(C.Structure):
     _fields_ = [("queries", C.c_int64), ("dist_evals", C.c_int64), ("expansions", C.c_int64), ("adc_rows", C.c_int64),
-                ("last_kernel_ms", C.c_float), ("last_total_ms", C.c_float), ("flat_certified", C.c_int64), ("flat_fallback", C.c_int64)]
+                ("last_kernel_ms", C.c_float), ("last_total_ms", C.c_float), ("flat_certified", C.c_int64), ("flat_fallback", C.c_int64),
+                ("trav_format", C.c_int32), ("reserved", C.c_int32)]
 
 
 class VdbError(RuntimeError):

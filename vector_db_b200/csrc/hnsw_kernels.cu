@@ -1288,6 +1288,25 @@ void launch_scatter_adj_rows(int32_t* d_adj, const int32_t* d_payload, const uin
     const int64_t tot = (int64_t)cnt * deg;
     scatter_adj_rows_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(d_adj, d_payload, d_targets, cnt, deg, adj_stride);
 }
+__global__ void count_outlier_rows_kernel(const float* __restrict__ base, int64_t n, int dim, float ratio2, unsigned long long* __restrict__ count) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    unsigned long long bad = 0;
+    for (int64_t r = warp; r < n; r += nwarps) {
+        float mx = 0.0f, ss = 0.0f;
+        for (int c = lane; c < dim; c += 32) { const float v = base[r * dim + c]; mx = fmaxf(mx, fabsf(v)); ss = __fmaf_rn(v, v, ss); }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o)); ss += __shfl_xor_sync(0xffffffffu, ss, o); }
+        if (mx * mx * (float)dim > ratio2 * ss) bad++;            // max^2 > ratio^2 * mean square
+    }
+    if (lane == 0 && bad) atomicAdd(count, bad);
+}
+void launch_count_outlier_rows(const float* d_base, int64_t n, int dim, float ratio, unsigned long long* d_count, cudaStream_t st) {
+    if (n <= 0) return;
+    int blocks = (int)std::min<int64_t>((n + 7) / 8, 148 * 16);
+    count_outlier_rows_kernel<<<blocks, 256, 0, st>>>(d_base, n, dim, ratio * ratio, d_count);
+}
 void launch_make_traversal_rows(const float* d_base, int64_t n, int dim, int dpad, int mode, void* d_out, float* d_tnorm, float* d_tscale,
                                 cudaStream_t st) {
     if (n <= 0) return;

@@ -65,6 +65,8 @@ int hnsw_max_batch(int deg);
 // write `cnt` changed adjacency rows (payload[cnt][deg]) to their (level, row) targets: target = level << 32 | row
 void launch_scatter_adj_rows(int32_t* d_adj, const int32_t* d_payload, const uint64_t* d_targets, int cnt, int deg, int64_t adj_stride,
                              cudaStream_t st);
+// rows of d_base[n][dim] whose largest |element| exceeds `ratio` x rms(row): *d_count += that number (int8 suitability check)
+void launch_count_outlier_rows(const float* d_base, int64_t n, int dim, float ratio, unsigned long long* d_count, cudaStream_t st);
 void launch_make_traversal_rows(const float* d_base, int64_t n, int dim, int dpad, int mode /* 0 fp32, 1 bf16, 2 fp8, 3 int8 */, void* d_out, float* d_tnorm,
                                 float* d_tscale, cudaStream_t st);
 

@@ -86,8 +86,8 @@ extern "C" int vdb_create(const vdb_config* cfg, vdb_index** out) {
     if (cudaStreamCreateWithFlags(&x->stream, cudaStreamNonBlocking) != cudaSuccess) { delete x; FAIL(VDB_ERR_CUDA, "stream create failed"); }
     cudaEventCreate(&x->ev_total0); cudaEventCreate(&x->ev_total1); cudaEventCreate(&x->ev_k0); cudaEventCreate(&x->ev_k1);
     cudaEventCreateWithFlags(&x->ev_done, cudaEventDisableTiming);
-    if (x->d_counters.ensure(16, 0, x->stream) != VDB_OK) { delete x; return VDB_ERR_CUDA; }
-    cudaMemsetAsync(x->d_counters.p, 0, 16 * sizeof(unsigned long long), x->stream);
+    if (x->d_counters.ensure(24, 0, x->stream) != VDB_OK) { delete x; return VDB_ERR_CUDA; }
+    cudaMemsetAsync(x->d_counters.p, 0, 24 * sizeof(unsigned long long), x->stream);
     *out = x;
     return VDB_OK;
 }
@@ -139,14 +139,41 @@ static int upload_rows(vdb_index* x) {
 
 // traversal copy of rows [n_trav, n_dev): zero-padded to 8 elements, bf16 (default) or fp32 (strict mode)
 static inline int trav_dpad(const vdb_index* x) { return (x->cfg.dim + 7) & ~7; }
+static inline int trav_mode(const vdb_index* x) { return x->trav_eff; }      // kernel tstore: 0 fp32, 1 bf16, 2 fp8, 3 int8
 static inline int trav_stride(const vdb_index* x) {
-    return (x->cfg.trav_store == VDB_TRAV_FP8 || x->cfg.trav_store == VDB_TRAV_INT8) ? x->cfg.dim : trav_dpad(x) * (x->cfg.trav_store == VDB_TRAV_F32 ? 4 : 2);    // fp8: dim % 128 == 0
+    return (x->trav_eff == 2 || x->trav_eff == 3) ? x->cfg.dim : trav_dpad(x) * (x->trav_eff == 0 ? 4 : 2);    // 8-bit rows: dim % 128 == 0
 }
-static inline int trav_mode(const vdb_index* x) {
-    return x->cfg.trav_store == VDB_TRAV_F32 ? 0 : (x->cfg.trav_store == VDB_TRAV_FP8 ? 2 : (x->cfg.trav_store == VDB_TRAV_INT8 ? 3 : 1));
+// VDB_TRAV_AUTO: int8 rows need every row's quantisation step (max|x| / 127) to be small against its typical element: rows whose
+// largest element exceeds 6 x rms would spend the 8 bits on the outlier. Checked on the rows about to be converted.
+static int pick_trav_format(vdb_index* x, int64_t row0, int64_t cnt, bool* changed) {
+    *changed = false;
+    int want;
+    switch (x->cfg.trav_store) {
+        case VDB_TRAV_F32: want = 0; break;
+        case VDB_TRAV_FP8: want = 2; break;
+        case VDB_TRAV_INT8: want = 3; break;
+        case VDB_TRAV_BF16: want = 1; break;
+        default: {
+            want = 1;
+            if ((x->cfg.dim % 128) == 0 && !getenv("VDB_TRAV_NO_INT8") && (row0 == 0 || x->trav_eff == 3)) {
+                VDB_CUDA(cudaMemsetAsync(x->d_counters.p + 16, 0, sizeof(unsigned long long), x->stream));
+                launch_count_outlier_rows(x->d_base.p + (size_t)row0 * x->cfg.dim, cnt, x->cfg.dim, 6.0f, x->d_counters.p + 16, x->stream);
+                unsigned long long bad = 0;
+                VDB_CUDA(cudaMemcpyAsync(&bad, x->d_counters.p + 16, sizeof bad, cudaMemcpyDeviceToHost, x->stream));
+                VDB_CUDA(cudaStreamSynchronize(x->stream));
+                if (bad * 1000ull <= (unsigned long long)cnt) want = 3;
+            }
+        }
+    }
+    if (row0 == 0 || want != x->trav_eff) *changed = want != x->trav_eff;
+    x->trav_eff = want;
+    return VDB_OK;
 }
 static int build_traversal_rows(vdb_index* x) {
     if (x->n_trav >= x->n_dev) return VDB_OK;
+    bool changed = false;
+    VDB_TRY(pick_trav_format(x, x->n_trav, x->n_dev - x->n_trav, &changed));
+    if (changed) x->n_trav = 0;                    // newly added rows fail the int8 check (or first build): convert everything
     const size_t stride = (size_t)trav_stride(x);
     VDB_TRY(x->d_trav.ensure((size_t)x->n_dev * stride, (size_t)x->n_trav * stride, x->stream));
     VDB_TRY(x->d_tnorm.ensure((size_t)x->n_dev, (size_t)x->n_trav, x->stream));
@@ -867,6 +894,7 @@ extern "C" int vdb_get_stats(vdb_index* x, vdb_stats* out) {
         fprintf(stderr, "[vdb hnsw profile] accepted keys: sum %llu | rounds with > 256: %llu (sort cycles %llu), with 129..256: %llu\n", c[13], c[12], c[15], c[14]);
     x->stats.dist_evals = (int64_t)c[0]; x->stats.expansions = (int64_t)c[1];
     x->stats.flat_certified = (int64_t)c[10]; x->stats.flat_fallback = (int64_t)c[11];
+    x->stats.trav_format = x->trav_eff == 0 ? VDB_TRAV_F32 : (x->trav_eff == 2 ? VDB_TRAV_FP8 : (x->trav_eff == 3 ? VDB_TRAV_INT8 : VDB_TRAV_BF16));
     *out = x->stats;
     return VDB_OK;
 }

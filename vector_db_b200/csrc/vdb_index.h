@@ -85,6 +85,7 @@ struct vdb_index {
     int64_t n_codesT = 0;           // rows present in d_codesT
     DevBuf<unsigned char> d_trav;   // traversal rows (bf16 or padded fp32), rebuilt when rows are uploaded
     int64_t n_trav = 0;
+    int trav_eff = 1;               // effective row format (kernel tstore: 0 fp32, 1 bf16, 2 fp8, 3 int8), decided when the copy is (re)built
     DevBuf<float> d_tnorm;          // squared norms of the traversal rows
     DevBuf<float> d_tscale;         // fp8 traversal rows: inverse of the per-row scale
     DevBuf<uint16_t> d_fmirror;     // flat index: bf16 mirror [n][dpad] for the tensor-core search (flat_gemm.cu)
