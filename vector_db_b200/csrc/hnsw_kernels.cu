@@ -255,8 +255,10 @@ struct FreshOut {
     int* nacc;        // shared counter
     bool full;        // results.size() >= ef
     float bound;      // furthest (live or stale)
+    bool ordered;     // keep EVERY key at its fresh-list position j (fkey[j]): the round is replayed in Java's order afterwards
 };
-__device__ __forceinline__ void accept_key(const FreshOut& o, float d, int node) {
+__device__ __forceinline__ void accept_key(const FreshOut& o, float d, int node, int j) {
+    if (o.ordered) { o.fkey[j] = pool_key(d, node); return; }
     if (!o.full || d < o.bound) {
         const int slot = atomicAdd(o.nacc, 1);
         o.fkey[slot] = pool_key(d, node);
@@ -324,7 +326,7 @@ __device__ __noinline__ void fresh_distances(const HnswSearchParams& p, const fl
             }
 #pragma unroll
             for (int off = G / 2; off >= 1; off >>= 1) acc = __fadd_rn(acc, __shfl_xor_sync(0xffffffffu, acc, off));
-            if (g == 0 && node[u] >= 0) accept_key(o, finish_dist<BF16>(p, acc, rs[u], qnorm, qq), node[u]);
+            if (g == 0 && node[u] >= 0) accept_key(o, finish_dist<BF16>(p, acc, rs[u], qnorm, qq), node[u], base + grp * U + u);
         }
         if (more) {
 #pragma unroll
@@ -387,7 +389,7 @@ __device__ __noinline__ void fresh_distances_long(const HnswSearchParams& p, con
             float a = acc[u];
 #pragma unroll
             for (int off = 16; off >= 1; off >>= 1) a = __fadd_rn(a, __shfl_xor_sync(0xffffffffu, a, off));
-            if (lane == 0 && node[u] >= 0) accept_key(o, finish_dist<BF16>(p, a, row_scalar<BF16>(p, node[u]), qnorm, qq), node[u]);
+            if (lane == 0 && node[u] >= 0) accept_key(o, finish_dist<BF16>(p, a, row_scalar<BF16>(p, node[u]), qnorm, qq), node[u], base + warp * 2 + u);
         }
     }
 }
@@ -515,11 +517,11 @@ __device__ __forceinline__ void fresh_distances_fp8(const HnswSearchParams& p, c
         if (c == 0) {
             if (j0 < nf) {
                 const float dot = __fmul_rn(__fmaf_rn(al[0], 0.0625f, ah[0]), __fmul_rn(is0, qinv));
-                accept_key(o, p.metric == 1 ? cosine_dist_from_dot(dot, sc0, qnorm) : fmaxf(__fmaf_rn(-2.0f, dot, __fadd_rn(qq, sc0)), 0.0f), n0);
+                accept_key(o, p.metric == 1 ? cosine_dist_from_dot(dot, sc0, qnorm) : fmaxf(__fmaf_rn(-2.0f, dot, __fadd_rn(qq, sc0)), 0.0f), n0, j0);
             }
             if (j1 < nf) {
                 const float dot = __fmul_rn(__fmaf_rn(al[2], 0.0625f, ah[2]), __fmul_rn(is1, qinv));
-                accept_key(o, p.metric == 1 ? cosine_dist_from_dot(dot, sc1, qnorm) : fmaxf(__fmaf_rn(-2.0f, dot, __fadd_rn(qq, sc1)), 0.0f), n1);
+                accept_key(o, p.metric == 1 ? cosine_dist_from_dot(dot, sc1, qnorm) : fmaxf(__fmaf_rn(-2.0f, dot, __fadd_rn(qq, sc1)), 0.0f), n1, j1);
             }
         }
     }
@@ -567,11 +569,11 @@ __device__ __forceinline__ void fresh_distances_i8(const HnswSearchParams& p, co
         if (c == 0) {
             if (j0 < nf) {
                 const float dot = __fmul_rn((float)(a0[0] + a1[0]), __fmul_rn(is0, qinv));
-                accept_key(o, p.metric == 1 ? cosine_dist_from_dot(dot, sc0, qnorm) : fmaxf(__fmaf_rn(-2.0f, dot, __fadd_rn(qq, sc0)), 0.0f), n0);
+                accept_key(o, p.metric == 1 ? cosine_dist_from_dot(dot, sc0, qnorm) : fmaxf(__fmaf_rn(-2.0f, dot, __fadd_rn(qq, sc0)), 0.0f), n0, j0);
             }
             if (j1 < nf) {
                 const float dot = __fmul_rn((float)(a0[2] + a1[2]), __fmul_rn(is1, qinv));
-                accept_key(o, p.metric == 1 ? cosine_dist_from_dot(dot, sc1, qnorm) : fmaxf(__fmaf_rn(-2.0f, dot, __fadd_rn(qq, sc1)), 0.0f), n1);
+                accept_key(o, p.metric == 1 ? cosine_dist_from_dot(dot, sc1, qnorm) : fmaxf(__fmaf_rn(-2.0f, dot, __fadd_rn(qq, sc1)), 0.0f), n1, j1);
             }
         }
     }
@@ -615,8 +617,8 @@ __device__ __forceinline__ void fresh_distances_mma_full(const HnswSearchParams&
             }
         }
         if (c == 0) {
-            if (j0 < nf) accept_key(o, finish_dist<true>(p, acc0[0] + acc1[0], sc0, qnorm, qq), n0);
-            if (j1 < nf) accept_key(o, finish_dist<true>(p, acc0[2] + acc1[2], sc1, qnorm, qq), n1);
+            if (j0 < nf) accept_key(o, finish_dist<true>(p, acc0[0] + acc1[0], sc0, qnorm, qq), n0, j0);
+            if (j1 < nf) accept_key(o, finish_dist<true>(p, acc0[2] + acc1[2], sc1, qnorm, qq), n1, j1);
         }
     }
 }
@@ -660,8 +662,8 @@ __device__ __forceinline__ void fresh_distances_mma(const HnswSearchParams& p, c
             }
         }
         if (c == 0) {
-            if (j0 < nf) accept_key(o, finish_dist<true>(p, acc0[0] + acc1[0], sc0, qnorm, qq), n0);
-            if (j1 < nf) accept_key(o, finish_dist<true>(p, acc0[2] + acc1[2], sc1, qnorm, qq), n1);
+            if (j0 < nf) accept_key(o, finish_dist<true>(p, acc0[0] + acc1[0], sc0, qnorm, qq), n0, j0);
+            if (j1 < nf) accept_key(o, finish_dist<true>(p, acc0[2] + acc1[2], sc1, qnorm, qq), n1, j1);
         }
     }
 }
@@ -852,6 +854,7 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
     __shared__ GreedyShared GS;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int ef = p.ef, variant = p.variant, B = p.batch;
+    const int32_t* adj0 = p.adj + (size_t)p.beam_level * p.adj_stride * p.deg;      // the level the beam walks
     const int uncertain_ok = B == 1 ? 1 : 128;    // side-buffer entries tolerated while candidates come from the array's tail
     unsigned long long evals = 0, exps = 0;
     if (tid < 8) S.ph[tid] = 0;
@@ -862,7 +865,8 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
         // ---- A. stage the query (HnswIndex normalises it: HnswIndex.java:344, core/Vector.java:107-116) ----
         __syncthreads();
         if (p.profile && tid == 0) S.tp = clock64();
-        for (int i = tid; i < qpad; i += HN_NT) sq[i] = i < p.dim ? p.queries[(size_t)q * p.dim + i] : 0.0f;
+        const float* qsrc = p.qrows ? p.base + (size_t)__ldg(p.qrows + q) * p.dim : p.queries + (size_t)q * p.dim;
+        for (int i = tid; i < qpad; i += HN_NT) sq[i] = i < p.dim ? qsrc[i] : 0.0f;
         for (int i = tid; i < vwords; i += HN_NT) vis[i] = p.dead ? __ldg(p.dead + i) : 0u;
         __syncthreads();
         if (p.metric == 1) {
@@ -936,18 +940,21 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
         const float qnorm = S.qnorm, qq = S.qq;
 
         // ---- B. greedy descent on levels max_level-1 .. 1 (warp 0), then the entry point's layer-0 distance ----
-        if ((p.metric == 0) && p.trained) {
+        const int qe = p.qentry ? __ldg(p.qentry + q) : -1;
+        if (qe >= 0) {
+            if (tid == 0) { fnode[0] = qe; S.nacc = 0; vis[qe >> 5] |= 1u << (qe & 31); }
+        } else if ((p.metric == 0) && p.trained) {
             int cur = p.entry;
-            for (int l = p.max_level - 1; l > 0; l--) cur = greedy_level_pq(p, sq, cur, l, GS, vis);
+            for (int l = p.max_level - 1; l > p.beam_level; l--) cur = greedy_level_pq(p, sq, cur, l, GS, vis);
             if (tid == 0) { fnode[0] = cur; S.nacc = 0; vis[cur >> 5] |= 1u << (cur & 31); }
         } else if (warp == 0) {
             int cur = p.entry;
-            for (int l = p.max_level - 1; l > 0; l--) cur = greedy_level(p, sq, qnorm, cur, l, false, evals, vis);
+            for (int l = p.max_level - 1; l > p.beam_level; l--) cur = greedy_level(p, sq, qnorm, cur, l, false, evals, vis);
             if (lane == 0) { fnode[0] = cur; S.nacc = 0; vis[cur >> 5] |= 1u << (cur & 31); }
         }
         __syncthreads();
         {
-            FreshOut o{fkey, &S.nacc, false, 0.0f};
+            FreshOut o{fkey, &S.nacc, false, 0.0f, false};
             if constexpr (FP8 != 0 && I8) fresh_distances_i8<FP8 ? FP8 : 1>(p, reinterpret_cast<const unsigned char*>(sqh), qnorm, qq, S.qinv, fnode, 1, o);
             else if constexpr (FP8 != 0) fresh_distances_fp8<FP8 ? FP8 : 1>(p, reinterpret_cast<const unsigned char*>(sqh), qnorm, qq, S.qinv, fnode, 1, o);
             else if (BF16) fresh_distances_mma<FULL>(p, sqh, qnorm, qq, fnode, 1, o);
@@ -1029,7 +1036,7 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
                         nb[t] = -1;
                         if (it < nitems) {
                             const int s = nj == 1 ? it : it / nj, j = (it - s * nj) * 32 + lane;
-                            if (j < p.deg) nb[t] = __ldg(p.adj + (size_t)S.sel[s] * p.deg + j);
+                            if (j < p.deg) nb[t] = __ldg(adj0 + (size_t)S.sel[s] * p.deg + j);
                         }
                     }
                     // visited test-and-set of all eight lists first (independent shared-memory atomics, pipelined), then ONE
@@ -1067,6 +1074,11 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
             __syncthreads();
             const int nf = S.nfresh;
             if (tid == 0) { exps += nsel; evals += nf; S.ph[7]++; }
+            // Java's searchLayer (HnswPqIndex.java:876-884, HnswIndex.java:611-625) refreshes `furthest` only when an insert evicts:
+            // until the first eviction it is the ENTRY distance, so what is accepted in the round where the result set fills up (and in
+            // any later round before the first eviction) depends on the order of the neighbours. Such rounds are replayed in that
+            // order by one thread below; they are few (at most until the first eviction) and small.
+            const bool replay = variant != 0 && !evicted && countF == 0 && countP + nf > ef && nf <= 512;
             HN_MARK(2);
             // C3. distances of the fresh rows; acceptance: results.size() < ef || d < furthest
             //     (furthest live: HnswPqIndex.java:953-963; stale == entry distance until the first eviction: :876-884,
@@ -1075,13 +1087,37 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
             {
                 float bound = 0.0f;
                 if (full) bound = (variant == 0 || evicted) ? pool_dist(P[ef - 1]) : S.dentry;
-                FreshOut o{fkey, &S.nacc, full, bound};
+                FreshOut o{fkey, &S.nacc, full, bound, replay};
                 if constexpr (FP8 != 0 && I8) fresh_distances_i8<FP8 ? FP8 : 1>(p, reinterpret_cast<const unsigned char*>(sqh), qnorm, qq, S.qinv, fnode, nf, o);
                 else if constexpr (FP8 != 0) fresh_distances_fp8<FP8 ? FP8 : 1>(p, reinterpret_cast<const unsigned char*>(sqh), qnorm, qq, S.qinv, fnode, nf, o);
                 else if (BF16) fresh_distances_mma<FULL>(p, sqh, qnorm, qq, fnode, nf, o);
                 else fresh_dispatch<false>(p, sq, qnorm, qq, fnode, nf, o);
             }
             __syncthreads();
+            if (replay) {
+                if (tid == 0) {
+                    int size = countP, pe = countP - 1, out = 0, ev = 0;
+                    float furthest = S.dentry;
+                    for (int j = 0; j < nf; j++) {
+                        const uint64_t key = fkey[j];
+                        if (size < ef || pool_dist(key) < furthest) {
+                            fkey[out++] = key; size++;
+                            if (size > ef) {                               // resultSet.poll(): the current maximum leaves
+                                int mi = -1; uint64_t mk = 0;
+                                for (int t = 0; t < out; t++) if ((fkey[t] & ~EXP_BIT) >= mk) { mk = fkey[t] & ~EXP_BIT; mi = t; }
+                                if (pe >= 0 && (P[pe] & ~EXP_BIT) > mk) pe--; else { fkey[mi] = fkey[--out]; }
+                                size--; ev = 1;
+                                float f = pe >= 0 ? pool_dist(P[pe]) : 0.0f;     // furthest = resultSet.peek()
+                                for (int t = 0; t < out; t++) f = fmaxf(f, pool_dist(fkey[t]));
+                                furthest = f;
+                            }
+                        }
+                    }
+                    S.nacc = out;
+                    if (ev) S.evicted = 1;
+                }
+                __syncthreads();
+            }
             const int nacc = S.nacc;
             HN_MARK(3);
             int r0 = newfrontF;

@@ -58,6 +58,11 @@ struct HnswSearchParams {
     int profile;              // accumulate thread-0 cycle counters per phase into counters[2..9]
     int visited_in_smem;
     int prefetch;             // pull fresh rows towards L2 as soon as they are discovered (traversal copy well beyond L2 only)
+    // graph construction (graph_build.cu) runs the same kernel for the inserts of a batch:
+    int beam_level;           // adjacency level the beam walks (0 for searches; l for the level-l links of new nodes)
+    const int* qrows;         // query q = base row qrows[q] (new nodes of a batch that reach this level), or nullptr: queries[q]
+    const int32_t* qentry;    // per-query start node of the beam (>= 0: no greedy descent: the nearest node found on the level above,
+                              // HnswPqIndex.java:526-531), or nullptr / -1: greedy descent from `entry`
 };
 int launch_hnsw_search(const HnswSearchParams& p, int grid, cudaStream_t st);
 size_t hnsw_search_smem_bytes(const HnswSearchParams& p);

@@ -187,6 +187,11 @@ static int build_traversal_rows(vdb_index* x) {
     return VDB_OK;
 }
 
+int vdb_upload_rows_and_traversal_copy(vdb_index* x) {
+    VDB_TRY(upload_rows(x));
+    return build_traversal_rows(x);
+}
+
 static int train_on_device(vdb_index* x, const float* h_samples, int64_t ns) {
     if (ns <= 0) FAIL(VDB_ERR_INVALID, "Invalid training samples");   // PQIndex.cpp:30-32
     const int dim = x->cfg.dim, M = x->pq_m;
@@ -601,6 +606,17 @@ extern "C" int vdb_build(vdb_index* x) {
     x->id2row.clear();
     for (int64_t r = 0; r < x->n; r++) x->id2row[x->h_ids[r]] = r;
     x->n_live = x->n; x->any_dead = false; x->dead_dirty = false; x->h_jindex.clear(); x->java_size = 0; x->jindex_rows.clear();
+    // large rebuilds run on the GPU (graph_build.cu: batched inserts with the beam kernel); strict mode and small indexes keep the
+    // host builder, whose graph is the oracle's link for link
+    const bool pq_ready = t != VDB_INDEX_HNSW_PQ || x->trained;
+    if (!x->g.exact_order && pq_ready && x->n >= 8192 && !getenv("VDB_HOST_GRAPH_BUILD")) {
+        const int ef = t == VDB_INDEX_HNSW_PQ ? std::max(x->cfg.ef_construction, 200) : x->cfg.ef_construction;     // :498 / HnswIndex.java:22
+        VDB_TRY(vdb_gpu_build_graph(x, ef, t == VDB_INDEX_HNSW_PQ ? 1 : 2));
+        x->n_indexed = x->n;
+        x->h_jindex.resize(x->n);
+        std::iota(x->h_jindex.begin(), x->h_jindex.end(), (int64_t)0);
+        x->java_size = x->n;
+    }
     return sync_index(x);
 }
 
@@ -652,10 +668,16 @@ static int search_graph(vdb_index* x, const float* d_q, int64_t nq, int k, int32
     } else { p.variant = 2; p.ef = std::max(x->cfg.ef_search, k * 4); }        // HnswIndex.java:347
     p.ef = (int)std::min<int64_t>(p.ef, std::max<int64_t>(live, 1));
     p.k = k; p.nq = (int)nq;
+    return vdb_graph_search_launch(x, p, st);
+}
+
+// fills the traversal-copy fields and the launch shape of a beam-kernel call and launches it (searches and graph construction)
+int vdb_graph_search_launch(vdb_index* x, HnswSearchParams& p, cudaStream_t st) {
     p.tbase = x->d_trav.p; p.tnorm = x->d_tnorm.p; p.tscale = x->d_tscale.p; p.tstride = trav_stride(x); p.tstore = trav_mode(x);
     // candidates expanded per round: ~1.5 % of the beam keeps >= 99 % of the ids equal to the Java pop order (tests) and halves the
     // per-round bookkeeping of small beams (C1, ef = 1500: 11 -> 23 per round, 4.65 -> 2.9 ms per 1000 queries)
-    p.batch = x->cfg.trav_batch > 0 ? x->cfg.trav_batch : (p.ef >= 4096 ? 64 : std::max(4, std::min(32, p.ef / 64)));
+    if (p.batch <= 0)      // the graph builder presets 1 (the Java pop order)
+        p.batch = x->cfg.trav_batch > 0 ? x->cfg.trav_batch : (p.ef >= 4096 ? 64 : std::max(4, std::min(32, p.ef / 64)));
     p.batch = std::max(1, std::min(p.batch, hnsw_max_batch(p.deg)));
     p.profile = getenv("VDB_HNSW_PROFILE") ? 1 : 0;
     if (const char* eb = getenv("VDB_HNSW_BATCH")) p.batch = std::max(1, std::min(atoi(eb), hnsw_max_batch(p.deg)));
@@ -668,9 +690,9 @@ static int search_graph(vdb_index* x, const float* d_q, int64_t nq, int k, int32
     if (smem > 112 * 1024) { p.visited_in_smem = 0; smem = hnsw_search_smem_bytes(p); }
     if (smem > 227 * 1024) FAIL(VDB_ERR_INVALID, "ef too large for the shared-memory pool");
     int per_sm = (int)std::max<size_t>(1, std::min<size_t>(2, (227 * 1024) / (smem + 1024)));
-    int grid = (int)std::min<int64_t>(nq, (int64_t)x->num_sms * per_sm);
+    int grid = (int)std::min<int64_t>(p.nq, (int64_t)x->num_sms * per_sm);
     if (!p.visited_in_smem) {
-        VDB_TRY(x->d_visited.ensure((size_t)grid * ((x->n + 31) / 32), 0, st));
+        VDB_TRY(x->d_visited.ensure((size_t)grid * ((p.n + 31) / 32), 0, st));
         p.visited_scratch = x->d_visited.p;
     }
     if (x->timed) cudaEventRecord(x->ev_k0, st);

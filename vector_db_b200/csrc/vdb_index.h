@@ -144,3 +144,11 @@ struct vdb_index {
 
     vdb_stats stats{};
 };
+
+struct HnswSearchParams;
+// vdb_api.cu: completes the launch shape of a beam-kernel call (traversal rows, round batch, shared memory, grid) and launches it
+int vdb_graph_search_launch(vdb_index* x, HnswSearchParams& p, cudaStream_t st);
+// graph_build.cu: rebuild the whole graph of a graph index on the GPU (batched inserts); the host graph adopts the result
+int vdb_gpu_build_graph(vdb_index* x, int ef, int variant);
+// vdb_api.cu helpers the builder needs
+int vdb_upload_rows_and_traversal_copy(vdb_index* x);
