@@ -161,6 +161,16 @@ int vdb_encode_all(vdb_index* idx);
 int vdb_pq_lut_device(vdb_index* idx, const float* d_queries, int64_t nq, float* d_lut, void* stream);
 /* ADC distances of every stored row for ONE query's LUT: d_out[n] (test hook, order R3) */
 int vdb_adc_scan_device(vdb_index* idx, const float* d_lut, float* d_out, void* stream);
+/* PQ search in two phases for id-range shards in SEPARATE processes (one per GPU, torch.distributed; inside one process
+ * vdb_config.n_devices does all of this): phase 1 = LUT + ADC scan -> this shard's top-R keys d_keys_out[nq][R] (ordered ADC
+ * distance << 32 | id, ascending; R = max(rerank, k), returned in *shortlist_len; nq <= 1024); the caller all-gathers the keys,
+ * vdb_select_kth_key_device gives the GLOBAL R-th key per query from the g lists [g][nq][R]; phase 2 (vdb_pq_rerank_device, same
+ * queries, right after phase 1 on the same handle) drops the shard's entries above that boundary and re-scores the rest exactly
+ * -> the shard's top-k; vdb_merge_topk_device merges the g lists. The merged answer equals the single-GPU answer bit for bit. */
+int vdb_pq_shortlist_device(vdb_index* idx, const float* d_queries, int64_t nq, int32_t k, uint64_t* d_keys_out, int32_t* shortlist_len, void* stream);
+int vdb_pq_rerank_device(vdb_index* idx, const float* d_queries, int64_t nq, int32_t k, const uint64_t* d_kth /* [nq] or NULL */,
+                         int32_t* d_ids, float* d_dists, void* stream);
+int vdb_select_kth_key_device(const uint64_t* d_keys /* [g][nq][R] */, int32_t g, int64_t nq, int32_t R, uint64_t* d_kth, void* stream);
 /* merge g per-shard result lists [g][nq][k] (dist,id) into [nq][k] ordered by (dist,id) */
 int vdb_merge_topk_device(const float* d_dists, const int32_t* d_ids, int32_t g, int64_t nq, int32_t k,
                           float* d_out_dists, int32_t* d_out_ids, void* stream);

@@ -52,3 +52,71 @@ def test_sharded_search_world2_matches_single_index():
     gi, gd = po.flat_search(X, Q, k)
     assert np.array_equal(ids, gi)
     assert np.array_equal(d.view(np.uint32), gd.view(np.uint32))
+
+
+def _worker_pq(rank, world, port, n, dim, M, nq, k, R, ret):
+    """two-phase PQ search over id-range shards, world 2, on CPU: the local phases are the ORACLE's (checker), the exchange and
+    the boundary logic are the product's host code (vector_db_b200/sharded.py)"""
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from oracle import pyoracle as po
+    from vector_db_b200.sharded import ShardedSearcher, kth_key_host, merge_topk_host, plan_shards
+    lo, hi = plan_shards(n, world)[rank]
+    Xall, Q = po.synth(42, n, dim), po.synth(43, nq, dim)
+    cb = po.pq_train(Xall[:600], M, 25, po.TRAIN_NATIVE_PQ)
+    X = Xall[lo:hi]
+    codes = po.pq_encode(X, cb, po.ARITH_NATIVE_AVX2)
+    gids = np.arange(lo, hi, dtype=np.int32)
+    state = {}
+
+    def key_of(d, i):                                   # the library's key: ordered fp32 bits << 32 | (id ^ 0x80000000)
+        b = d.view(np.uint32).astype(np.uint64)
+        b = np.where(b & 0x80000000, ~b & 0xffffffff, b | 0x80000000)
+        return (b << np.uint64(32)) | (i.astype(np.int64).astype(np.uint64) ^ np.uint64(0x80000000)) & np.uint64(0xffffffff)
+
+    def phase1(q, kk):
+        ids, d = po.pq_flat_search(q.numpy(), cb, codes, R, po.ARITH_NATIVE_AVX2, ids=gids)     # local top-R by (ADC dist, id)
+        keys = key_of(d, ids)
+        keys[ids < 0] = np.uint64(0xffffffffffffffff)
+        state["ids"], state["keys"] = ids, keys
+        return torch.from_numpy(keys.view(np.int64))
+
+    def phase2(q, kk, kth):
+        keep = state["keys"] <= kth.numpy().view(np.uint64)[:, None]
+        out_i = np.full((nq, kk), -1, np.int32); out_d = np.full((nq, kk), np.inf, np.float32)
+        for qi in range(nq):
+            cand = state["ids"][qi][keep[qi]]
+            if cand.size:
+                i2, d2 = po.flat_search(Xall[cand], q.numpy()[qi:qi + 1], min(kk, cand.size), order=1, ids=cand.astype(np.int32))
+                out_i[qi, :i2.shape[1]] = i2[0]; out_d[qi, :i2.shape[1]] = d2[0]
+        return torch.from_numpy(out_i), torch.from_numpy(out_d)
+
+    def merge(all_d, all_i, kk):
+        d, i = merge_topk_host(all_d.numpy(), all_i.numpy(), kk)
+        return torch.from_numpy(d), torch.from_numpy(i)
+
+    s = ShardedSearcher(None, rank, world, merge_fn=merge)
+    ids, d = s.search_pq(torch.from_numpy(Q), k, phase1=phase1, phase2=phase2,
+                         kth_fn=lambda ak, r: torch.from_numpy(kth_key_host(ak.numpy().view(np.uint64), r).view(np.int64)))
+    if rank == 0:
+        ret["ids"], ret["d"] = ids.numpy().copy(), d.numpy().copy()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_sharded_pq_rerank_world2_equals_single_index():
+    from oracle import pyoracle as po
+    po.build()
+    n, dim, M, nq, k, R = 3001, 32, 4, 6, 5, 40
+    with mp.Manager() as mgr:
+        ret = mgr.dict()
+        mp.spawn(_worker_pq, args=(2, 29519, n, dim, M, nq, k, R, ret), nprocs=2, join=True)
+        ids, d = ret["ids"], ret["d"]
+    X, Q = po.synth(42, n, dim), po.synth(43, nq, dim)
+    cb = po.pq_train(X[:600], M, 25, po.TRAIN_NATIVE_PQ)
+    codes = po.pq_encode(X, cb, po.ARITH_NATIVE_AVX2)
+    gi, gd = po.pq_flat_search(Q, cb, codes, k, po.ARITH_NATIVE_AVX2, rerank=R, base=X, exact_order=1)
+    assert np.array_equal(ids, gi)                       # the sharded answer IS the single-index answer (global top-R, then rerank)
+    assert np.array_equal(d.view(np.uint32), gd.view(np.uint32))

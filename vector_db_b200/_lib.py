@@ -20,6 +20,7 @@ SYMBOLS = [
     "vdb_set_codebooks", "vdb_get_codebooks", "vdb_get_codes", "vdb_set_codes", "vdb_set_graph", "vdb_get_graph",
     "vdb_max_level", "vdb_save", "vdb_load", "vdb_fill_synthetic", "vdb_encode_all", "vdb_pq_lut_device",
     "vdb_adc_scan_device", "vdb_merge_topk_device", "vdb_distance_device", "vdb_flat_search_noalloc_device", "vdb_remove", "vdb_contains", "vdb_rows", "vdb_microbench_device",
+    "vdb_pq_shortlist_device", "vdb_pq_rerank_device", "vdb_select_kth_key_device",
 ]
 
 
@@ -86,6 +87,9 @@ def lib():
     L.vdb_adc_scan_device.argtypes = [vp, vp, vp, vp]
     L.vdb_merge_topk_device.argtypes = [vp, vp, i32, i64, i32, vp, vp, vp]
     L.vdb_distance_device.argtypes = [vp, vp, i64, i32, i32, i32, vp, vp]
+    L.vdb_pq_shortlist_device.argtypes = [vp, vp, i64, i32, vp, C.POINTER(i32), vp]
+    L.vdb_pq_rerank_device.argtypes = [vp, vp, i64, i32, vp, vp, vp, vp]
+    L.vdb_select_kth_key_device.argtypes = [vp, i32, i64, i32, vp, vp]
     L.vdb_flat_search_noalloc_device.argtypes = [vp, i64, i32, i32, vp, i64, i32, vp, vp, vp]
     _lib = L
     return L

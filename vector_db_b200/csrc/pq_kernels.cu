@@ -145,6 +145,31 @@ void launch_keys_to_results(const uint64_t* d_keys, int R, int k, int64_t nq, in
     keys_to_results_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(d_keys, R, k, nq, d_ids, d_dists, only_flag);
 }
 
+__global__ void mask_keys_above_kernel(uint64_t* __restrict__ keys, uint32_t* __restrict__ rows, int nq, int R, const uint64_t* __restrict__ kth) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= (int64_t)nq * R) return;
+    if (keys[t] > kth[t / R]) { keys[t] = KEY_MAX; rows[t] = 0xffffffffu; }
+}
+void launch_mask_keys_above(uint64_t* d_keys, uint32_t* d_rows, int nq, int R, const uint64_t* d_kth, cudaStream_t st) {
+    const int64_t tot = (int64_t)nq * R;
+    if (tot > 0) mask_keys_above_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(d_keys, d_rows, nq, R, d_kth);
+}
+// one CTA per query: the g sorted lists are merged by sorting their g * R keys in shared memory; element R-1 is the boundary
+__global__ void select_kth_key_kernel(const uint64_t* __restrict__ keys, int g, int nq, int R, int cap, uint64_t* __restrict__ kth) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint64_t* b = reinterpret_cast<uint64_t*>(smem_raw);
+    const int q = blockIdx.x, total = g * R;
+    for (int i = threadIdx.x; i < cap; i += blockDim.x) b[i] = i < total ? keys[((size_t)(i / R) * nq + q) * R + (i % R)] : KEY_MAX;
+    block_bitonic_sort<false>(b, nullptr, cap);
+    if (threadIdx.x == 0) kth[q] = b[R - 1];
+}
+void launch_select_kth_key(const uint64_t* d_keys, int g, int nq, int R, uint64_t* d_kth, cudaStream_t st) {
+    const int cap = next_pow2(g * R);
+    const size_t smem = (size_t)cap * 8;
+    cudaFuncSetAttribute(select_kth_key_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    select_kth_key_kernel<<<nq, 256, smem, st>>>(d_keys, g, nq, R, cap, d_kth);
+}
+
 // plain ADC distances for one LUT (test hook; order R3)
 __global__ void adc_scan_plain_kernel(const uint8_t* __restrict__ codes, int64_t n, int M, const float* __restrict__ lut_g,
                                       float* __restrict__ out) {

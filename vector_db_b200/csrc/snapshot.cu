@@ -37,6 +37,7 @@ int vdb_validate_graph(const int32_t* levels, const int32_t* adj, int64_t n, int
 
 extern "C" int vdb_save(vdb_index* x, const char* path) {
     if (!x || !path) FAILS(VDB_ERR_INVALID, "vdb_save: bad arguments");
+    if (!x->shards.empty()) FAILS(VDB_ERR_INVALID, "vdb_save: not available on a multi-device index (n_devices > 1)");
     if (x->device_only) FAILS(VDB_ERR_INVALID, "vdb_save: device-generated rows are not persisted");
     const bool graph = x->cfg.index_type == VDB_INDEX_HNSW || x->cfg.index_type == VDB_INDEX_HNSW_PQ;
     if (graph) { int rc = vdb_get_graph(x, nullptr, nullptr, nullptr); if (rc != VDB_OK) return rc; }   // forces a sync
@@ -149,6 +150,7 @@ extern "C" int vdb_load(vdb_index* x, const char* path) {
     if (!x || !path) FAILS(VDB_ERR_INVALID, "vdb_load: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
     VDB_CUDA(cudaSetDevice(x->cfg.device));
+    if (!x->shards.empty()) FAILS(VDB_ERR_INVALID, "vdb_load: not available on a multi-device index (n_devices > 1)");
     if (x->n != 0) FAILS(VDB_ERR_INVALID, "vdb_load: index must be empty");
     try { return load_impl(x, path); }
     catch (const std::bad_alloc&) { FAILS(VDB_ERR_IO, "vdb_load: out of memory (corrupt snapshot header?)"); }

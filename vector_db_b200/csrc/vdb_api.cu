@@ -88,12 +88,19 @@ extern "C" int vdb_create(const vdb_config* cfg, vdb_index** out) {
     cudaEventCreateWithFlags(&x->ev_done, cudaEventDisableTiming);
     if (x->d_counters.ensure(24, 0, x->stream) != VDB_OK) { delete x; return VDB_ERR_CUDA; }
     cudaMemsetAsync(x->d_counters.p, 0, 24 * sizeof(unsigned long long), x->stream);
+    if (c.n_devices > 1) {
+        const int rc = vdb_multi_create(x);
+        if (rc != VDB_OK) { const std::string keep = g_err; vdb_destroy(x); g_err = keep; return rc; }
+    }
     *out = x;
     return VDB_OK;
 }
+#define MULTI(x) (!(x)->shards.empty())
+#define NOT_MULTI(x, what) do { if (MULTI(x)) FAIL(VDB_ERR_INVALID, what ": not available on a multi-device index (n_devices > 1)"); } while (0)
 
 extern "C" int vdb_destroy(vdb_index* x) {
     if (!x) return VDB_OK;
+    if (MULTI(x)) vdb_multi_destroy(x);
     cudaSetDevice(x->cfg.device);
     if (x->stream) cudaStreamSynchronize(x->stream);
     x->d_base.release(); x->d_norms.release(); x->d_cb.release(); x->d_ids.release(); x->d_adj.release(); x->d_codes.release();
@@ -384,7 +391,7 @@ extern "C" int vdb_add_batch(vdb_index* x, const int32_t* ids, const float* vecs
     const size_t old = x->h_vecs.size();
     x->h_vecs.insert(x->h_vecs.end(), vecs, vecs + (size_t)cnt * dim);
     for (int64_t i = 0; i < cnt; i++) x->h_ids.push_back(ids ? ids[i] : (int32_t)(x->cfg.id_offset + x->n + i));
-    if (x->cfg.metric == VDB_METRIC_COSINE && cnt > 0) {
+    if (x->cfg.metric == VDB_METRIC_COSINE && cnt > 0 && !MULTI(x)) {       // (a multi-device front hands raw rows to its shards)
         // normalise on insert (HnswIndex.java:154) with Java's arithmetic, on the device; keep the normalised copy on the host
         VDB_TRY(x->d_q.ensure((size_t)cnt * dim, 0, x->stream));
         VDB_TRY(x->d_out_d.ensure((size_t)cnt, 0, x->stream));
@@ -452,6 +459,7 @@ extern "C" int vdb_train(vdb_index* x, const float* samples, int64_t ns) {
     if (!x || !samples) FAIL(VDB_ERR_INVALID, "Invalid training samples");
     std::lock_guard<std::mutex> lk(x->mu);
     if (x->pq_m == 0) FAIL(VDB_ERR_INVALID, "index has no PQ stage");
+    if (MULTI(x)) return vdb_multi_train(x, samples, ns);
     VDB_CUDA(cudaSetDevice(x->cfg.device));
     VDB_TRY(train_on_device(x, samples, ns));
     x->n_coded = 0;
@@ -461,6 +469,7 @@ extern "C" int vdb_train(vdb_index* x, const float* samples, int64_t ns) {
 extern "C" int vdb_set_codebooks(vdb_index* x, const float* cb) {
     if (!x || !cb || x->pq_m == 0) FAIL(VDB_ERR_INVALID, "vdb_set_codebooks: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
+    if (MULTI(x)) { for (auto* sh : x->shards) VDB_TRY(vdb_set_codebooks(sh, cb)); x->trained = true; return VDB_OK; }
     VDB_CUDA(cudaSetDevice(x->cfg.device));
     const size_t cnt = (size_t)x->pq_m * VDB_NCENT * x->sd;
     VDB_TRY(x->d_cb.ensure(cnt, 0, x->stream));
@@ -472,6 +481,7 @@ extern "C" int vdb_set_codebooks(vdb_index* x, const float* cb) {
 extern "C" int vdb_get_codebooks(vdb_index* x, float* out) {
     if (!x || !out || !x->trained) FAIL(VDB_ERR_UNTRAINED, "no codebooks");
     std::lock_guard<std::mutex> lk(x->mu);
+    if (MULTI(x)) return vdb_get_codebooks(x->shards[0], out);
     VDB_CUDA(cudaSetDevice(x->cfg.device));
     VDB_CUDA(cudaMemcpy(out, x->d_cb.p, (size_t)x->pq_m * VDB_NCENT * x->sd * 4, cudaMemcpyDeviceToHost));
     return VDB_OK;
@@ -479,6 +489,7 @@ extern "C" int vdb_get_codebooks(vdb_index* x, float* out) {
 extern "C" int vdb_set_codes(vdb_index* x, const uint8_t* codes) {
     if (!x || !codes || x->pq_m == 0) FAIL(VDB_ERR_INVALID, "vdb_set_codes: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
+    NOT_MULTI(x, "vdb_set_codes");
     x->h_codes_override.assign(codes, codes + (size_t)x->n * x->pq_m);
     x->codes_overridden = true; x->n_coded = 0;
     return VDB_OK;
@@ -486,6 +497,7 @@ extern "C" int vdb_set_codes(vdb_index* x, const uint8_t* codes) {
 extern "C" int vdb_get_codes(vdb_index* x, uint8_t* out) {
     if (!x || !out || x->pq_m == 0) FAIL(VDB_ERR_INVALID, "vdb_get_codes: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
+    NOT_MULTI(x, "vdb_get_codes");
     VDB_TRY(sync_index(x));
     if (x->n_coded < x->n_dev) FAIL(VDB_ERR_UNTRAINED, "codes not available (untrained)");
     VDB_CUDA(cudaMemcpy(out, x->d_codes.p, (size_t)x->n_dev * x->pq_m, cudaMemcpyDeviceToHost));
@@ -495,6 +507,7 @@ extern "C" int vdb_encode_all(vdb_index* x) {
     if (!x || x->pq_m == 0) FAIL(VDB_ERR_INVALID, "vdb_encode_all: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
     if (!x->trained) FAIL(VDB_ERR_UNTRAINED, "train first");
+    if (MULTI(x)) { VDB_TRY(vdb_multi_sync(x)); return vdb_multi_encode_all(x); }
     VDB_CUDA(cudaSetDevice(x->cfg.device));
     VDB_TRY(upload_rows(x));
     x->n_coded = 0; x->raw_rows = 0;
@@ -544,6 +557,7 @@ extern "C" int vdb_build(vdb_index* x) {
     std::lock_guard<std::mutex> lk(x->mu);
     VDB_CUDA(cudaSetDevice(x->cfg.device));
     const int t = x->cfg.index_type;
+    if (MULTI(x)) return vdb_multi_sync(x);
     if (t == VDB_INDEX_FLAT || t == VDB_INDEX_PQ) return sync_index(x);     // NativeIndex.buildIndex() is a no-op (NativeIndex.java:84-87)
     if (x->device_only) FAIL(VDB_ERR_INVALID, "graph indexes need host rows");
     const int dim = x->cfg.dim;
@@ -626,6 +640,7 @@ extern "C" int vdb_fill_synthetic(vdb_index* x, uint64_t seed, int64_t cnt) {
     if (x->cfg.index_type != VDB_INDEX_FLAT && x->cfg.index_type != VDB_INDEX_PQ) FAIL(VDB_ERR_INVALID, "synthetic fill is for FLAT/PQ indexes");
     if (x->n > 0 && !x->device_only) FAIL(VDB_ERR_INVALID, "index already holds host rows");
     if (x->n + cnt > x->cfg.max_elements) FAIL(VDB_ERR_FULL, "max_elements exceeded");
+    if (MULTI(x)) return vdb_multi_fill_synthetic(x, seed, cnt);
     VDB_CUDA(cudaSetDevice(x->cfg.device));
     const int dim = x->cfg.dim;
     VDB_TRY(x->d_base.ensure((size_t)(x->n + cnt) * dim, (size_t)x->n * dim, x->stream));
@@ -711,54 +726,74 @@ static int pick_chunks(const vdb_index* x, int64_t nq, int64_t n, int R) {
     return c;
 }
 
+// ---- PQ search in two phases, so that shards can agree on ONE global shortlist in between (multi_gpu.cu, vdb_pq_*_device):
+//      phase 1  LUT build + ADC scan -> the shard's top-R keys (ordered ADC distance << 32 | id) in x->d_keys, rows in x->d_rows;
+//      phase 2  entries whose key is above the caller's per-query threshold (the global R-th key) are masked, then the exact
+//               re-score of the rest (or, without rerank, the keys themselves) gives the shard's top-k.
+static inline int pq_shortlist_len(const vdb_index* x, int k) { return x->cfg.rerank > 0 ? std::max(x->cfg.rerank, k) : k; }
+int vdb_pq_phase1(vdb_index* x, const float* d_q, int64_t qb, int k, cudaStream_t st) {
+    const int M = x->pq_m, dim = x->cfg.dim;
+    const int R = pq_shortlist_len(x, k);
+    if (R > 4096) FAIL(VDB_ERR_INVALID, "rerank shortlist > 4096 not supported");
+    if (qb > 1024) FAIL(VDB_ERR_INVALID, "PQ phase 1 handles at most 1024 queries per call");
+    const int32_t* ids = x->device_only ? nullptr : x->d_ids.p;
+    const bool fast = adc_fast_supported(M, R) && !getenv("VDB_ADC_EXACT_SCAN");
+    const int R2 = fast ? adc_fast_r2(R) : R;
+    const int nch = pick_chunks(x, qb, x->n, R2);
+    VDB_TRY(x->d_lut.ensure((size_t)qb * M * VDB_NCENT, 0, st));
+    VDB_TRY(x->d_keys.ensure((size_t)qb * R, 0, st));
+    VDB_TRY(x->d_rows.ensure((size_t)qb * R, 0, st));
+    VDB_TRY(x->d_keys_tmp.ensure((size_t)qb * R2 * (nch + 1), 0, st));
+    VDB_TRY(x->d_rows_tmp.ensure((size_t)qb * R2 * (nch + 1), 0, st));
+    launch_pq_lut(d_q, x->d_cb.p, (int)qb, dim, M, x->cfg.arith, x->d_lut.p, st);
+    if (fast) {
+        const int groups = (M + 63) / 64;
+        VDB_TRY(x->d_lutg.ensure((size_t)qb * groups * 16384, 0, st));
+        VDB_TRY(x->d_flag.ensure((size_t)qb, 0, st));
+        launch_lut_to_gather_layout(x->d_lut.p, (int)qb, M, x->d_lutg.p, st);
+        if (x->timed) cudaEventRecord(x->ev_k0, st);
+        if (launch_adc_scan_fast(x->d_codesT.p, x->d_codes.p, x->n, M, x->d_lut.p, x->d_lutg.p, (int)qb, ids, x->cfg.id_offset, R, nch,
+                                 x->d_keys_tmp.p, x->d_rows_tmp.p, x->d_keys.p, x->d_rows.p, x->d_flag.p, st) != 0)
+            FAIL(VDB_ERR_INVALID, "fast ADC scan rejected the launch");
+        if (x->timed) cudaEventRecord(x->ev_k1, st);
+        // queries whose shortlist could not be certified (massive ties) are redone in the reference's own order
+        launch_adc_scan_topr(x->d_codes.p, x->n, M, x->d_lut.p, (int)qb, ids, x->cfg.id_offset, R, 1, nullptr, nullptr, x->d_keys.p,
+                             x->d_rows.p, st, x->d_flag.p);
+    } else {
+        if (x->timed) cudaEventRecord(x->ev_k0, st);
+        launch_adc_scan_topr(x->d_codes.p, x->n, M, x->d_lut.p, (int)qb, ids, x->cfg.id_offset, R, nch, x->d_keys_tmp.p, x->d_rows_tmp.p,
+                             x->d_keys.p, x->d_rows.p, st);
+        if (x->timed) cudaEventRecord(x->ev_k1, st);
+    }
+    VDB_CUDA(cudaGetLastError());
+    x->stats.adc_rows += qb * x->n;
+    return VDB_OK;
+}
+int vdb_pq_phase2(vdb_index* x, const float* d_q, int64_t qb, int k, const uint64_t* d_kth, int32_t* d_ids, float* d_dists, cudaStream_t st) {
+    const int R = pq_shortlist_len(x, k);
+    const int32_t* ids = x->device_only ? nullptr : x->d_ids.p;
+    if (d_kth) launch_mask_keys_above(x->d_keys.p, x->d_rows.p, (int)qb, R, d_kth, st);
+    if (x->cfg.rerank > 0)
+        launch_rerank(x->d_base.p, ids, x->cfg.id_offset, x->cfg.dim, d_q, (int)qb, x->d_rows.p, R,
+                      x->cfg.arith == VDB_ARITH_NATIVE_AVX2 ? ORDER_R1 : ORDER_SEQ, k, d_ids, d_dists, st);
+    else
+        launch_keys_to_results(x->d_keys.p, R, k, qb, d_ids, d_dists, st);
+    VDB_CUDA(cudaGetLastError());
+    return VDB_OK;
+}
+
 static int search_pq(vdb_index* x, const float* d_q, int64_t nq, int k, int32_t* d_ids, float* d_dists, cudaStream_t st) {
     if (!x->trained) {   // PQIndex.cpp:147-150 / :259-270: untrained -> no results
         launch_keys_to_results(nullptr, 0, k, nq, d_ids, d_dists, st);
         return VDB_OK;
     }
-    const int M = x->pq_m, dim = x->cfg.dim;
-    const int R = x->cfg.rerank > 0 ? std::max(x->cfg.rerank, k) : k;
-    if (R > 4096) FAIL(VDB_ERR_INVALID, "rerank shortlist > 4096 not supported");
+    const int dim = x->cfg.dim;
     const int64_t QB = 1024;   // query sub-batch: bounds the LUT buffers (QB * M * 1 KB each)
-    const int32_t* ids = x->device_only ? nullptr : x->d_ids.p;
-    const bool fast = adc_fast_supported(M, R) && !getenv("VDB_ADC_EXACT_SCAN");
-    const int R2 = fast ? adc_fast_r2(R) : R;
     for (int64_t q0 = 0; q0 < nq; q0 += QB) {
         const int64_t qb = std::min(QB, nq - q0);
-        const int nch = pick_chunks(x, qb, x->n, R2);
-        VDB_TRY(x->d_lut.ensure((size_t)qb * M * VDB_NCENT, 0, st));
-        VDB_TRY(x->d_keys.ensure((size_t)qb * R, 0, st));
-        VDB_TRY(x->d_rows.ensure((size_t)qb * R, 0, st));
-        VDB_TRY(x->d_keys_tmp.ensure((size_t)qb * R2 * (nch + 1), 0, st));
-        VDB_TRY(x->d_rows_tmp.ensure((size_t)qb * R2 * (nch + 1), 0, st));
-        launch_pq_lut(d_q + q0 * dim, x->d_cb.p, (int)qb, dim, M, x->cfg.arith, x->d_lut.p, st);
-        if (fast) {
-            const int groups = (M + 63) / 64;
-            VDB_TRY(x->d_lutg.ensure((size_t)qb * groups * 16384, 0, st));
-            VDB_TRY(x->d_flag.ensure((size_t)qb, 0, st));
-            launch_lut_to_gather_layout(x->d_lut.p, (int)qb, M, x->d_lutg.p, st);
-            if (x->timed && q0 == 0) cudaEventRecord(x->ev_k0, st);
-            if (launch_adc_scan_fast(x->d_codesT.p, x->d_codes.p, x->n, M, x->d_lut.p, x->d_lutg.p, (int)qb, ids, x->cfg.id_offset, R, nch,
-                                     x->d_keys_tmp.p, x->d_rows_tmp.p, x->d_keys.p, x->d_rows.p, x->d_flag.p, st) != 0)
-                FAIL(VDB_ERR_INVALID, "fast ADC scan rejected the launch");
-            if (x->timed && q0 == 0) cudaEventRecord(x->ev_k1, st);
-            // queries whose shortlist could not be certified (massive ties) are redone in the reference's own order
-            launch_adc_scan_topr(x->d_codes.p, x->n, M, x->d_lut.p, (int)qb, ids, x->cfg.id_offset, R, 1, nullptr, nullptr, x->d_keys.p,
-                                 x->d_rows.p, st, x->d_flag.p);
-        } else {
-            if (x->timed && q0 == 0) cudaEventRecord(x->ev_k0, st);
-            launch_adc_scan_topr(x->d_codes.p, x->n, M, x->d_lut.p, (int)qb, ids, x->cfg.id_offset, R, nch, x->d_keys_tmp.p, x->d_rows_tmp.p,
-                                 x->d_keys.p, x->d_rows.p, st);
-            if (x->timed && q0 == 0) cudaEventRecord(x->ev_k1, st);
-        }
-        if (x->cfg.rerank > 0)
-            launch_rerank(x->d_base.p, ids, x->cfg.id_offset, dim, d_q + q0 * dim, (int)qb, x->d_rows.p, R,
-                          x->cfg.arith == VDB_ARITH_NATIVE_AVX2 ? ORDER_R1 : ORDER_SEQ, k, d_ids + q0 * k, d_dists + q0 * k, st);
-        else
-            launch_keys_to_results(x->d_keys.p, R, k, qb, d_ids + q0 * k, d_dists + q0 * k, st);
-        VDB_CUDA(cudaGetLastError());
+        VDB_TRY(vdb_pq_phase1(x, d_q + q0 * dim, qb, k, st));
+        VDB_TRY(vdb_pq_phase2(x, d_q + q0 * dim, qb, k, nullptr, d_ids + q0 * k, d_dists + q0 * k, st));
     }
-    x->stats.adc_rows += nq * x->n;
     return VDB_OK;
 }
 
@@ -866,10 +901,16 @@ static int search_device_locked(vdb_index* x, const float* d_q, int64_t nq, int 
     return rc;
 }
 
+int vdb_search_device_nolock(vdb_index* x, const float* d_q, int64_t nq, int k, int32_t* d_ids, float* d_dists, cudaStream_t st) {
+    return search_device_locked(x, d_q, nq, k, d_ids, d_dists, st);
+}
+int vdb_sync_index_nolock(vdb_index* x) { return sync_index(x); }
+
 extern "C" int vdb_search_batch_device(vdb_index* x, const float* d_q, int64_t nq, int32_t k, int32_t* d_ids, float* d_dists, void* stream) {
     if (!x || nq < 0 || k <= 0 || (nq > 0 && (!d_q || !d_ids || !d_dists))) FAIL(VDB_ERR_INVALID, "vdb_search_batch_device: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
     cudaStream_t st = (cudaStream_t)stream;   // verbatim cudaStream_t: NULL is CUDA's legacy default stream
+    if (MULTI(x)) return vdb_multi_search(x, d_q, true, nq, k, d_ids, d_dists, st);      // buffers on the front device (cfg.device)
     return search_device_locked(x, d_q, nq, k, d_ids, d_dists, st);
 }
 
@@ -878,6 +919,7 @@ extern "C" int vdb_search_batch(vdb_index* x, const float* q, int64_t nq, int32_
     std::lock_guard<std::mutex> lk(x->mu);
     VDB_CUDA(cudaSetDevice(x->cfg.device));
     if (nq == 0) return VDB_OK;
+    if (MULTI(x)) return vdb_multi_search(x, q, false, nq, k, out_ids, out_d, x->stream);
     const int dim = x->cfg.dim;
     cudaStream_t st = x->stream;
     VDB_TRY(x->d_q.ensure((size_t)nq * dim, 0, st));
@@ -901,6 +943,7 @@ extern "C" int vdb_search_batch(vdb_index* x, const float* q, int64_t nq, int32_
 extern "C" int vdb_get_stats(vdb_index* x, vdb_stats* out) {
     if (!x || !out) FAIL(VDB_ERR_INVALID, "vdb_get_stats: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
+    if (MULTI(x)) return vdb_multi_stats(x, out);
     VDB_CUDA(cudaSetDevice(x->cfg.device));
     if (x->timed) {
         VDB_CUDA(cudaEventSynchronize(x->ev_total1));
@@ -925,6 +968,7 @@ extern "C" int vdb_get_stats(vdb_index* x, vdb_stats* out) {
 extern "C" int vdb_pq_lut_device(vdb_index* x, const float* d_q, int64_t nq, float* d_lut, void* stream) {
     if (!x || !d_q || !d_lut || x->pq_m == 0) FAIL(VDB_ERR_INVALID, "vdb_pq_lut_device: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
+    NOT_MULTI(x, "vdb_pq_lut_device");
     if (!x->trained) FAIL(VDB_ERR_UNTRAINED, "train first");
     cudaStream_t st = (cudaStream_t)stream;   // verbatim cudaStream_t: NULL is CUDA's legacy default stream
     launch_pq_lut(d_q, x->d_cb.p, (int)nq, x->cfg.dim, x->pq_m, x->cfg.arith, d_lut, st);
@@ -934,10 +978,41 @@ extern "C" int vdb_pq_lut_device(vdb_index* x, const float* d_q, int64_t nq, flo
 extern "C" int vdb_adc_scan_device(vdb_index* x, const float* d_lut, float* d_out, void* stream) {
     if (!x || !d_lut || !d_out || x->pq_m == 0) FAIL(VDB_ERR_INVALID, "vdb_adc_scan_device: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
+    NOT_MULTI(x, "vdb_adc_scan_device");
     VDB_TRY(sync_index(x));
     if (x->n_coded < x->n) FAIL(VDB_ERR_UNTRAINED, "no codes");
     cudaStream_t st = (cudaStream_t)stream;   // verbatim cudaStream_t: NULL is CUDA's legacy default stream
     launch_adc_scan_plain(x->d_codes.p, x->n, x->pq_m, d_lut, d_out, st);
+    VDB_CUDA(cudaGetLastError());
+    return VDB_OK;
+}
+// ---- the two PQ phases and the boundary selection as device-level calls: one process per GPU (torch.distributed) runs phase 1,
+//      all-gathers the keys (ONE collective of nq x R x 8 bytes), selects the global boundary, runs phase 2, all-gathers the top-k ----
+extern "C" int vdb_pq_shortlist_device(vdb_index* x, const float* d_q, int64_t nq, int32_t k, uint64_t* d_keys_out, int32_t* shortlist_len, void* stream) {
+    if (!x || !d_q || !d_keys_out || nq <= 0 || k <= 0 || x->cfg.index_type != VDB_INDEX_PQ) FAIL(VDB_ERR_INVALID, "vdb_pq_shortlist_device: bad arguments");
+    std::lock_guard<std::mutex> lk(x->mu);
+    NOT_MULTI(x, "vdb_pq_shortlist_device");
+    if (!x->trained) FAIL(VDB_ERR_UNTRAINED, "train first");
+    VDB_TRY(sync_index(x));
+    cudaStream_t st = (cudaStream_t)stream;
+    const int R = pq_shortlist_len(x, k);
+    if (shortlist_len) *shortlist_len = R;
+    if (x->n == 0) { VDB_CUDA(cudaMemsetAsync(d_keys_out, 0xff, (size_t)nq * R * 8, st)); return VDB_OK; }
+    VDB_TRY(vdb_pq_phase1(x, d_q, nq, k, st));
+    VDB_CUDA(cudaMemcpyAsync(d_keys_out, x->d_keys.p, (size_t)nq * R * 8, cudaMemcpyDeviceToDevice, st));
+    return VDB_OK;
+}
+extern "C" int vdb_pq_rerank_device(vdb_index* x, const float* d_q, int64_t nq, int32_t k, const uint64_t* d_kth, int32_t* d_ids, float* d_dists, void* stream) {
+    if (!x || !d_q || !d_ids || !d_dists || nq <= 0 || k <= 0 || x->cfg.index_type != VDB_INDEX_PQ) FAIL(VDB_ERR_INVALID, "vdb_pq_rerank_device: bad arguments");
+    std::lock_guard<std::mutex> lk(x->mu);
+    NOT_MULTI(x, "vdb_pq_rerank_device");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (x->n == 0) { launch_keys_to_results(nullptr, 0, k, nq, d_ids, d_dists, st); return VDB_OK; }
+    return vdb_pq_phase2(x, d_q, nq, k, d_kth, d_ids, d_dists, st);
+}
+extern "C" int vdb_select_kth_key_device(const uint64_t* d_keys, int32_t g, int64_t nq, int32_t R, uint64_t* d_kth, void* stream) {
+    if (!d_keys || !d_kth || g <= 0 || R <= 0 || nq <= 0 || (int64_t)g * R > 16384) FAIL(VDB_ERR_INVALID, "vdb_select_kth_key_device: bad arguments (g x R <= 16384)");
+    launch_select_kth_key(d_keys, g, (int)nq, R, d_kth, (cudaStream_t)stream);
     VDB_CUDA(cudaGetLastError());
     return VDB_OK;
 }

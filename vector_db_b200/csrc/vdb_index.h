@@ -143,6 +143,16 @@ struct vdb_index {
     DevBuf<int> d_asg;
 
     vdb_stats stats{};
+
+    // multi-device index (cfg.n_devices > 1, FLAT / PQ; multi_gpu.cu): this object is the front, the rows live in `shards`
+    std::vector<vdb_index*> shards;         // one single-device index per GPU (device cfg.device + s), id-range shards
+    std::vector<cudaEvent_t> shard_ev;      // per shard: "my part of the step is done"
+    cudaEvent_t ev_front = nullptr;         // front (device cfg.device): "the gathered data is merged / the boundary is known"
+    int64_t n_distributed = 0;              // host rows already handed to the shards
+    DevBuf<uint64_t> g_keys, g_kth;         // front device: gathered shortlist keys [g][qb][R], global boundary [qb]
+    DevBuf<uint64_t> d_kth;                 // shard: its copy of the boundary
+    DevBuf<float> g_d;                      // gathered results [g][qb][k]
+    DevBuf<int32_t> g_i;
 };
 
 struct HnswSearchParams;
@@ -150,5 +160,19 @@ struct HnswSearchParams;
 int vdb_graph_search_launch(vdb_index* x, HnswSearchParams& p, cudaStream_t st);
 // graph_build.cu: rebuild the whole graph of a graph index on the GPU (batched inserts); the host graph adopts the result
 int vdb_gpu_build_graph(vdb_index* x, int ef, int variant);
+int vdb_pq_phase1(vdb_index* x, const float* d_q, int64_t qb, int k, cudaStream_t st);
+int vdb_pq_phase2(vdb_index* x, const float* d_q, int64_t qb, int k, const uint64_t* d_kth, int32_t* d_ids, float* d_dists, cudaStream_t st);
 // vdb_api.cu helpers the builder needs
 int vdb_upload_rows_and_traversal_copy(vdb_index* x);
+// multi_gpu.cu
+int vdb_multi_create(vdb_index* front);
+void vdb_multi_destroy(vdb_index* front);
+int vdb_multi_train(vdb_index* front, const float* samples, int64_t ns);
+int vdb_multi_sync(vdb_index* front);
+int vdb_multi_fill_synthetic(vdb_index* front, uint64_t seed, int64_t cnt);
+int vdb_multi_encode_all(vdb_index* front);
+int vdb_multi_search(vdb_index* front, const float* q, bool q_on_device, int64_t nq, int k, int32_t* out_ids, float* out_d, cudaStream_t user_stream);
+int vdb_multi_stats(vdb_index* front, vdb_stats* out);
+// per-shard search without the handle's mutex juggling (vdb_api.cu)
+int vdb_search_device_nolock(vdb_index* x, const float* d_q, int64_t nq, int k, int32_t* d_ids, float* d_dists, cudaStream_t st);
+int vdb_sync_index_nolock(vdb_index* x);

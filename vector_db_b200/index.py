@@ -56,6 +56,8 @@ class GpuIndex:
             from .database import CompressionConfig
             self.pq_m = CompressionConfig.recommendedConfig(dimension).pqSubspaces
         self.hnsw_m = cfg.hnsw_m
+        self.rerank = cfg.rerank
+        self.n_devices = max(1, cfg.n_devices)
 
     # ---- lifecycle ----
     def close(self):

@@ -41,6 +41,13 @@ def merge_topk_host(dists, ids, k):
     return out_d, out_i
 
 
+def kth_key_host(keys, R):
+    """numpy statement of vdb_select_kth_key_device: keys [g][nq][R] (uint64, each list ascending, 2^64-1 = empty) -> the R-th
+    smallest key per query = the boundary of the GLOBAL shortlist"""
+    g, nq, r = keys.shape
+    return np.sort(np.transpose(keys, (1, 0, 2)).reshape(nq, g * r), axis=1)[:, R - 1].copy()
+
+
 class ShardedSearcher:
     """Wraps one local GpuIndex shard per rank. `search(d_queries, k)` returns the merged global top-k on every rank."""
 
@@ -60,6 +67,50 @@ class ShardedSearcher:
         _lib.check(_lib.lib().vdb_merge_topk_device(all_d.data_ptr(), all_i.data_ptr(), g, nq, k, out_d.data_ptr(),
                                                     out_i.data_ptr(), st))
         return out_d, out_i
+
+    def search_pq(self, d_queries, k, phase1=None, phase2=None, kth_fn=None):
+        """PQ shards (with or without rerank) in two phases so that the answer does not depend on the number of shards: every rank
+        scans its codes (phase 1: local top-R keys), ONE all_gather of the keys, the global R-th key per query bounds the global
+        shortlist, every rank re-scores only its own rows inside it (phase 2) and the top-k lists are merged as in `search`.
+        phase1(q, k) -> uint64 keys [nq][R]; phase2(q, k, kth) -> (ids, dists); injectable for the CPU (gloo) tests."""
+        import torch
+        import torch.distributed as dist
+        if phase1 is None:
+            from . import _lib
+            import ctypes as C
+            L, h = _lib.lib(), self.index._h
+            st = torch.cuda.current_stream(d_queries.device).cuda_stream
+            nq = d_queries.shape[0]
+
+            def phase1(q, kk):
+                R = C.c_int32(0)
+                keys = torch.empty((nq, max(self.index_rerank(), kk)), dtype=torch.int64, device=q.device)
+                _lib.check(L.vdb_pq_shortlist_device(h, q.data_ptr(), nq, kk, keys.data_ptr(), C.byref(R), st))
+                assert R.value == keys.shape[1]
+                return keys
+
+            def phase2(q, kk, kth):
+                ids = torch.empty((nq, kk), dtype=torch.int32, device=q.device)
+                d = torch.empty((nq, kk), dtype=torch.float32, device=q.device)
+                _lib.check(L.vdb_pq_rerank_device(h, q.data_ptr(), nq, kk, 0 if kth is None else kth.data_ptr(), ids.data_ptr(), d.data_ptr(), st))
+                return ids, d
+
+            def kth_fn(all_keys, R):
+                out = torch.empty((nq,), dtype=torch.int64, device=all_keys.device)
+                _lib.check(L.vdb_select_kth_key_device(all_keys.data_ptr(), all_keys.shape[0], nq, R, out.data_ptr(), st))
+                return out
+        keys = phase1(d_queries, k)
+        if self.world == 1:
+            ids, d = phase2(d_queries, k, None)
+            return ids, d
+        nq, R = keys.shape
+        all_keys = torch.empty((self.world * nq, R), dtype=keys.dtype, device=keys.device)
+        dist.all_gather_into_tensor(all_keys, keys.contiguous(), group=self.group)
+        kth = kth_fn(all_keys.view(self.world, nq, R), R)
+        return self.search(d_queries, k, local_search=lambda q, kk: phase2(q, kk, kth))
+
+    def index_rerank(self):
+        return int(getattr(self.index, "rerank", 0))
 
     def search(self, d_queries, k, local_search=None):
         import torch
