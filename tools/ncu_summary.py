@@ -1,11 +1,15 @@
 #!/usr/bin/env python
-"""tools/ncu_summary.py <report.ncu-rep> — print the roofline-relevant raw metrics and the stall mix of the last kernel
+"""tools/ncu_summary.py <report.ncu-rep> [kernel-substring] — print the roofline-relevant raw metrics and the stall mix of the last kernel
 in an ncu report (read on the CPU box: `ncu -i`). Output is what gets committed under profiles/."""
 import csv, subprocess, sys
 rep = sys.argv[1]
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(raw.splitlines()))
 hdr, units, vals = rows[0], rows[1], rows[-1]
+if len(sys.argv) > 2:                       # kernel-name substring: the longest matching launch
+    ki, ti = hdr.index("Kernel Name"), hdr.index("gpu__time_duration.sum")
+    m = [r for r in rows[2:] if sys.argv[2] in r[ki]]
+    vals = max(m, key=lambda r: float(r[ti].replace(",", "")))
 want = ["Kernel Name", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "dram__throughput.avg.pct_of_peak_sustained_elapsed",
         "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "lts__t_bytes.sum", "lts__t_sector_hit_rate.pct",
         "lts__throughput.avg.pct_of_peak_sustained_elapsed", "l1tex__throughput.avg.pct_of_peak_sustained_elapsed",

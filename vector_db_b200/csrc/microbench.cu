@@ -92,7 +92,8 @@ extern "C" int vdb_microbench_device(int32_t kind, int64_t rows, int32_t row_byt
     std::vector<float> ms;
     double units = 0;
     if (kind == 0 || kind == 1) {
-        if (rows <= 0 || row_bytes <= 0 || (row_bytes % 1024) != 0 || work <= 0) { vdb_set_error("row gather: rows > 0, row_bytes % 1024 == 0, work = rows gathered per CTA"); return VDB_ERR_INVALID; }
+        // kind 0 keeps 2 lines per row in flight (row_bytes % 256 == 0: 512-byte int8 rows included), kind 1 keeps 8 (or 4 for 512-byte rows)
+        if (rows <= 0 || row_bytes <= 0 || (row_bytes % (kind == 0 ? 256 : 512)) != 0 || work <= 0) { vdb_set_error("row gather: rows > 0, row_bytes % 256 (kind 0) / % 512 (kind 1) == 0, work = rows gathered per CTA"); return VDB_ERR_INVALID; }
         const int grid = sms * 2, per_cta = (work + 127) / 128 * 128;
         unsigned char* table = nullptr; int* idx = nullptr; uint32_t* sink = nullptr;
         VDB_CUDA(cudaMalloc(&table, (size_t)rows * row_bytes));
@@ -105,7 +106,8 @@ extern "C" int vdb_microbench_device(int32_t kind, int64_t rows, int32_t row_byt
         for (int r = 0; r < reps + 2; r++) {
             cudaEventRecord(e0);
             if (kind == 0) row_gather_kernel<2><<<grid, 256>>>(table, idx, per_cta, row_bytes, sink);
-            else row_gather_kernel<8><<<grid, 256>>>(table, idx, per_cta, row_bytes, sink);
+            else if (row_bytes % 1024 == 0) row_gather_kernel<8><<<grid, 256>>>(table, idx, per_cta, row_bytes, sink);
+            else row_gather_kernel<4><<<grid, 256>>>(table, idx, per_cta, row_bytes, sink);
             cudaEventRecord(e1);
             VDB_CUDA(cudaEventSynchronize(e1));
             float t; cudaEventElapsedTime(&t, e0, e1);
