@@ -15,6 +15,9 @@
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <string>
+#include <thread>
+#include <vector>
 
 #include "kernels.h"
 #include "vdb_index.h"
@@ -116,6 +119,28 @@ int vdb_multi_stats(vdb_index* f, vdb_stats* out) {
     return VDB_OK;
 }
 
+// Run fn(shard) for every shard, each on its own host thread: the shards' search calls block the calling thread in places
+// (certification read-backs), so issuing them from one thread would serialise the GPUs. Errors travel back with their message
+// (vdb_last_error is per thread).
+template <class F>
+static int for_each_shard(vdb_index* f, F fn) {
+    const int g = (int)f->shards.size();
+    std::vector<int> rc(g, VDB_OK);
+    std::vector<std::string> msg(g);
+    auto run = [&](int s) {
+        if (cudaSetDevice(f->shards[s]->cfg.device) != cudaSuccess) { rc[s] = VDB_ERR_CUDA; msg[s] = "cudaSetDevice failed"; return; }
+        rc[s] = fn(s);
+        if (rc[s] != VDB_OK) msg[s] = vdb_last_error();
+    };
+    std::vector<std::thread> th;
+    for (int s = 1; s < g; s++) th.emplace_back(run, s);
+    run(0);
+    for (auto& t : th) t.join();
+    cudaSetDevice(f->cfg.device);
+    for (int s = 0; s < g; s++) if (rc[s] != VDB_OK) { vdb_set_error(msg[s]); return rc[s]; }
+    return VDB_OK;
+}
+
 int vdb_multi_search(vdb_index* f, const float* q, bool q_on_device, int64_t nq, int k, int32_t* out_ids, float* out_d, cudaStream_t user_stream) {
     const int g = (int)f->shards.size(), dim = f->cfg.dim, d0 = f->cfg.device;
     VDB_TRY(vdb_multi_sync(f));
@@ -138,7 +163,7 @@ int vdb_multi_search(vdb_index* f, const float* q, bool q_on_device, int64_t nq,
         const int R = pq ? (f->cfg.rerank > 0 ? std::max(f->cfg.rerank, k) : k) : 0;
         if (pq && (int64_t)g * R > 16384) MG_FAIL(VDB_ERR_INVALID, "multi-device PQ search: n_devices x shortlist > 16384 not supported");
         if ((int64_t)g * k > 8192) MG_FAIL(VDB_ERR_INVALID, "multi-device search: n_devices x k > 8192 not supported");
-        const int64_t QB = 1024;
+        const int64_t QB = pq ? 1024 : 8192;        // flat: whole batches (the GEMM wants many query tiles); PQ: the LUT scratch is per query
         VDB_TRY(f->g_d.ensure((size_t)g * nq * k, 0, fs)); VDB_TRY(f->g_i.ensure((size_t)g * nq * k, 0, fs));
         if (pq) { VDB_TRY(f->g_keys.ensure((size_t)g * QB * R, 0, fs)); VDB_TRY(f->g_kth.ensure((size_t)QB, 0, fs)); }
         // queries to every shard
@@ -155,32 +180,29 @@ int vdb_multi_search(vdb_index* f, const float* q, bool q_on_device, int64_t nq,
                 VDB_CUDA(cudaMemcpyAsync(sh->d_q.p, f->p_q.p, (size_t)nq * dim * 4, cudaMemcpyHostToDevice, sh->stream));
             }
         }
+        VDB_CUDA(cudaSetDevice(d0));
         for (int64_t q0 = 0; q0 < nq; q0 += QB) {
             const int64_t qb = std::min(QB, nq - q0);
             float* gd = f->g_d.p + (size_t)g * q0 * k; int32_t* gi = f->g_i.p + (size_t)g * q0 * k;
             if (pq) {
-                for (int s = 0; s < g; s++) {
+                for (int s = 0; s < g; s++)
+                    if (vdb_size(f->shards[s]) == 0) VDB_CUDA(cudaMemsetAsync(f->g_keys.p + (size_t)s * qb * R, 0xff, (size_t)qb * R * 8, fs));
+                VDB_TRY(for_each_shard(f, [&](int s) -> int {
                     vdb_index* sh = f->shards[s];
-                    VDB_CUDA(cudaSetDevice(sh->cfg.device));
                     if (q0 > 0) VDB_CUDA(cudaStreamWaitEvent(sh->stream, f->ev_front, 0));       // g_keys of the previous sub-batch consumed
                     if (vdb_size(sh) > 0) {
                         VDB_TRY(vdb_pq_phase1(sh, sh->d_q.p + q0 * dim, qb, k, sh->stream));
                         VDB_CUDA(cudaMemcpyPeerAsync(f->g_keys.p + (size_t)s * qb * R, d0, sh->d_keys.p, sh->cfg.device, (size_t)qb * R * 8, sh->stream));
-                    } else {
-                        VDB_CUDA(cudaSetDevice(d0));
-                        VDB_CUDA(cudaMemsetAsync(f->g_keys.p + (size_t)s * qb * R, 0xff, (size_t)qb * R * 8, fs));
-                        VDB_CUDA(cudaSetDevice(sh->cfg.device));
                     }
                     VDB_CUDA(cudaEventRecord(f->shard_ev[s], sh->stream));
-                }
-                VDB_CUDA(cudaSetDevice(d0));
+                    return VDB_OK;
+                }));
                 for (int s = 0; s < g; s++) VDB_CUDA(cudaStreamWaitEvent(fs, f->shard_ev[s], 0));
                 launch_select_kth_key(f->g_keys.p, g, (int)qb, R, f->g_kth.p, fs);
                 VDB_CUDA(cudaEventRecord(f->ev_front, fs));
             }
-            for (int s = 0; s < g; s++) {
+            VDB_TRY(for_each_shard(f, [&](int s) -> int {
                 vdb_index* sh = f->shards[s];
-                VDB_CUDA(cudaSetDevice(sh->cfg.device));
                 if (vdb_size(sh) > 0) {
                     if (pq) {
                         VDB_CUDA(cudaStreamWaitEvent(sh->stream, f->ev_front, 0));
@@ -196,7 +218,8 @@ int vdb_multi_search(vdb_index* f, const float* q, bool q_on_device, int64_t nq,
                 VDB_CUDA(cudaMemcpyPeerAsync(gd + (size_t)s * qb * k, d0, sh->d_out_d.p, sh->cfg.device, (size_t)qb * k * 4, sh->stream));
                 VDB_CUDA(cudaMemcpyPeerAsync(gi + (size_t)s * qb * k, d0, sh->d_out_ids.p, sh->cfg.device, (size_t)qb * k * 4, sh->stream));
                 VDB_CUDA(cudaEventRecord(f->shard_ev[s], sh->stream));
-            }
+                return VDB_OK;
+            }));
             VDB_CUDA(cudaSetDevice(d0));
             for (int s = 0; s < g; s++) VDB_CUDA(cudaStreamWaitEvent(fs, f->shard_ev[s], 0));
             launch_merge_topk(gd, gi, g, qb, k, o_d + q0 * k, o_ids + q0 * k, fs);
