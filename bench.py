@@ -433,7 +433,7 @@ def flat_gemm_aux(v, po, torch, rows, pk):
                        "threshold_select + flat_shortlist (fp32 R6 order)"}
 
 
-def sharded_aux(v, po, torch, dist, rank, world, local, rows_c5, rows_c4):
+def sharded_aux(v, po, torch, dist, rank, world, local, rows_c5, rows_c4, cpu_group=None):
     """BASELINE.json configs[4] / [3] sharded by contiguous id range over all ranks. C5 runs in two phases so that
     the answer does not depend on the number of shards: every rank scans its N/g code rows (local top-R keys), ONE all_gather of the
     keys, the global R-th key bounds the global shortlist, every rank re-scores only its own rows inside it, then one all_gather of the
@@ -461,6 +461,12 @@ def sharded_aux(v, po, torch, dist, rank, world, local, rows_c5, rows_c4):
 
     def bits(a):
         return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+    def host_wait():
+        # ranks waiting for rank 0's single-process work must NOT wait inside an NCCL kernel: it would sit on their GPU and
+        # time-slice against rank 0's n_devices shards running there
+        torch.cuda.synchronize()
+        dist.barrier(group=cpu_group)
 
     out = {}
     NS = 64                                                # queries of the N = 1 comparison
@@ -492,7 +498,7 @@ def sharded_aux(v, po, torch, dist, rank, world, local, rows_c5, rows_c4):
             line["e2e"] = {"value": nq / el, "unit": "queries/s", "h2d_bytes_per_step": nq * dim * 4, "d2h_bytes_per_step": nq * k * 8}
         p.close()
         if world > 1:
-            dist.barrier()
+            host_wait()
             if rank == 0:
                 try:
                     # (1) the whole index on ONE GPU: the N = 1 answer for the first NS queries
@@ -519,7 +525,7 @@ def sharded_aux(v, po, torch, dist, rank, world, local, rows_c5, rows_c4):
                                                      "dist_bits_equal_torchrun_path": bool(np.array_equal(bits(fd), bits(md)))}
                 except Exception as e:
                     line["vs_single_gpu_error"] = str(e)
-            dist.barrier()
+            host_wait()
         out["c5_sharded"] = line
     if rows_c4 > 0 and world > 1:
         dim, nq, k = 768, 4096, 100
@@ -535,7 +541,7 @@ def sharded_aux(v, po, torch, dist, rank, world, local, rows_c5, rows_c4):
         f.close()
         line = {"workload": "C4: %d x 768-d flat sq-L2, %d queries, k=%d, rows split by id over %d GPUs" % (rows_c4, nq, k, world),
                 "ms_per_batch": ms, "qps": nq / ms * 1e3, "tflops_all_gpus": 2.0 * nq * rows_c4 * dim / (ms * 1e-3) / 1e12, "scaling": "strong"}
-        dist.barrier()
+        host_wait()
         if rank == 0:
             try:
                 one = v.NativeFlatIndex(dim, rows_c4, device=local)
@@ -559,7 +565,7 @@ def sharded_aux(v, po, torch, dist, rank, world, local, rows_c5, rows_c4):
                                                  "dist_bits_equal_torchrun_path": bool(np.array_equal(bits(gd), bits(md)))}
             except Exception as e:
                 line["vs_single_gpu_error"] = str(e)
-        dist.barrier()
+        host_wait()
         out["c4_sharded"] = line
     return out
 
@@ -688,9 +694,11 @@ def run_b200(args, rank, world):
     from vector_db_b200 import synth as sy
     if rank == 0:
         ge.build_product()
+    cpu_group = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ.get("LOCAL_RANK", 0))))
         dist.barrier()
+        cpu_group = dist.new_group(backend="gloo")        # host-side waits (no kernel parked on a GPU while another rank works on it)
     import vector_db_b200 as v
     local = int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
@@ -762,7 +770,7 @@ def run_b200(args, rank, world):
     sharded = None
     if args.shard_rows > 0:
         try:
-            sharded = sharded_aux(v, po, torch, dist, rank, world, local, args.shard_rows, args.flat_rows)
+            sharded = sharded_aux(v, po, torch, dist, rank, world, local, args.shard_rows, args.flat_rows, cpu_group)
         except Exception as e:
             sharded = {"error": str(e)}
 
