@@ -100,6 +100,10 @@ const char* vdb_version(void);
 /* fills *cfg with the defaults of the given reference class */
 int vdb_default_config(int32_t index_type, int32_t dim, int32_t max_elements, vdb_config* cfg);
 
+/* Device contract: every entry point that takes an index handle makes the index's device (cfg.device) current in the calling
+ * thread with cudaSetDevice and leaves it current on return; callers that use several devices re-select their own afterwards.
+ * An index with cfg.n_devices = g > 1 (FLAT / PQ only) owns id-range shards on devices cfg.device .. cfg.device + g - 1 and
+ * returns with cfg.device current. */
 /* nativeCreateHNSW / nativeCreatePQ (VectorDBJNI.cpp:39-65) — one constructor for all index types */
 int vdb_create(const vdb_config* cfg, vdb_index** out);
 /* nativeDestroy (VectorDBJNI.cpp:161-164) */
