@@ -740,7 +740,7 @@ struct HnswShared {
     uint64_t ckP[HN_MAXB], ckF[HN_MAXB];  // their keys (expanded bit clear): the rank-merge of the two lists reads these
     int sel[HN_MAXB];
     int wsum[HN_WARPS], wsum2[HN_WARPS];
-    int nfresh, nacc, takenP;
+    int nfresh, nacc, takenP, nextq;
     int countP, countF;   // entries in the main array (<= ef) / side buffer
     int frontP, frontF;   // every entry below these indices carries the expanded bit
     int whichF;           // which of the two side-buffer halves is current
@@ -748,6 +748,7 @@ struct HnswShared {
     float dentry, qnorm, qq, qinv;
     long long ph[8];      // profile: per-phase cycles of thread 0
     long long tp;
+    long long sub[4];     // profile: cycles of the C0 folds, number of C0 folds, scan cycles, cycles of the folds inside sort / merge
     long long hist[4];    // profile: rounds with > 256 accepted keys, sum of accepted keys, rounds with 129..256, sort cycles of the first
 };
 
@@ -895,10 +896,10 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
     const int uncertain_ok = B == 1 ? 1 : 128;    // side-buffer entries tolerated while candidates come from the array's tail
     unsigned long long evals = 0, exps = 0;
     if (tid < 8) S.ph[tid] = 0;
-    if (tid < 4) S.hist[tid] = 0;
+    if (tid < 4) { S.hist[tid] = 0; S.sub[tid] = 0; }
 #define HN_MARK(slot) do { if (p.profile && tid == 0) { const long long now_ = clock64(); S.ph[slot] += now_ - S.tp; S.tp = now_; } } while (0)
 
-    for (int q = blockIdx.x; q < p.nq; q += gridDim.x) {
+    for (int q = blockIdx.x; q < p.nq;) {
         // ---- A. stage the query (HnswIndex normalises it: HnswIndex.java:344, core/Vector.java:107-116) ----
         __syncthreads();
         if (p.profile && tid == 0) S.tp = clock64();
@@ -1014,9 +1015,13 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
             //     the buffer holds entries that may push that tail out of the best ef
             {
                 const int cP = S.countP, cF = S.countF;
-                if (cF > 0 && (cP < ef || cF > HN_FTH || (S.frontP + B > ef - cF && cF >= uncertain_ok)))
+                if (cF > 0 && (cP < ef || cF > HN_FTH || (S.frontP + B > ef - cF && cF >= uncertain_ok))) {
+                    const long long t0_ = (p.profile && tid == 0) ? clock64() : 0;
                     fold_side_buffer(P, F0, S, ef, reinterpret_cast<int*>(fkey));     // fkey is idle here
+                    if (p.profile && tid == 0) { S.sub[0] += clock64() - t0_; S.sub[1]++; }
+                }
             }
+            const long long ts_ = (p.profile && tid == 0) ? clock64() : 0;
             const uint64_t* Fc = F0 + (size_t)S.whichF * HN_FCAP;
             uint64_t* Fc_w = F0 + (size_t)S.whichF * HN_FCAP;
             uint64_t* Fn = F0 + (size_t)(S.whichF ^ 1) * HN_FCAP;
@@ -1030,6 +1035,7 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
             // C1. candidates.poll() x B: the B best unexpanded entries of array + buffer
             int toP, toF, fndP, fndF;
             scan_unexpanded2(P, S.frontP, lim, Fc, S.frontF, countF, B, S, &fndP, &toP, &fndF, &toF);
+            if (p.profile && tid == 0) S.sub[2] += clock64() - ts_;
             const int a = min(fndP, B), b = min(fndF, B);
             if (a + b == 0) break;                                    // no eligible candidate left: the search ends
             const int nsel = min(a + b, B);
@@ -1237,6 +1243,13 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
             }
         }
         HN_MARK(6);
+        // next query: the first one is blockIdx.x, the following ones are handed out dynamically (queries differ in length)
+        if (p.qcounter) {
+            __syncthreads();
+            if (tid == 0) S.nextq = (int)gridDim.x + atomicAdd(p.qcounter, 1);
+            __syncthreads();
+            q = S.nextq;
+        } else q += gridDim.x;
     }
     if (p.counters && tid == 0) {
         if (evals) atomicAdd(&p.counters[0], evals);
@@ -1244,6 +1257,7 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
         if (p.profile) {
             for (int i = 0; i < 8; i++) atomicAdd(&p.counters[2 + i], (unsigned long long)S.ph[i]);
             for (int i = 0; i < 4; i++) atomicAdd(&p.counters[12 + i], (unsigned long long)S.hist[i]);
+            for (int i = 0; i < 4; i++) atomicAdd(&p.counters[17 + i], (unsigned long long)S.sub[i]);
         }
     }
 }

@@ -711,6 +711,8 @@ int vdb_graph_search_launch(vdb_index* x, HnswSearchParams& p, cudaStream_t st) 
         p.visited_scratch = x->d_visited.p;
     }
     if (x->timed) cudaEventRecord(x->ev_k0, st);
+    p.qcounter = reinterpret_cast<int*>(x->d_counters.p + 22);
+    VDB_CUDA(cudaMemsetAsync(p.qcounter, 0, sizeof(unsigned long long), st));
     int rc = launch_hnsw_search(p, grid, st);
     if (rc != 0) FAIL(VDB_ERR_INVALID, rc == 1 ? "k or degree too large for the graph kernel" : "shared memory request rejected");
     if (x->timed) cudaEventRecord(x->ev_k1, st);
@@ -950,13 +952,15 @@ extern "C" int vdb_get_stats(vdb_index* x, vdb_stats* out) {
         cudaEventElapsedTime(&x->stats.last_total_ms, x->ev_total0, x->ev_total1);
         if (cudaEventElapsedTime(&x->stats.last_kernel_ms, x->ev_k0, x->ev_k1) != cudaSuccess) { x->stats.last_kernel_ms = 0; cudaGetLastError(); }
     }
-    unsigned long long c[16] = {0};
+    unsigned long long c[24] = {0};
     VDB_CUDA(cudaMemcpy(c, x->d_counters.p, sizeof(c), cudaMemcpyDeviceToHost));
     if (getenv("VDB_HNSW_PROFILE"))
         fprintf(stderr, "[vdb hnsw profile] cycles: setup %llu select %llu gather %llu dist %llu sort %llu merge %llu final %llu | rounds %llu\n",
                 c[2], c[3], c[4], c[5], c[6], c[7], c[8], c[9]);
-    if (getenv("VDB_HNSW_PROFILE"))
+    if (getenv("VDB_HNSW_PROFILE")) {
+        fprintf(stderr, "[vdb hnsw profile] select split: C0 folds %llu cycles in %llu folds, candidate scan %llu cycles\n", c[17], c[18], c[19]);
         fprintf(stderr, "[vdb hnsw profile] accepted keys: sum %llu | rounds with > 256: %llu (sort cycles %llu), with 129..256: %llu\n", c[13], c[12], c[15], c[14]);
+    }
     x->stats.dist_evals = (int64_t)c[0]; x->stats.expansions = (int64_t)c[1];
     x->stats.flat_certified = (int64_t)c[10]; x->stats.flat_fallback = (int64_t)c[11];
     x->stats.trav_format = x->trav_eff == 0 ? VDB_TRAV_F32 : (x->trav_eff == 2 ? VDB_TRAV_FP8 : (x->trav_eff == 3 ? VDB_TRAV_INT8 : VDB_TRAV_BF16));
