@@ -428,6 +428,50 @@ __device__ __forceinline__ int count_le_i32(const int* __restrict__ r, int n, in
     return lo;
 }
 
+// N binary searches in lock-step: the trip count depends on n only (halving form), so the N dependent chains of shared-memory
+// loads are independent of each other and overlap — the `while (lo < hi)` forms above have data-dependent trip counts and run
+// one after the other. Same results as count_le_i32 / lower_bound_u64.
+template <int N>
+__device__ __forceinline__ void count_le_i32_multi(const int* __restrict__ r, int n, const int (&x)[N], int (&out)[N]) {
+    if (n <= 0) {
+#pragma unroll
+        for (int t = 0; t < N; t++) out[t] = 0;
+        return;
+    }
+    int base[N];
+#pragma unroll
+    for (int t = 0; t < N; t++) base[t] = 0;
+    int len = n;
+    while (len > 1) {
+        const int half = len >> 1;
+#pragma unroll
+        for (int t = 0; t < N; t++) base[t] += (r[base[t] + half - 1] <= x[t]) ? half : 0;
+        len -= half;
+    }
+#pragma unroll
+    for (int t = 0; t < N; t++) out[t] = base[t] + ((r[base[t]] <= x[t]) ? 1 : 0);
+}
+template <int N>
+__device__ __forceinline__ void lower_bound_u64_multi(const uint64_t* __restrict__ a, int n, const uint64_t (&key)[N], int (&out)[N]) {
+    if (n <= 0) {
+#pragma unroll
+        for (int t = 0; t < N; t++) out[t] = 0;
+        return;
+    }
+    int base[N];
+#pragma unroll
+    for (int t = 0; t < N; t++) base[t] = 0;
+    int len = n;
+    while (len > 1) {
+        const int half = len >> 1;
+#pragma unroll
+        for (int t = 0; t < N; t++) base[t] += ((a[base[t] + half - 1] & ~EXP_BIT) < key[t]) ? half : 0;
+        len -= half;
+    }
+#pragma unroll
+    for (int t = 0; t < N; t++) out[t] = base[t] + (((a[base[t]] & ~EXP_BIT) < key[t]) ? 1 : 0);
+}
+
 // ---- bf16 traversal distances on the tensor pipe ------------------------------------------------------------------------
 // The fresh rows of a round form a [rows x D] bf16 matrix that is multiplied by ONE vector (the query): a gather-bound
 // matrix-vector product. It is issued as mma.sync m16n8k16 (16 rows per warp tile; the 8 result columns all hold the same
@@ -725,8 +769,21 @@ __device__ __forceinline__ void chunk_sort_merge(uint64_t* __restrict__ keys, in
         const uint64_t key = keys[idx];
         const int mych = idx / CH;
         int r = idx - mych * CH;
-        for (int ch = 0; ch < nch; ch++)
-            if (ch != mych) r += lower_bound_u64(keys + ch * CH, min(CH, n - ch * CH), key);
+        // the <= 7 searches run in lock-step over whole chunks (the ragged last chunk is padded with KEY_MAX, which no key is below)
+        int base[HN_WARPS];
+#pragma unroll
+        for (int ch = 0; ch < HN_WARPS; ch++) base[ch] = ch * CH;
+        int len = CH;
+        while (len > 1) {
+            const int half = len >> 1;
+#pragma unroll
+            for (int ch = 0; ch < HN_WARPS; ch++)
+                if (ch < nch) base[ch] += (keys[base[ch] + half - 1] < key) ? half : 0;
+            len -= half;
+        }
+#pragma unroll
+        for (int ch = 0; ch < HN_WARPS; ch++)
+            if (ch < nch && ch != mych) r += base[ch] - ch * CH + ((keys[base[ch]] < key) ? 1 : 0);
         out[r] = key;
     }
     __syncthreads();
@@ -812,19 +869,40 @@ __device__ __forceinline__ void scan_unexpanded2(const uint64_t* __restrict__ a,
     *foundA_ = foundA; *toA = min(posA, limA); *foundB_ = foundB; *toB = min(posB, limB);
 }
 
+// rr[j] = number of entries of the sorted array a[0..na) below s[j] (expanded bits ignored), four searches per thread in lock-step
+__device__ __forceinline__ void rank_keys(const uint64_t* __restrict__ a, int na, const uint64_t* __restrict__ s, int ns, int* __restrict__ rr) {
+    for (int j0 = threadIdx.x; j0 < ns; j0 += 4 * HN_NT) {
+        uint64_t key[4]; int r[4];
+#pragma unroll
+        for (int t = 0; t < 4; t++) { const int j = j0 + t * HN_NT; key[t] = j < ns ? (s[j] & ~EXP_BIT) : 0ull; }
+        lower_bound_u64_multi<4>(a, na, key, r);
+#pragma unroll
+        for (int t = 0; t < 4; t++) { const int j = j0 + t * HN_NT; if (j < ns) rr[j] = r[t]; }
+    }
+}
+
 // Merge the sorted keys s[0..ns) into the sorted array a[0..na) writing out[0..min(na+ns,cap)) (out != a): every
 // element finds its final slot by ranking (rr[j] = #a-entries below s[j]). Barriers inside; rr is scratch [ns].
 __device__ __forceinline__ void merge_ranked(const uint64_t* __restrict__ a, int na, const uint64_t* __restrict__ s, int ns,
                                              uint64_t* __restrict__ out, int cap, int* __restrict__ rr) {
     const int tid = threadIdx.x;
-    for (int j = tid; j < ns; j += HN_NT) rr[j] = lower_bound_u64(a, na, s[j] & ~EXP_BIT);
+    rank_keys(a, na, s, ns, rr);
     __syncthreads();
     const int r0 = rr[0];
-#pragma unroll 4
-    for (int i = tid; i < na; i += HN_NT) {
-        const uint64_t e = a[i];
-        const int np = i < r0 ? i : i + count_le_i32(rr, ns, i);
-        if (np < cap) out[np] = e;
+    for (int i0 = tid; i0 < na; i0 += 4 * HN_NT) {
+        int x[4], c[4];
+#pragma unroll
+        for (int t = 0; t < 4; t++) x[t] = i0 + t * HN_NT;
+        if (i0 + 3 * HN_NT < r0) {                                   // below the first insertion point nothing moves
+#pragma unroll
+            for (int t = 0; t < 4; t++) out[x[t]] = a[x[t]];
+            continue;
+        }
+        count_le_i32_multi<4>(rr, ns, x, c);
+#pragma unroll
+        for (int t = 0; t < 4; t++) {
+            if (x[t] < na) { const int np = x[t] + c[t]; if (np < cap) out[np] = a[x[t]]; }
+        }
     }
     for (int j = tid; j < ns; j += HN_NT) { const int np = rr[j] + j; if (np < cap) out[np] = s[j]; }
     __syncthreads();
@@ -835,18 +913,20 @@ __device__ __forceinline__ void merge_ranked(const uint64_t* __restrict__ a, int
 __device__ __forceinline__ void merge_ranked_inplace(uint64_t* __restrict__ a, int na, const uint64_t* __restrict__ s, int ns, int cap,
                                                      int* __restrict__ rr) {
     const int tid = threadIdx.x;
-    for (int j = tid; j < ns; j += HN_NT) rr[j] = lower_bound_u64(a, na, s[j] & ~EXP_BIT);
+    rank_keys(a, na, s, ns, rr);
     __syncthreads();
     const int r0 = rr[0];
     constexpr int PERC = 4;
     for (int hi = na; hi > r0; hi -= HN_NT * PERC) {
         const int lo = max(r0, hi - HN_NT * PERC);
-        uint64_t e[PERC]; int np[PERC];
+        uint64_t e[PERC]; int np[PERC], x[PERC], c[PERC];
+#pragma unroll
+        for (int t = 0; t < PERC; t++) x[t] = lo + tid + t * HN_NT;
+        count_le_i32_multi<PERC>(rr, ns, x, c);
 #pragma unroll
         for (int t = 0; t < PERC; t++) {
-            const int i = lo + tid + t * HN_NT;
             np[t] = -1;
-            if (i < hi) { e[t] = a[i]; np[t] = i + count_le_i32(rr, ns, i); }
+            if (x[t] < hi) { e[t] = a[x[t]]; np[t] = x[t] + c[t]; }
         }
         __syncthreads();
 #pragma unroll
