@@ -677,8 +677,26 @@ def recall_gate_c2(v, po, torch, cores):
     cpu_s = time.perf_counter() - t0
     orec = float(np.mean([len(set(a) & set(b)) / K for a, b in zip(oid, gt)]))
     idx.close()
+    # the reference's NATIVE HNSWIndex (sq-L2, its own graph and dynamic ef), compiled unmodified into oracle/_ref
+    native = None
+    try:
+        if po.ref_available() and hasattr(po.ref(), "ref_hnsw_create"):
+            r = po.RefHnsw(dim, n, M=32, efC=64, ef=64)
+            t0 = time.perf_counter()
+            r.add_batch(X, np.arange(n, dtype=np.int32))
+            nb = time.perf_counter() - t0
+            r.search_batch(Q[:50], K)
+            t0 = time.perf_counter()
+            rid, _ = r.search_batch(Q, K)
+            ns_ = time.perf_counter() - t0
+            gl2, _ = po.flat_search(X, Q, K, nthreads=cores)
+            native = {"kind": "reference", "what": "native HNSWIndex::searchBatch (sq-L2, own graph, 4 threads hard-wired, HNSWIndex.cpp:543-571)",
+                      "qps": nq / ns_, "recall_at_10_l2": recall(rid, gl2), "build_s": nb}
+            r.close()
+    except Exception as e:
+        native = {"error": str(e)}
     t = float(np.median(ms)) * 1e-3
-    return {"workload": "C2: 10k x 128-d, HNSW uncompressed (cosine, ef=400), 1000 queries, k=10", "qps_device": nq / t, "kernel_ms": t * 1e3,
+    return {"native_hnsw_reference": native, "workload": "C2: 10k x 128-d, HNSW uncompressed (cosine, ef=400), 1000 queries, k=10", "qps_device": nq / t, "kernel_ms": t * 1e3,
             "recall_at_10": rec, "reference_recall_at_10": orec, "id_match_vs_oracle": float((ids == oid).mean()),
             "flat_gemm_ids_equal_cpu_bruteforce": float((fi == gt).mean()), "cpu_port_qps": nq / cpu_s, "cpu_cores": cores,
             "note": "the reference's HnswIndex.searchLayer compares candidates with a `furthest` that stays at the entry distance until the "

@@ -473,6 +473,17 @@ def ref():
         R.ref_hnswpq_search.argtypes = [C.c_void_p, _f32p, C.c_int, _i32p, _f32p]; R.ref_hnswpq_search.restype = C.c_int
         R.ref_hnswpq_search_batch.argtypes = [C.c_void_p, _f32p, C.c_int, C.c_int, _i32p, _f32p]
         R.ref_hnswpq_pq_distance.argtypes = [C.c_void_p, _f32p, C.c_int]; R.ref_hnswpq_pq_distance.restype = C.c_float
+        if hasattr(R, "ref_hnsw_create"):
+            R.ref_hnsw_create.argtypes = [C.c_int] * 5; R.ref_hnsw_create.restype = C.c_void_p
+            R.ref_hnsw_destroy.argtypes = [C.c_void_p]
+            R.ref_hnsw_add.argtypes = [C.c_void_p, C.c_int, _f32p]; R.ref_hnsw_add.restype = C.c_int
+            R.ref_hnsw_add_batch.argtypes = [C.c_void_p, _f32p, _i32p, C.c_int]; R.ref_hnsw_add_batch.restype = C.c_int
+            R.ref_hnsw_size.argtypes = [C.c_void_p]; R.ref_hnsw_size.restype = C.c_int
+            R.ref_hnsw_search.argtypes = [C.c_void_p, _f32p, C.c_int, _i32p, _f32p]; R.ref_hnsw_search.restype = C.c_int
+            R.ref_hnsw_search_batch.argtypes = [C.c_void_p, _f32p, C.c_int, C.c_int, _i32p, _f32p]
+            R.ref_hnsw_entry.argtypes = [C.c_void_p]; R.ref_hnsw_entry.restype = C.c_int
+            R.ref_hnsw_node_level.argtypes = [C.c_void_p, C.c_int]; R.ref_hnsw_node_level.restype = C.c_int
+            R.ref_hnsw_neighbors.argtypes = [C.c_void_p, C.c_int, C.c_int, _i32p, C.c_int]; R.ref_hnsw_neighbors.restype = C.c_int
         _ref = R
     return _ref
 
@@ -559,3 +570,54 @@ class RefHnswPq:
         d = np.full((q.shape[0], k), np.inf, dtype=np.float32)
         ref().ref_hnswpq_search_batch(self.h, q, q.shape[0], k, ids, d)
         return ids, d
+
+
+class RefHnsw:
+    """The reference's native HNSWIndex, unmodified (native/index/HNSWIndex.cpp; BLAS calls through oracle/shim/cblas.h)."""
+
+    def __init__(self, dim, max_elements, M=32, efC=64, ef=64):
+        self.dim, self.M = dim, M
+        self.h = ref().ref_hnsw_create(dim, max_elements, M, efC, ef)
+        assert self.h
+
+    def close(self):
+        if self.h:
+            ref().ref_hnsw_destroy(self.h)
+            self.h = None
+
+    def add(self, id_, v):
+        return ref().ref_hnsw_add(self.h, int(id_), _f32(v)) == 0
+
+    def add_batch(self, vecs, ids):
+        v = _f32(vecs)
+        assert ref().ref_hnsw_add_batch(self.h, v, np.ascontiguousarray(ids, dtype=np.int32), v.shape[0]) == 0
+
+    def size(self):
+        return ref().ref_hnsw_size(self.h)
+
+    def search(self, q, k):
+        ids = np.full(k, -1, dtype=np.int32)
+        d = np.full(k, np.inf, dtype=np.float32)
+        cnt = ref().ref_hnsw_search(self.h, _f32(q), k, ids, d)
+        return ids, d, cnt
+
+    def search_batch(self, queries, k):
+        q = _f32(queries)
+        ids = np.full((q.shape[0], k), -1, dtype=np.int32)
+        d = np.full((q.shape[0], k), np.inf, dtype=np.float32)
+        ref().ref_hnsw_search_batch(self.h, q, q.shape[0], k, ids, d)
+        return ids, d
+
+    def graph(self):
+        """(levels[n], {level: adj[n][2M] padded with -1}, entry)"""
+        n = self.size()
+        levels = np.array([ref().ref_hnsw_node_level(self.h, i) for i in range(n)], dtype=np.int32)
+        adj = {}
+        buf = np.empty(4 * self.M, dtype=np.int32)
+        for lv in range(int(levels.max()) + 1 if n else 0):
+            a = np.full((n, 2 * self.M), -1, dtype=np.int32)
+            for i in np.nonzero(levels >= lv)[0]:
+                c = ref().ref_hnsw_neighbors(self.h, int(i), lv, buf, buf.size)
+                a[i, :min(c, 2 * self.M)] = buf[:min(c, 2 * self.M)]
+            adj[lv] = a
+        return levels, adj, ref().ref_hnsw_entry(self.h)

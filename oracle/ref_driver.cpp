@@ -30,6 +30,7 @@
 #define private public
 #include "index/PQIndex.h"
 #include "index/HNSWPQIndex.h"
+#include "index/HNSWIndex.h"
 #undef private
 #include "compute/ADCUtils.h"
 #include "compute/DistanceUtils.h"
@@ -87,3 +88,53 @@ REF_API int ref_hnswpq_add(void* h, int id, const float* v) { try { ((HNSWPQInde
 REF_API int ref_hnswpq_search(void* h, const float* q, int k, int* ids, float* d) { int c = 0; ((HNSWPQIndex*)h)->search(q, k, ids, d, &c); return c; }
 REF_API void ref_hnswpq_search_batch(void* h, const float* q, int nq, int k, int* ids, float* d) { ((HNSWPQIndex*)h)->searchBatch(q, nq, k, ids, d); }
 REF_API float ref_hnswpq_pq_distance(void* h, const float* q, int node) { return ((HNSWPQIndex*)h)->computeDistancePQ(q, node); }
+
+// ---- the three BLAS calls of native/compute/BatchDistance.cpp (declared in oracle/shim/cblas.h): the reference's own fallback
+//      loops (BatchDistance.cpp:36-46, 62-70, 98-105), row-major, the only argument combinations the reference uses ----
+extern "C" {
+#include "cblas.h"
+void cblas_sgemm(enum CBLAS_ORDER, enum CBLAS_TRANSPOSE, enum CBLAS_TRANSPOSE, int m, int n, int k, float alpha, const float* A, int lda,
+                 const float* B, int ldb, float beta, float* C, int ldc) {          // C = alpha * A * B^T + beta * C
+    for (int i = 0; i < m; i++)
+        for (int j = 0; j < n; j++) {
+            float sum = 0.0f;
+            for (int l = 0; l < k; l++) sum += A[(size_t)i * lda + l] * B[(size_t)j * ldb + l];
+            C[(size_t)i * ldc + j] = alpha * sum + (beta == 0.0f ? 0.0f : beta * C[(size_t)i * ldc + j]);
+        }
+}
+float cblas_sdot(int n, const float* x, int incx, const float* y, int incy) {
+    float sum = 0.0f;
+    for (int i = 0; i < n; i++) sum += x[(size_t)i * incx] * y[(size_t)i * incy];
+    return sum;
+}
+void cblas_sgemv(enum CBLAS_ORDER, enum CBLAS_TRANSPOSE, int m, int n, float alpha, const float* A, int lda, const float* x, int incx,
+                 float beta, float* y, int incy) {                                   // y = alpha * A * x + beta * y
+    for (int i = 0; i < m; i++) {
+        float sum = 0.0f;
+        for (int j = 0; j < n; j++) sum += A[(size_t)i * lda + j] * x[(size_t)j * incx];
+        y[(size_t)i * incy] = alpha * sum + (beta == 0.0f ? 0.0f : beta * y[(size_t)i * incy]);
+    }
+}
+}
+
+// ---- native HNSWIndex (native/index/HNSWIndex.cpp): the one beam search of the reference that runs on this image ----
+REF_API void* ref_hnsw_create(int dim, int maxElements, int M, int efC, int ef) {
+    HNSWConfig c; c.M = M; c.efConstruction = efC; c.efSearch = ef;
+    try { return new HNSWIndex(dim, maxElements, c); } catch (...) { return nullptr; }
+}
+REF_API void ref_hnsw_destroy(void* h) { delete (HNSWIndex*)h; }
+REF_API int ref_hnsw_add(void* h, int id, const float* v) { try { ((HNSWIndex*)h)->add(id, v); return 0; } catch (...) { return 1; } }
+REF_API int ref_hnsw_add_batch(void* h, const float* v, const int* ids, int n) { try { ((HNSWIndex*)h)->addBatch(v, ids, n); return 0; } catch (...) { return 1; } }
+REF_API int ref_hnsw_size(void* h) { return ((HNSWIndex*)h)->size(); }
+REF_API int ref_hnsw_search(void* h, const float* q, int k, int* ids, float* d) { int c = 0; ((HNSWIndex*)h)->search(q, k, ids, d, &c); return c; }
+REF_API void ref_hnsw_search_batch(void* h, const float* q, int nq, int k, int* ids, float* d) { ((HNSWIndex*)h)->searchBatch(q, nq, k, ids, d); }
+REF_API int ref_hnsw_entry(void* h) { return ((HNSWIndex*)h)->entryPoint_.load(); }
+REF_API int ref_hnsw_node_level(void* h, int node) { return ((HNSWIndex*)h)->nodes_[node].level; }
+// neighbours of `node` on `level` into out[cap]; returns the count
+REF_API int ref_hnsw_neighbors(void* h, int node, int level, int* out, int cap) {
+    auto& nb = ((HNSWIndex*)h)->nodes_[node].neighbors;
+    if (level < 0 || level >= (int)nb.size()) return 0;
+    int n = std::min<int>(cap, (int)nb[level].size());
+    for (int i = 0; i < n; i++) out[i] = nb[level][i];
+    return n;
+}
