@@ -126,7 +126,9 @@ def test_c3_headline_shape_sample(v, po):
     b1.set_codebooks(state[3]); b1.set_graph(state[0], list(state[1]), state[2]); b1.set_codes(state[4])
     bid, bd = b1.searchBatch(Q[:64], k)
     b1.close()
-    assert (bid == jid[:64]).mean() >= 0.995
+    # bf16 rounding can flip one comparison early in a walk, after which that query's whole list may differ (the graph is built on the
+    # device and differs from run to run, so WHICH query does varies): the bar is per id over the sample, with room for one such query
+    assert (bid == jid[:64]).mean() >= 0.97
     same = ids == jid
     assert np.array_equal(bits(d[same]), bits(jd[same]))
     st = g.stats()

@@ -55,11 +55,12 @@ def test_product_walks_the_reference_built_graph(po, native):
     g = v.NativeHnswPqIndex(dim, 2 * n, M=2 * M, ef=64, pqM=8, level_seed=1234)
     g.addBatch(np.arange(n, dtype=np.int32), X)                                     # trains + encodes (300-insert trigger); own graph replaced below
     L = g.max_level
-    # the product's convention (Java's): levels[i] = number of layers node i is on; adj[l][i][0..hnsw_m) padded with -1
+    # the product's convention (Java's, and the native class's): levels[i] = top layer of node i; adj[l][i][0..hnsw_m) padded with -1
     A = np.full((L, n, 2 * M), -1, dtype=np.int32)
     for lv, a in adj.items():
-        A[lv] = a
-    g.set_graph(levels + 1, list(A), entry)
+        if lv < L:            # the Java level cap (log(maxElements)/log(M)) can be below the native one: layers above it are dropped,
+            A[lv] = a         # the native entry point (on every layer) stays the entry
+    g.set_graph(np.minimum(levels, L - 1), list(A), entry)
     ids, d = g.searchBatch(Q, k)
     rg, rr = recall(ids, gt), recall(rid, gt)
     assert rg >= rr - 0.02, (rg, rr)                                                # same graph, beam >= the reference's

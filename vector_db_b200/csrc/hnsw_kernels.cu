@@ -29,6 +29,9 @@
 #define EXP_BIT 0x80000000ull
 #define HN_FMAX 2048      // fresh rows per round (batch * deg <= HN_FMAX)
 #define HN_MAXB 64
+#ifndef HN_SMALL_SORT
+#define HN_SMALL_SORT 128   // rounds with at most this many accepted keys are sorted by counting ranks
+#endif
 
 
 __device__ __forceinline__ uint64_t pool_key(float d, int node) { return ((uint64_t)f2ord(d) << 32) | (uint32_t)node; }
@@ -789,6 +792,19 @@ __device__ __forceinline__ void chunk_sort_merge(uint64_t* __restrict__ keys, in
     __syncthreads();
 }
 
+// Small rounds (n <= HN_NT): every key counts the keys below it (broadcast reads, no sorting network, one barrier). Keys are unique.
+__device__ __forceinline__ void count_rank_sort(const uint64_t* __restrict__ keys, int n, uint64_t* __restrict__ out) {
+    const int tid = threadIdx.x;
+    if (tid < n) {
+        const uint64_t key = keys[tid];
+        int r = 0;
+#pragma unroll 8
+        for (int j = 0; j < n; j++) r += (keys[j] < key) ? 1 : 0;
+        out[r] = key;
+    }
+    __syncthreads();
+}
+
 #define HN_FCAP 2048      // side buffer capacity (entries); must stay >= HN_FMAX (a round's accepted keys always fit)
 #define HN_FTH 1024       // side buffer is folded into the main array when it holds more than this
 
@@ -1251,7 +1267,8 @@ __global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchP
                 bool direct = false;
                 if (nacc <= 8 * 128) {
                     uint64_t* sk = reinterpret_cast<uint64_t*>(fnode);          // fnode (idle after the distance phase) holds 1024 keys
-                    if (nacc <= 8 * 64) chunk_sort_merge<2>(fkey, nacc, sk); else chunk_sort_merge<4>(fkey, nacc, sk);
+                    if (nacc <= HN_SMALL_SORT) count_rank_sort(fkey, nacc, sk);
+                    else if (nacc <= 8 * 64) chunk_sort_merge<2>(fkey, nacc, sk); else chunk_sort_merge<4>(fkey, nacc, sk);
                     skeys = sk; rr = reinterpret_cast<int*>(fkey);              // the append list is dead from here on
                 } else {
                     // a large round (the early rounds accept everything): empty the side buffer first, then sort straight into
