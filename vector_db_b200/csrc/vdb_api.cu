@@ -931,8 +931,17 @@ extern "C" int vdb_search_batch(vdb_index* x, const float* q, int64_t nq, int32_
     VDB_TRY(x->p_q.ensure((size_t)nq * dim));
     VDB_TRY(x->p_d.ensure((size_t)nq * k));
     VDB_TRY(x->p_ids.ensure((size_t)nq * k));
-    std::memcpy(x->p_q.p, q, (size_t)nq * dim * 4);
-    VDB_CUDA(cudaMemcpyAsync(x->d_q.p, x->p_q.p, (size_t)nq * dim * 4, cudaMemcpyHostToDevice, st));
+    {   // in 1 MB pieces: the DMA of a piece runs while the next one is being staged
+        const size_t total = (size_t)nq * dim * 4, piece = (size_t)1 << 20;
+        const char* src = reinterpret_cast<const char*>(q);
+        char* pin = reinterpret_cast<char*>(x->p_q.p);
+        char* dst = reinterpret_cast<char*>(x->d_q.p);
+        for (size_t off = 0; off < total; off += piece) {
+            const size_t len = std::min(piece, total - off);
+            std::memcpy(pin + off, src + off, len);
+            VDB_CUDA(cudaMemcpyAsync(dst + off, pin + off, len, cudaMemcpyHostToDevice, st));
+        }
+    }
     VDB_TRY(search_device_locked(x, x->d_q.p, nq, k, x->d_out_ids.p, x->d_out_d.p, st));
     VDB_CUDA(cudaMemcpyAsync(x->p_ids.p, x->d_out_ids.p, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, st));
     VDB_CUDA(cudaMemcpyAsync(x->p_d.p, x->d_out_d.p, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, st));
