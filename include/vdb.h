@@ -92,7 +92,7 @@ typedef struct vdb_stats {
     int64_t flat_certified;  /* flat search: queries answered by the tensor-core shortlist and certified exact */
     int64_t flat_fallback;   /* flat search: queries that failed certification and were re-run by the order-exact scan */
     int32_t trav_format;     /* HNSW*: row format the traversal copy currently has (VDB_TRAV_F32 / FP8 / INT8 / BF16; what AUTO picked) */
-    int32_t reserved;
+    int32_t shortlist_retries;   /* n_devices > 1, PQ: queries repeated with full-length shard shortlists (0 on evenly spread rows) */
 } vdb_stats;
 
 const char* vdb_last_error(void);
@@ -167,7 +167,8 @@ int vdb_pq_lut_device(vdb_index* idx, const float* d_queries, int64_t nq, float*
 int vdb_adc_scan_device(vdb_index* idx, const float* d_lut, float* d_out, void* stream);
 /* PQ search in two phases for id-range shards in SEPARATE processes (one per GPU, torch.distributed; inside one process
  * vdb_config.n_devices does all of this): phase 1 = LUT + ADC scan -> this shard's top-R keys d_keys_out[nq][R] (ordered ADC
- * distance << 32 | id, ascending; R = max(rerank, k), returned in *shortlist_len; nq <= 1024); the caller all-gathers the keys,
+ * distance << 32 | id, ascending; R = max(rerank, k), or the local length passed IN *shortlist_len, see below; the length used is
+ * returned in *shortlist_len; nq <= 1024); the caller all-gathers the keys,
  * vdb_select_kth_key_device gives the GLOBAL R-th key per query from the g lists [g][nq][R]; phase 2 (vdb_pq_rerank_device, same
  * queries, right after phase 1 on the same handle) drops the shard's entries above that boundary and re-scores the rest exactly
  * -> the shard's top-k; vdb_merge_topk_device merges the g lists. The merged answer equals the single-GPU answer bit for bit. */
@@ -175,6 +176,14 @@ int vdb_pq_shortlist_device(vdb_index* idx, const float* d_queries, int64_t nq, 
 int vdb_pq_rerank_device(vdb_index* idx, const float* d_queries, int64_t nq, int32_t k, const uint64_t* d_kth /* [nq] or NULL */,
                          int32_t* d_ids, float* d_dists, void* stream);
 int vdb_select_kth_key_device(const uint64_t* d_keys /* [g][nq][R] */, int32_t g, int64_t nq, int32_t R, uint64_t* d_kth, void* stream);
+/* Shorter LOCAL shortlists (no reference counterpart: the reference has no shards). The scan's candidate bookkeeping grows with the
+ * list length, and a shard of an evenly spread index holds only ~R/g of the global top-R, so sharded callers may pass a local length
+ * L (k <= L < R, e.g. 2R/g + 64) in *shortlist_len of vdb_pq_shortlist_device (0 = R; the length used comes back in it and stays in
+ * force for the following vdb_pq_rerank_device). The boundary of rank R among the g lists [g][nq][L] is then only certain if no shard
+ * ran out of keys below it: this call also counts the uncertain queries in *d_uncertain (device int, zeroed by the caller; NULL = do
+ * not check). A caller that finds it non-zero repeats the batch with full-length lists. */
+int vdb_select_kth_key_ex_device(const uint64_t* d_keys /* [g][nq][list_len] */, int32_t g, int64_t nq, int32_t list_len, int32_t rank,
+                                 uint64_t* d_kth, int32_t* d_uncertain, void* stream);
 /* merge g per-shard result lists [g][nq][k] (dist,id) into [nq][k] ordered by (dist,id) */
 int vdb_merge_topk_device(const float* d_dists, const int32_t* d_ids, int32_t g, int64_t nq, int32_t k,
                           float* d_out_dists, int32_t* d_out_ids, void* stream);

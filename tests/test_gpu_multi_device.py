@@ -86,6 +86,37 @@ def test_pq_multi_device_equals_single_for_any_shard_count(v, po, monkeypatch, r
     a.close(); b.close()
 
 
+def test_pq_multi_device_local_shortlists_retry_when_rows_are_not_spread_evenly(v, po, monkeypatch):
+    """shards keep LOCAL shortlists of ~2R/g + 64 keys (csrc/multi_gpu.cu); when the whole global shortlist sits in one shard the
+    boundary check must notice and the sub-batch is repeated with full-length lists — the answer stays the single-GPU answer"""
+    monkeypatch.setenv("VDB_MULTI_SAME_DEVICE", "1")
+    n, dim, M, nq, k, R, g = 40000, 64, 8, 300, 10, 300, 5
+    X, Q = po.synth(42, n, dim), po.synth(43, nq, dim)
+    c = X[7].copy()
+    Q = (c[None, :] + 0.01 * Q).astype(np.float32)
+    X = np.ascontiguousarray(X[np.argsort(((X - c[None, :]) ** 2).sum(axis=1), kind="stable")])
+    X[n // g:] += np.float32(6.0)                                  # everything near the queries lives in shard 0
+    T = np.ascontiguousarray(X[::5][:2000])
+    ref = v.NativePqIndex(dim, n, M=M, rerank=R)
+    ref.train(T); ref.addBatch(np.arange(n, dtype=np.int32), X)
+    ri, rd = ref.searchBatch(Q, k)
+    cb = ref.codebooks()
+    ref.close()
+    f = v.NativePqIndex(dim, n, M=M, rerank=R, n_devices=g)
+    f.set_codebooks(cb); f.addBatch(np.arange(n, dtype=np.int32), X)
+    ids, d = f.searchBatch(Q, k)
+    assert np.array_equal(ids, ri) and np.array_equal(bits(d), bits(rd))
+    assert f.stats()["shortlist_retries"] > 0
+    f.close()
+    # evenly spread rows: no retry
+    X2 = po.synth(44, n, dim)
+    f = v.NativePqIndex(dim, n, M=M, rerank=R, n_devices=g)
+    f.set_codebooks(cb); f.addBatch(np.arange(n, dtype=np.int32), X2)
+    f.searchBatch(po.synth(45, nq, dim), k)
+    assert f.stats()["shortlist_retries"] == 0
+    f.close()
+
+
 def test_multi_device_rejects_graph_indexes_and_unsupported_calls(v, monkeypatch):
     monkeypatch.setenv("VDB_MULTI_SAME_DEVICE", "1")
     with pytest.raises(Exception, match="replica"):

@@ -54,9 +54,27 @@ def test_sharded_search_world2_matches_single_index():
     assert np.array_equal(d.view(np.uint32), gd.view(np.uint32))
 
 
-def _worker_pq(rank, world, port, n, dim, M, nq, k, R, ret):
-    """two-phase PQ search over id-range shards, world 2, on CPU: the local phases are the ORACLE's (checker), the exchange and
-    the boundary logic are the product's host code (vector_db_b200/sharded.py)"""
+def _pq_data(po, n, dim, nq, skew):
+    """rows, queries and training sample of the PQ shard tests. skew: the queries sit in one small cluster, the rows are stored in
+    order of their distance to it and the last two thirds are moved far away, so the whole global shortlist lives in shard 0 — the
+    case the local shortlists cannot cover"""
+    X, Q = po.synth(42, n, dim), po.synth(43, nq, dim)
+    if skew:
+        c = X[7].copy()
+        Q = (c[None, :] + 0.01 * Q).astype(np.float32)
+        X = np.ascontiguousarray(X[np.argsort(((X - c[None, :]) ** 2).sum(axis=1), kind="stable")])
+        X[n // 3:] += np.float32(6.0)
+    return X, Q, np.ascontiguousarray(X[::5][:600])
+
+
+class _StubIndex:                                       # what search_pq reads from the local index on the CPU path
+    def __init__(self, rerank):
+        self.rerank = rerank
+
+
+def _worker_pq(rank, world, port, n, dim, M, nq, k, R, skew, ret):
+    """two-phase PQ search over id-range shards on CPU: the local phases are the ORACLE's (checker), the exchange, the local
+    shortlist length, the boundary certainty rule and the retry are the product's host code (vector_db_b200/sharded.py)"""
     sys.path.insert(0, ROOT)
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
@@ -64,23 +82,24 @@ def _worker_pq(rank, world, port, n, dim, M, nq, k, R, ret):
     from oracle import pyoracle as po
     from vector_db_b200.sharded import ShardedSearcher, kth_key_host, merge_topk_host, plan_shards
     lo, hi = plan_shards(n, world)[rank]
-    Xall, Q = po.synth(42, n, dim), po.synth(43, nq, dim)
-    cb = po.pq_train(Xall[:600], M, 25, po.TRAIN_NATIVE_PQ)
+    Xall, Q, T = _pq_data(po, n, dim, nq, skew)
+    cb = po.pq_train(T, M, 25, po.TRAIN_NATIVE_PQ)
     X = Xall[lo:hi]
     codes = po.pq_encode(X, cb, po.ARITH_NATIVE_AVX2)
     gids = np.arange(lo, hi, dtype=np.int32)
-    state = {}
+    state = {"lens": []}
 
     def key_of(d, i):                                   # the library's key: ordered fp32 bits << 32 | (id ^ 0x80000000)
         b = d.view(np.uint32).astype(np.uint64)
         b = np.where(b & 0x80000000, ~b & 0xffffffff, b | 0x80000000)
         return (b << np.uint64(32)) | (i.astype(np.int64).astype(np.uint64) ^ np.uint64(0x80000000)) & np.uint64(0xffffffff)
 
-    def phase1(q, kk):
-        ids, d = po.pq_flat_search(q.numpy(), cb, codes, R, po.ARITH_NATIVE_AVX2, ids=gids)     # local top-R by (ADC dist, id)
+    def phase1(q, kk, L):
+        ids, d = po.pq_flat_search(q.numpy(), cb, codes, L, po.ARITH_NATIVE_AVX2, ids=gids)     # local top-L by (ADC dist, id)
         keys = key_of(d, ids)
         keys[ids < 0] = np.uint64(0xffffffffffffffff)
         state["ids"], state["keys"] = ids, keys
+        state["lens"].append(L)
         return torch.from_numpy(keys.view(np.int64))
 
     def phase2(q, kk, kth):
@@ -97,26 +116,45 @@ def _worker_pq(rank, world, port, n, dim, M, nq, k, R, ret):
         d, i = merge_topk_host(all_d.numpy(), all_i.numpy(), kk)
         return torch.from_numpy(d), torch.from_numpy(i)
 
-    s = ShardedSearcher(None, rank, world, merge_fn=merge)
-    ids, d = s.search_pq(torch.from_numpy(Q), k, phase1=phase1, phase2=phase2,
-                         kth_fn=lambda ak, r: torch.from_numpy(kth_key_host(ak.numpy().view(np.uint64), r).view(np.int64)))
+    def kth_fn(ak, r):
+        kth, unc = kth_key_host(ak.numpy().view(np.uint64), r)
+        return torch.from_numpy(kth.view(np.int64)), unc
+
+    s = ShardedSearcher(_StubIndex(R), rank, world, merge_fn=merge)
+    ids, d = s.search_pq(torch.from_numpy(Q), k, phase1=phase1, phase2=phase2, kth_fn=kth_fn)
     if rank == 0:
-        ret["ids"], ret["d"] = ids.numpy().copy(), d.numpy().copy()
+        ret["ids"], ret["d"], ret["lens"], ret["retries"] = ids.numpy().copy(), d.numpy().copy(), list(state["lens"]), s.shortlist_retries
     dist.barrier()
     dist.destroy_process_group()
 
 
-def test_sharded_pq_rerank_world2_equals_single_index():
+def _check_pq(world, port, n, dim, M, nq, k, R, skew):
     from oracle import pyoracle as po
     po.build()
-    n, dim, M, nq, k, R = 3001, 32, 4, 6, 5, 40
     with mp.Manager() as mgr:
         ret = mgr.dict()
-        mp.spawn(_worker_pq, args=(2, 29519, n, dim, M, nq, k, R, ret), nprocs=2, join=True)
-        ids, d = ret["ids"], ret["d"]
-    X, Q = po.synth(42, n, dim), po.synth(43, nq, dim)
-    cb = po.pq_train(X[:600], M, 25, po.TRAIN_NATIVE_PQ)
+        mp.spawn(_worker_pq, args=(world, port, n, dim, M, nq, k, R, skew, ret), nprocs=world, join=True)
+        ids, d, lens, retries = ret["ids"], ret["d"], list(ret["lens"]), ret["retries"]
+    X, Q, T = _pq_data(po, n, dim, nq, skew)
+    cb = po.pq_train(T, M, 25, po.TRAIN_NATIVE_PQ)
     codes = po.pq_encode(X, cb, po.ARITH_NATIVE_AVX2)
     gi, gd = po.pq_flat_search(Q, cb, codes, k, po.ARITH_NATIVE_AVX2, rerank=R, base=X, exact_order=1)
     assert np.array_equal(ids, gi)                       # the sharded answer IS the single-index answer (global top-R, then rerank)
     assert np.array_equal(d.view(np.uint32), gd.view(np.uint32))
+    return lens, retries
+
+
+def test_sharded_pq_rerank_world2_equals_single_index():
+    lens, retries = _check_pq(2, 29519, 3001, 32, 4, 6, 5, 40, False)
+    assert lens == [40] and retries == 0                 # two shards: full-length lists
+
+
+def test_sharded_pq_rerank_world3_local_shortlists_and_retry():
+    from vector_db_b200.sharded import local_shortlist_len
+    n, dim, M, nq, k, R = 3001, 32, 4, 6, 5, 400
+    L = local_shortlist_len(R, 3, k)
+    assert k <= L < R
+    lens, retries = _check_pq(3, 29521, n, dim, M, nq, k, R, False)
+    assert lens == [L] and retries == 0                  # evenly spread rows: the short local lists are certified, no retry
+    lens, retries = _check_pq(3, 29523, n, dim, M, nq, k, R, True)
+    assert lens == [L, R] and retries > 0                # the whole shortlist in shard 0: detected, repeated with full lists, same answer

@@ -19,7 +19,7 @@ SYMBOLS = [
     "vdb_build", "vdb_search_batch", "vdb_search_batch_device", "vdb_size", "vdb_is_trained", "vdb_get_stats",
     "vdb_set_codebooks", "vdb_get_codebooks", "vdb_get_codes", "vdb_set_codes", "vdb_set_graph", "vdb_get_graph",
     "vdb_max_level", "vdb_save", "vdb_load", "vdb_fill_synthetic", "vdb_encode_all", "vdb_pq_lut_device",
-    "vdb_adc_scan_device", "vdb_merge_topk_device", "vdb_distance_device", "vdb_flat_search_noalloc_device", "vdb_remove", "vdb_contains", "vdb_rows", "vdb_microbench_device",
+    "vdb_adc_scan_device", "vdb_merge_topk_device", "vdb_distance_device", "vdb_flat_search_noalloc_device", "vdb_remove", "vdb_contains", "vdb_rows", "vdb_microbench_device", "vdb_select_kth_key_ex_device",
     "vdb_pq_shortlist_device", "vdb_pq_rerank_device", "vdb_select_kth_key_device",
 ]
 
@@ -34,7 +34,7 @@ class VdbConfig(C.Structure):
 class VdbStats(C.Structure):
     _fields_ = [("queries", C.c_int64), ("dist_evals", C.c_int64), ("expansions", C.c_int64), ("adc_rows", C.c_int64),
                 ("last_kernel_ms", C.c_float), ("last_total_ms", C.c_float), ("flat_certified", C.c_int64), ("flat_fallback", C.c_int64),
-                ("trav_format", C.c_int32), ("reserved", C.c_int32)]
+                ("trav_format", C.c_int32), ("shortlist_retries", C.c_int32)]
 
 
 class VdbError(RuntimeError):
@@ -90,6 +90,7 @@ def lib():
     L.vdb_pq_shortlist_device.argtypes = [vp, vp, i64, i32, vp, C.POINTER(i32), vp]
     L.vdb_pq_rerank_device.argtypes = [vp, vp, i64, i32, vp, vp, vp, vp]
     L.vdb_select_kth_key_device.argtypes = [vp, i32, i64, i32, vp, vp]
+    L.vdb_select_kth_key_ex_device.argtypes = [vp, i32, i64, i32, i32, vp, vp, vp]
     L.vdb_flat_search_noalloc_device.argtypes = [vp, i64, i32, i32, vp, i64, i32, vp, vp, vp]
     _lib = L
     return L

@@ -23,7 +23,7 @@ void launch_keys_to_results(const uint64_t* d_keys, int R, int k, int64_t nq, in
 // shortlist entries whose key is above the per-query threshold kth[q] are removed (key = KEY_MAX, row = 0xffffffff)
 void launch_mask_keys_above(uint64_t* d_keys, uint32_t* d_rows, int nq, int R, const uint64_t* d_kth, cudaStream_t st);
 // kth[q] = the R-th smallest of the g * R keys keys[s][q][0..R) (each list ascending): the global shortlist boundary
-void launch_select_kth_key(const uint64_t* d_keys, int g, int nq, int R, uint64_t* d_kth, cudaStream_t st);
+void launch_select_kth_key(const uint64_t* d_keys, int g, int nq, int L, int rank, uint64_t* d_kth, int* d_uncertain, cudaStream_t st);
 void launch_adc_scan_plain(const uint8_t* d_codes, int64_t n, int M, const float* d_lut, float* d_out, cudaStream_t st);
 void launch_rerank(const float* d_base, const int32_t* d_ids, int id_offset, int dim, const float* d_q, int nq,
                    const uint32_t* d_rows, int R, int order, int k, int32_t* d_out_ids, float* d_out_d, cudaStream_t st);

@@ -114,7 +114,7 @@ int vdb_multi_stats(vdb_index* f, vdb_stats* out) {
         t.adc_rows += s.adc_rows; t.flat_certified += s.flat_certified; t.flat_fallback += s.flat_fallback;
         t.last_kernel_ms = std::max(t.last_kernel_ms, s.last_kernel_ms); t.last_total_ms = std::max(t.last_total_ms, s.last_total_ms);
     }
-    t.queries = f->stats.queries;
+    t.queries = f->stats.queries; t.shortlist_retries = f->stats.shortlist_retries;
     *out = t;
     return VDB_OK;
 }
@@ -165,7 +165,12 @@ int vdb_multi_search(vdb_index* f, const float* q, bool q_on_device, int64_t nq,
         if ((int64_t)g * k > 8192) MG_FAIL(VDB_ERR_INVALID, "multi-device search: n_devices x k > 8192 not supported");
         const int64_t QB = pq ? 1024 : 8192;        // flat: whole batches (the GEMM wants many query tiles); PQ: the LUT scratch is per query
         VDB_TRY(f->g_d.ensure((size_t)g * nq * k, 0, fs)); VDB_TRY(f->g_i.ensure((size_t)g * nq * k, 0, fs));
-        if (pq) { VDB_TRY(f->g_keys.ensure((size_t)g * QB * R, 0, fs)); VDB_TRY(f->g_kth.ensure((size_t)QB, 0, fs)); }
+        if (pq) { VDB_TRY(f->g_keys.ensure((size_t)g * QB * R, 0, fs)); VDB_TRY(f->g_kth.ensure((size_t)QB, 0, fs)); VDB_TRY(f->g_unc.ensure(1, 0, fs)); }
+        // Each shard keeps a LOCAL shortlist of about twice its expected share of the global top-R (the scan's candidate bookkeeping
+        // grows with the list length and does not shrink with the shard): with rows spread evenly a shard holds Binomial(R, 1/g) of
+        // the global shortlist, 2 R / g + 64 is more than ten standard deviations up. select_kth_key_kernel certifies the boundary per
+        // query (no shard may run out of keys below it); a sub-batch with an uncertain query is repeated with full-length lists.
+        const int Rloc = (pq && g > 2 && !getenv("VDB_MULTI_FULL_SHORTLIST")) ? std::min(R, std::max(k, 2 * ((R + g - 1) / g) + 64)) : R;
         // queries to every shard
         for (int s = 0; s < g; s++) {
             vdb_index* sh = f->shards[s];
@@ -185,21 +190,33 @@ int vdb_multi_search(vdb_index* f, const float* q, bool q_on_device, int64_t nq,
             const int64_t qb = std::min(QB, nq - q0);
             float* gd = f->g_d.p + (size_t)g * q0 * k; int32_t* gi = f->g_i.p + (size_t)g * q0 * k;
             if (pq) {
-                for (int s = 0; s < g; s++)
-                    if (vdb_size(f->shards[s]) == 0) VDB_CUDA(cudaMemsetAsync(f->g_keys.p + (size_t)s * qb * R, 0xff, (size_t)qb * R * 8, fs));
-                VDB_TRY(for_each_shard(f, [&](int s) -> int {
-                    vdb_index* sh = f->shards[s];
-                    if (q0 > 0) VDB_CUDA(cudaStreamWaitEvent(sh->stream, f->ev_front, 0));       // g_keys of the previous sub-batch consumed
-                    if (vdb_size(sh) > 0) {
-                        VDB_TRY(vdb_pq_phase1(sh, sh->d_q.p + q0 * dim, qb, k, sh->stream));
-                        VDB_CUDA(cudaMemcpyPeerAsync(f->g_keys.p + (size_t)s * qb * R, d0, sh->d_keys.p, sh->cfg.device, (size_t)qb * R * 8, sh->stream));
-                    }
-                    VDB_CUDA(cudaEventRecord(f->shard_ev[s], sh->stream));
-                    return VDB_OK;
-                }));
-                for (int s = 0; s < g; s++) VDB_CUDA(cudaStreamWaitEvent(fs, f->shard_ev[s], 0));
-                launch_select_kth_key(f->g_keys.p, g, (int)qb, R, f->g_kth.p, fs);
-                VDB_CUDA(cudaEventRecord(f->ev_front, fs));
+                for (int attempt = 0; attempt < 2; attempt++) {
+                    const int L = attempt == 0 ? Rloc : R;              // list length of this attempt
+                    for (int s = 0; s < g; s++)
+                        if (vdb_size(f->shards[s]) == 0) VDB_CUDA(cudaMemsetAsync(f->g_keys.p + (size_t)s * qb * L, 0xff, (size_t)qb * L * 8, fs));
+                    VDB_CUDA(cudaMemsetAsync(f->g_unc.p, 0, sizeof(int), fs));
+                    VDB_CUDA(cudaEventRecord(f->ev_front, fs));
+                    VDB_TRY(for_each_shard(f, [&](int s) -> int {
+                        vdb_index* sh = f->shards[s];
+                        VDB_CUDA(cudaStreamWaitEvent(sh->stream, f->ev_front, 0));       // g_keys of the previous sub-batch / attempt consumed
+                        if (vdb_size(sh) > 0) {
+                            sh->shortlist_override = L < R ? L : 0;
+                            VDB_TRY(vdb_pq_phase1(sh, sh->d_q.p + q0 * dim, qb, k, sh->stream));
+                            VDB_CUDA(cudaMemcpyPeerAsync(f->g_keys.p + (size_t)s * qb * L, d0, sh->d_keys.p, sh->cfg.device, (size_t)qb * L * 8, sh->stream));
+                        }
+                        VDB_CUDA(cudaEventRecord(f->shard_ev[s], sh->stream));
+                        return VDB_OK;
+                    }));
+                    for (int s = 0; s < g; s++) VDB_CUDA(cudaStreamWaitEvent(fs, f->shard_ev[s], 0));
+                    launch_select_kth_key(f->g_keys.p, g, (int)qb, L, R, f->g_kth.p, L < R ? f->g_unc.p : nullptr, fs);
+                    VDB_CUDA(cudaEventRecord(f->ev_front, fs));
+                    if (L == R) break;
+                    int unc = 0;
+                    VDB_CUDA(cudaMemcpyAsync(&unc, f->g_unc.p, sizeof(int), cudaMemcpyDeviceToHost, fs));
+                    VDB_CUDA(cudaStreamSynchronize(fs));
+                    if (unc == 0) break;
+                    f->stats.shortlist_retries += unc;                  // reported: queries that needed full-length lists
+                }
             }
             VDB_TRY(for_each_shard(f, [&](int s) -> int {
                 vdb_index* sh = f->shards[s];

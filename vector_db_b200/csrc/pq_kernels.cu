@@ -154,20 +154,35 @@ void launch_mask_keys_above(uint64_t* d_keys, uint32_t* d_rows, int nq, int R, c
     const int64_t tot = (int64_t)nq * R;
     if (tot > 0) mask_keys_above_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(d_keys, d_rows, nq, R, d_kth);
 }
-// one CTA per query: the g sorted lists are merged by sorting their g * R keys in shared memory; element R-1 is the boundary
-__global__ void select_kth_key_kernel(const uint64_t* __restrict__ keys, int g, int nq, int R, int cap, uint64_t* __restrict__ kth) {
+// one CTA per query: the g sorted lists (L keys each) are merged by sorting their g * L keys in shared memory; element rank-1 is
+// the boundary. When the lists are SHORTER than the rank asked for (L < rank: shards keep a local shortlist of ~2 rank / g), the
+// boundary is only certain if no shard ran out of keys below it: a full list whose last key is below the boundary may hide more.
+// Such queries are counted in *uncertain (the caller repeats them with full-length lists).
+__global__ void select_kth_key_kernel(const uint64_t* __restrict__ keys, int g, int nq, int L, int rank, int cap, uint64_t* __restrict__ kth,
+                                      int* __restrict__ uncertain) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint64_t* b = reinterpret_cast<uint64_t*>(smem_raw);
-    const int q = blockIdx.x, total = g * R;
-    for (int i = threadIdx.x; i < cap; i += blockDim.x) b[i] = i < total ? keys[((size_t)(i / R) * nq + q) * R + (i % R)] : KEY_MAX;
+    const int q = blockIdx.x, total = g * L;
+    for (int i = threadIdx.x; i < cap; i += blockDim.x) b[i] = i < total ? keys[((size_t)(i / L) * nq + q) * L + (i % L)] : KEY_MAX;
     block_bitonic_sort<false>(b, nullptr, cap);
-    if (threadIdx.x == 0) kth[q] = b[R - 1];
+    if (threadIdx.x == 0) {
+        const uint64_t bound = rank - 1 < cap ? b[rank - 1] : KEY_MAX;
+        kth[q] = bound;
+        if (uncertain && L < rank) {
+            bool bad = false;
+            for (int s = 0; s < g; s++) {
+                const uint64_t last = keys[((size_t)s * nq + q) * L + (L - 1)];
+                if (last != KEY_MAX && last < bound) bad = true;
+            }
+            if (bad) atomicAdd(uncertain, 1);
+        }
+    }
 }
-void launch_select_kth_key(const uint64_t* d_keys, int g, int nq, int R, uint64_t* d_kth, cudaStream_t st) {
-    const int cap = next_pow2(g * R);
+void launch_select_kth_key(const uint64_t* d_keys, int g, int nq, int L, int rank, uint64_t* d_kth, int* d_uncertain, cudaStream_t st) {
+    const int cap = next_pow2(g * L);
     const size_t smem = (size_t)cap * 8;
     cudaFuncSetAttribute(select_kth_key_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    select_kth_key_kernel<<<nq, 256, smem, st>>>(d_keys, g, nq, R, cap, d_kth);
+    select_kth_key_kernel<<<nq, 256, smem, st>>>(d_keys, g, nq, L, rank, cap, d_kth, d_uncertain);
 }
 
 // plain ADC distances for one LUT (test hook; order R3)

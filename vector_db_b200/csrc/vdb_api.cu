@@ -732,7 +732,12 @@ static int pick_chunks(const vdb_index* x, int64_t nq, int64_t n, int R) {
 //      phase 1  LUT build + ADC scan -> the shard's top-R keys (ordered ADC distance << 32 | id) in x->d_keys, rows in x->d_rows;
 //      phase 2  entries whose key is above the caller's per-query threshold (the global R-th key) are masked, then the exact
 //               re-score of the rest (or, without rerank, the keys themselves) gives the shard's top-k.
-static inline int pq_shortlist_len(const vdb_index* x, int k) { return x->cfg.rerank > 0 ? std::max(x->cfg.rerank, k) : k; }
+// shortlist of the PQ search: max(rerank, k); sharded callers may shorten a shard's LOCAL list (shortlist_override, >= k): the
+// global boundary is then checked for certainty by select_kth_key_kernel
+static inline int pq_shortlist_len(const vdb_index* x, int k) {
+    const int R = x->cfg.rerank > 0 ? std::max(x->cfg.rerank, k) : k;
+    return x->shortlist_override > 0 ? std::min(R, std::max(x->shortlist_override, k)) : R;
+}
 int vdb_pq_phase1(vdb_index* x, const float* d_q, int64_t qb, int k, cudaStream_t st) {
     const int M = x->pq_m, dim = x->cfg.dim;
     const int R = pq_shortlist_len(x, k);
@@ -1008,6 +1013,9 @@ extern "C" int vdb_pq_shortlist_device(vdb_index* x, const float* d_q, int64_t n
     if (!x->trained) FAIL(VDB_ERR_UNTRAINED, "train first");
     VDB_TRY(sync_index(x));
     cudaStream_t st = (cudaStream_t)stream;
+    // *shortlist_len on entry: 0 = the full shortlist, else the length of this shard's LOCAL list (kept until the next call; phase 2
+    // uses the same)
+    x->shortlist_override = (shortlist_len && *shortlist_len > 0) ? *shortlist_len : 0;
     const int R = pq_shortlist_len(x, k);
     if (shortlist_len) *shortlist_len = R;
     if (x->n == 0) { VDB_CUDA(cudaMemsetAsync(d_keys_out, 0xff, (size_t)nq * R * 8, st)); return VDB_OK; }
@@ -1025,7 +1033,15 @@ extern "C" int vdb_pq_rerank_device(vdb_index* x, const float* d_q, int64_t nq, 
 }
 extern "C" int vdb_select_kth_key_device(const uint64_t* d_keys, int32_t g, int64_t nq, int32_t R, uint64_t* d_kth, void* stream) {
     if (!d_keys || !d_kth || g <= 0 || R <= 0 || nq <= 0 || (int64_t)g * R > 16384) FAIL(VDB_ERR_INVALID, "vdb_select_kth_key_device: bad arguments (g x R <= 16384)");
-    launch_select_kth_key(d_keys, g, (int)nq, R, d_kth, (cudaStream_t)stream);
+    launch_select_kth_key(d_keys, g, (int)nq, R, R, d_kth, nullptr, (cudaStream_t)stream);
+    VDB_CUDA(cudaGetLastError());
+    return VDB_OK;
+}
+extern "C" int vdb_select_kth_key_ex_device(const uint64_t* d_keys, int32_t g, int64_t nq, int32_t list_len, int32_t rank, uint64_t* d_kth,
+                                            int32_t* d_uncertain, void* stream) {
+    if (!d_keys || !d_kth || g <= 0 || list_len <= 0 || rank <= 0 || nq <= 0 || (int64_t)g * list_len > 16384 || (int64_t)g * list_len < rank)
+        FAIL(VDB_ERR_INVALID, "vdb_select_kth_key_ex_device: bad arguments (rank <= g x list_len <= 16384)");
+    launch_select_kth_key(d_keys, g, (int)nq, list_len, rank, d_kth, d_uncertain, (cudaStream_t)stream);
     VDB_CUDA(cudaGetLastError());
     return VDB_OK;
 }

@@ -151,6 +151,8 @@ struct vdb_index {
     int64_t n_distributed = 0;              // host rows already handed to the shards
     DevBuf<uint64_t> g_keys, g_kth;         // front device: gathered shortlist keys [g][qb][R], global boundary [qb]
     DevBuf<uint64_t> d_kth;                 // shard: its copy of the boundary
+    DevBuf<int> g_unc;                      // front device: number of queries whose boundary is uncertain with local shortlists
+    int shortlist_override = 0;             // PQ shard: length of the LOCAL shortlist of the current sharded search (0 = max(rerank, k))
     DevBuf<float> g_d;                      // gathered results [g][qb][k]
     DevBuf<int32_t> g_i;
 };

@@ -42,10 +42,20 @@ def merge_topk_host(dists, ids, k):
 
 
 def kth_key_host(keys, R):
-    """numpy statement of vdb_select_kth_key_device: keys [g][nq][R] (uint64, each list ascending, 2^64-1 = empty) -> the R-th
-    smallest key per query = the boundary of the GLOBAL shortlist"""
-    g, nq, r = keys.shape
-    return np.sort(np.transpose(keys, (1, 0, 2)).reshape(nq, g * r), axis=1)[:, R - 1].copy()
+    """numpy statement of vdb_select_kth_key_ex_device: keys [g][nq][L] (uint64, each list ascending, 2^64-1 = empty) -> (the R-th
+    smallest key per query = the boundary of the GLOBAL shortlist, the number of queries whose boundary is uncertain because a full
+    list of a shard ends below it — only possible when L < R)"""
+    g, nq, L = keys.shape
+    kth = np.sort(np.transpose(keys, (1, 0, 2)).reshape(nq, g * L), axis=1)[:, min(R, g * L) - 1].copy()
+    last = keys[:, :, L - 1]                                    # [g][nq]
+    unc = int(((last != np.uint64(0xFFFFFFFFFFFFFFFF)) & (last < kth[None, :])).any(axis=0).sum()) if L < R else 0
+    return kth, unc
+
+
+def local_shortlist_len(R, g, k):
+    """length of a shard's LOCAL shortlist: about twice its expected share of the global top-R (rows spread evenly: Binomial(R, 1/g),
+    2 R / g + 64 is more than ten standard deviations up); the same rule as csrc/multi_gpu.cu"""
+    return R if g <= 2 else min(R, max(k, 2 * ((R + g - 1) // g) + 64))
 
 
 class ShardedSearcher:
@@ -54,6 +64,7 @@ class ShardedSearcher:
     def __init__(self, local_index, rank, world_size, group=None, merge_fn=None):
         self.index, self.rank, self.world, self.group = local_index, rank, world_size, group
         self._merge_fn = merge_fn            # injectable for CPU tests; default = CUDA merge kernel
+        self.shortlist_retries = 0           # queries that needed full-length shard shortlists (search_pq)
 
     def _merge(self, all_d, all_i, k):
         if self._merge_fn is not None:
@@ -70,43 +81,53 @@ class ShardedSearcher:
 
     def search_pq(self, d_queries, k, phase1=None, phase2=None, kth_fn=None):
         """PQ shards (with or without rerank) in two phases so that the answer does not depend on the number of shards: every rank
-        scans its codes (phase 1: local top-R keys), ONE all_gather of the keys, the global R-th key per query bounds the global
-        shortlist, every rank re-scores only its own rows inside it (phase 2) and the top-k lists are merged as in `search`.
-        phase1(q, k) -> uint64 keys [nq][R]; phase2(q, k, kth) -> (ids, dists); injectable for the CPU (gloo) tests."""
+        scans its codes (phase 1: local top-L keys, L = local_shortlist_len), ONE all_gather of the keys, the global R-th key per
+        query bounds the global shortlist, every rank re-scores only its own rows inside it (phase 2) and the top-k lists are merged
+        as in `search`. If a shard's local list ends below the boundary of some query (rows not spread evenly) the batch is repeated
+        with full-length lists — every rank sees the same gathered keys, so all take the same decision.
+        phase1(q, k, L) -> uint64 keys [nq][L]; phase2(q, k, kth) -> (ids, dists); kth_fn(all_keys [g][nq][L], R) -> (kth [nq],
+        uncertain count); injectable for the CPU (gloo) tests."""
         import torch
         import torch.distributed as dist
         if phase1 is None:
             from . import _lib
             import ctypes as C
-            L, h = _lib.lib(), self.index._h
+            L_, h = _lib.lib(), self.index._h
             st = torch.cuda.current_stream(d_queries.device).cuda_stream
             nq = d_queries.shape[0]
 
-            def phase1(q, kk):
-                R = C.c_int32(0)
-                keys = torch.empty((nq, max(self.index_rerank(), kk)), dtype=torch.int64, device=q.device)
-                _lib.check(L.vdb_pq_shortlist_device(h, q.data_ptr(), nq, kk, keys.data_ptr(), C.byref(R), st))
-                assert R.value == keys.shape[1]
+            def phase1(q, kk, L):
+                R = C.c_int32(L)
+                keys = torch.empty((nq, L), dtype=torch.int64, device=q.device)
+                _lib.check(L_.vdb_pq_shortlist_device(h, q.data_ptr(), nq, kk, keys.data_ptr(), C.byref(R), st))
+                assert R.value == L, (R.value, L)
                 return keys
 
             def phase2(q, kk, kth):
                 ids = torch.empty((nq, kk), dtype=torch.int32, device=q.device)
                 d = torch.empty((nq, kk), dtype=torch.float32, device=q.device)
-                _lib.check(L.vdb_pq_rerank_device(h, q.data_ptr(), nq, kk, 0 if kth is None else kth.data_ptr(), ids.data_ptr(), d.data_ptr(), st))
+                _lib.check(L_.vdb_pq_rerank_device(h, q.data_ptr(), nq, kk, 0 if kth is None else kth.data_ptr(), ids.data_ptr(), d.data_ptr(), st))
                 return ids, d
 
             def kth_fn(all_keys, R):
                 out = torch.empty((nq,), dtype=torch.int64, device=all_keys.device)
-                _lib.check(L.vdb_select_kth_key_device(all_keys.data_ptr(), all_keys.shape[0], nq, R, out.data_ptr(), st))
-                return out
-        keys = phase1(d_queries, k)
+                unc = torch.zeros((1,), dtype=torch.int32, device=all_keys.device)
+                _lib.check(L_.vdb_select_kth_key_ex_device(all_keys.data_ptr(), all_keys.shape[0], nq, all_keys.shape[2], R, out.data_ptr(),
+                                                           unc.data_ptr(), st))
+                return out, int(unc.item())
+        R = max(self.index_rerank(), k)
         if self.world == 1:
-            ids, d = phase2(d_queries, k, None)
-            return ids, d
-        nq, R = keys.shape
-        all_keys = torch.empty((self.world * nq, R), dtype=keys.dtype, device=keys.device)
-        dist.all_gather_into_tensor(all_keys, keys.contiguous(), group=self.group)
-        kth = kth_fn(all_keys.view(self.world, nq, R), R)
+            phase1(d_queries, k, R)
+            return phase2(d_queries, k, None)
+        for L in dict.fromkeys((local_shortlist_len(R, self.world, k), R)):       # local lists first, full-length lists if needed
+            keys = phase1(d_queries, k, L)
+            nq = keys.shape[0]
+            all_keys = torch.empty((self.world * nq, L), dtype=keys.dtype, device=keys.device)
+            dist.all_gather_into_tensor(all_keys, keys.contiguous(), group=self.group)
+            kth, unc = kth_fn(all_keys.view(self.world, nq, L), R)
+            if unc == 0 or L == R:
+                break
+            self.shortlist_retries += unc
         return self.search(d_queries, k, local_search=lambda q, kk: phase2(q, kk, kth))
 
     def index_rerank(self):
