@@ -37,3 +37,11 @@ print("| kernel | " + " | ".join(COLS) + " |")
 print("|---|" + "---|" * len(COLS))
 for k, c in sorted(tab.items(), key=lambda kv: -kv[1]["total"]):
     print("| `%s` | " % k[:90] + " | ".join(str(c[x]) if c[x] else "·" for x in COLS) + " |")
+print("""
+Legend. `UTCHMMA` = tcgen05.mma (5th-gen tensor core, operands in shared memory, accumulator in TMEM), `LDTM` = tcgen05.ld (TMEM -> registers),
+`UTMALDG` = TMA tile load (cp.async.bulk.tensor), `UTCBAR` = tcgen05.commit -> mbarrier; `HMMA` / `IMMA` = legacy warp-level mma.sync
+(bf16 / int8), used by the beam kernel for 16 x 8 query-row products only; `LDG.256` = 32-byte global loads (ld.global.nc.L1::no_allocate.v8.b32);
+`STL` / `LDL` = local-memory stores / loads (register spills and indexed local arrays). hnsw_search_kernel template arguments:
+<BF16 rows (false = fp32 strict), FULL, 8-bit stage count (0 = off), int8>. The shipped default on C3 is `<true, false, 2, true>` (int8 rows);
+the fp32 strict variant `<false, false, 0, false>` is the one with heavy local traffic (it is the bit-parity mode, not the fast path).
+Regenerate with `python tools/sass_table.py > profiles/r2_sass_opcodes.md`.""")
