@@ -15,6 +15,8 @@
 //                          the scan's layout offset(m, c) = (m >> 6) * 64 KB + c * 256 + (m & 63) * 4 (conflict-free for any
 //                          codes), address = one PRMT of (code word, lane constant), one LDS and one FADD per gathered value; code
 //                          words come from registers (an LCG), so no global traffic at all.  units = gathers.
+//   kind 3  LDS gather, two queries per word: the ceiling of a T = 2 scan (bf16 pairs unpacked to fp32) — measured to decide
+//                          against building it.  units = query-gathers.
 #include <algorithm>
 #include <vector>
 
@@ -78,6 +80,30 @@ __global__ void __launch_bounds__(512, 1) lds_gather_kernel(int iters, float* __
     }
     if (a0 + a1 + a2 + a3 == -1.0f) sink[0] = a0;
 }
+// kind 3: the same gather where one 32-bit LUT word carries the bf16 entries of TWO queries (lo half = query A, hi half = query B):
+// PRMT + LDS + 2 unpack ops + 2 FADD per word = two query-gathers. units = query-gathers.
+__global__ void __launch_bounds__(512, 1) lds_gather_pair_kernel(int iters, float* __restrict__ sink) {
+    extern __shared__ float lut[];
+    for (int i = threadIdx.x; i < 2 * 16384; i += 512) lut[i] = __uint_as_float(0x3f803f80u + (uint32_t)(i & 63));
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const uint32_t lane_off = (uint32_t)lane * 4u;
+    uint32_t w = 0x12345u * (threadIdx.x + 1) + blockIdx.x;
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, b0 = 0.f, b1 = 0.f, b2 = 0.f, b3 = 0.f;
+    const char* base = reinterpret_cast<const char*>(lut);
+    for (int it = 0; it < iters; it++) {
+        w = w * 1664525u + 1013904223u;
+        const uint32_t w0 = *reinterpret_cast<const uint32_t*>(base + __byte_perm(w, lane_off, 0x6504));
+        const uint32_t w1 = *reinterpret_cast<const uint32_t*>(base + __byte_perm(w, lane_off, 0x6514) + 65536);
+        const uint32_t w2 = *reinterpret_cast<const uint32_t*>(base + __byte_perm(w, lane_off, 0x6524) + 128);
+        const uint32_t w3 = *reinterpret_cast<const uint32_t*>(base + __byte_perm(w, lane_off, 0x6534) + 65536 + 128);
+        a0 += __uint_as_float(w0 << 16); b0 += __uint_as_float(w0 & 0xffff0000u);
+        a1 += __uint_as_float(w1 << 16); b1 += __uint_as_float(w1 & 0xffff0000u);
+        a2 += __uint_as_float(w2 << 16); b2 += __uint_as_float(w2 & 0xffff0000u);
+        a3 += __uint_as_float(w3 << 16); b3 += __uint_as_float(w3 & 0xffff0000u);
+    }
+    if (a0 + a1 + a2 + a3 + b0 + b1 + b2 + b3 == -1.0f) sink[0] = a0;
+}
 }  // namespace
 
 // out[0] = milliseconds per launch (median of `reps`), out[1] = units per launch (bytes gathered / gathers)
@@ -115,6 +141,21 @@ extern "C" int vdb_microbench_device(int32_t kind, int64_t rows, int32_t row_byt
         }
         units = (double)grid * per_cta * row_bytes;
         cudaFree(table); cudaFree(idx); cudaFree(sink);
+    } else if (kind == 3) {
+        if (work <= 0) { vdb_set_error("lds pair gather: work = iterations per thread"); return VDB_ERR_INVALID; }
+        float* sink = nullptr;
+        VDB_CUDA(cudaMalloc(&sink, 4));
+        VDB_CUDA(cudaFuncSetAttribute(lds_gather_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 131072));
+        for (int r = 0; r < reps + 2; r++) {
+            cudaEventRecord(e0);
+            lds_gather_pair_kernel<<<sms, 512, 131072>>>(work, sink);
+            cudaEventRecord(e1);
+            VDB_CUDA(cudaEventSynchronize(e1));
+            float t; cudaEventElapsedTime(&t, e0, e1);
+            if (r >= 2) ms.push_back(t);
+        }
+        units = (double)sms * 512 * (double)work * 8.0;
+        cudaFree(sink);
     } else if (kind == 2) {
         if (work <= 0) { vdb_set_error("lds gather: work = iterations per thread"); return VDB_ERR_INVALID; }
         float* sink = nullptr;
