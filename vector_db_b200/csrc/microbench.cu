@@ -11,6 +11,7 @@
 //                          words are XOR-folded so the loads cannot be dropped.  units = bytes gathered.
 //   kind 1  row gather, deep: same addresses with 8 lines per row in flight per lane (the load-level parallelism a register ring
 //                          would give if registers were free) — the upper bound of the L2 -> SM path for this access pattern.
+//   kind 4  row gather, one CTA per SM: kind 0 with 8 warps per SM instead of 16 — what ONE query's distance phase can have in flight.
 //   kind 2  LDS gather   : the ADC scan's shared-memory gather at its floor: 512 threads, one CTA per SM, a 128 KB LUT image in
 //                          the scan's layout offset(m, c) = (m >> 6) * 64 KB + c * 256 + (m & 63) * 4 (conflict-free for any
 //                          codes), address = one PRMT of (code word, lane constant), one LDS and one FADD per gathered value; code
@@ -117,10 +118,10 @@ extern "C" int vdb_microbench_device(int32_t kind, int64_t rows, int32_t row_byt
     VDB_CUDA(cudaEventCreate(&e0)); VDB_CUDA(cudaEventCreate(&e1));
     std::vector<float> ms;
     double units = 0;
-    if (kind == 0 || kind == 1) {
+    if (kind == 0 || kind == 1 || kind == 4) {            // kind 4 = kind 0 with ONE 8-warp CTA per SM (what one query's distance phase has)
         // kind 0 keeps 2 lines per row in flight (row_bytes % 256 == 0: 512-byte int8 rows included), kind 1 keeps 8 (or 4 for 512-byte rows)
-        if (rows <= 0 || row_bytes <= 0 || (row_bytes % (kind == 0 ? 256 : 512)) != 0 || work <= 0) { vdb_set_error("row gather: rows > 0, row_bytes % 256 (kind 0) / % 512 (kind 1) == 0, work = rows gathered per CTA"); return VDB_ERR_INVALID; }
-        const int grid = sms * 2, per_cta = (work + 127) / 128 * 128;
+        if (rows <= 0 || row_bytes <= 0 || (row_bytes % (kind != 1 ? 256 : 512)) != 0 || work <= 0) { vdb_set_error("row gather: rows > 0, row_bytes % 256 (kind 0) / % 512 (kind 1) == 0, work = rows gathered per CTA"); return VDB_ERR_INVALID; }
+        const int grid = kind == 4 ? sms : sms * 2, per_cta = (work + 127) / 128 * 128;
         unsigned char* table = nullptr; int* idx = nullptr; uint32_t* sink = nullptr;
         VDB_CUDA(cudaMalloc(&table, (size_t)rows * row_bytes));
         VDB_CUDA(cudaMemset(table, 1, (size_t)rows * row_bytes));
@@ -131,7 +132,7 @@ extern "C" int vdb_microbench_device(int32_t kind, int64_t rows, int32_t row_byt
         VDB_CUDA(cudaMemcpy(idx, h.data(), h.size() * 4, cudaMemcpyHostToDevice));
         for (int r = 0; r < reps + 2; r++) {
             cudaEventRecord(e0);
-            if (kind == 0) row_gather_kernel<2><<<grid, 256>>>(table, idx, per_cta, row_bytes, sink);
+            if (kind == 0 || kind == 4) row_gather_kernel<2><<<grid, 256>>>(table, idx, per_cta, row_bytes, sink);
             else if (row_bytes % 1024 == 0) row_gather_kernel<8><<<grid, 256>>>(table, idx, per_cta, row_bytes, sink);
             else row_gather_kernel<4><<<grid, 256>>>(table, idx, per_cta, row_bytes, sink);
             cudaEventRecord(e1);
