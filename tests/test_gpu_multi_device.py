@@ -117,6 +117,44 @@ def test_pq_multi_device_local_shortlists_retry_when_rows_are_not_spread_evenly(
     f.close()
 
 
+def test_multi_device_edge_shapes(v, po, monkeypatch):
+    """tiny and ragged cases: fewer rows than shards ask for, k beyond a shard's rows, a shortlist longer than a shard, rows arriving in
+    several calls that straddle shard boundaries — always the single-GPU answer"""
+    monkeypatch.setenv("VDB_MULTI_SAME_DEVICE", "1")
+    dim, M = 32, 4
+    Q = po.synth(43, 7, dim)
+    for n, g, k in ((10, 3, 5), (50, 4, 20), (301, 5, 64)):
+        X = po.synth(42, n, dim)
+        ref = v.NativeFlatIndex(dim, 400)
+        ref.addBatch(np.arange(n, dtype=np.int32), X)
+        ri, rd = ref.searchBatch(Q, k)
+        ref.close()
+        f = v.NativeFlatIndex(dim, 400, n_devices=g)                       # capacity 400 -> shards of 100 / 80 rows: later shards stay empty
+        for lo in range(0, n, 37):                                         # several calls, pieces straddle shard boundaries
+            hi = min(n, lo + 37)
+            f.addBatch(np.arange(lo, hi, dtype=np.int32), X[lo:hi])
+        ids, d = f.searchBatch(Q, k)
+        assert np.array_equal(ids, ri) and np.array_equal(bits(d), bits(rd)), (n, g, k)
+        assert f.size() == n
+        f.close()
+    # PQ + rerank: shortlist (R = 200) longer than every shard (<= 80 rows), k beyond a shard
+    n, g, k, R = 301, 5, 90, 200
+    X = po.synth(42, n, dim)
+    ref = v.NativePqIndex(dim, 400, M=M, rerank=R)
+    ref.train(X[:256]); ref.addBatch(np.arange(n, dtype=np.int32), X)
+    ri, rd = ref.searchBatch(Q, k)
+    cb = ref.codebooks()
+    ref.close()
+    f = v.NativePqIndex(dim, 400, M=M, rerank=R, n_devices=g)
+    f.set_codebooks(cb)
+    for lo in range(0, n, 37):
+        hi = min(n, lo + 37)
+        f.addBatch(np.arange(lo, hi, dtype=np.int32), X[lo:hi])
+    ids, d = f.searchBatch(Q, k)
+    assert np.array_equal(ids, ri) and np.array_equal(bits(d), bits(rd))
+    f.close()
+
+
 def test_multi_device_rejects_graph_indexes_and_unsupported_calls(v, monkeypatch):
     monkeypatch.setenv("VDB_MULTI_SAME_DEVICE", "1")
     with pytest.raises(Exception, match="replica"):
