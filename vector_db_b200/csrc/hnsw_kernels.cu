@@ -971,8 +971,12 @@ __device__ __forceinline__ void fold_side_buffer(uint64_t* P, const uint64_t* F0
 }
 
 // FULL (bf16 rows only): rows are a whole number of 256-byte MMA stages, the distance loop needs no bound checks
-template <bool BF16, bool FULL, int FP8 = 0, bool I8 = false>   // FP8: 0 = off, else 32-byte loads per row and stage (1 or 2) of the 8-bit rows; I8: int8 instead of e4m3
-__global__ void __launch_bounds__(HN_NT, 2) hnsw_search_kernel(const HnswSearchParams p) {
+// MINB = CTAs per SM the kernel is compiled for: 2 (128 registers per thread) when the search state of a query needs more than a third
+// of the shared memory (ef = 5000: 110 KB), 3 (80 registers, some spills) when three queries fit (ef <= ~1700: C1, C2, the graph
+// builder's insert searches) — small-ef walks are bookkeeping-bound and gain more from the third resident CTA than they lose to the
+// spills (C1: 2.39 -> 2.17 ms per 1000 queries), large-ef walks would only lose (C3 with the 80-register code: 19.6 -> 21.1 ms).
+template <bool BF16, bool FULL, int FP8 = 0, bool I8 = false, int MINB = 2>   // FP8: 0 = off, else 32-byte loads per row and stage (1 or 2) of the 8-bit rows; I8: int8 instead of e4m3
+__global__ void __launch_bounds__(HN_NT, MINB) hnsw_search_kernel(const HnswSearchParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int qpad = (p.dim + 7) & ~7;
     float* sq = reinterpret_cast<float*>(smem_raw);                       // [qpad] query, fp32 (zero padded)
@@ -1365,6 +1369,17 @@ size_t hnsw_search_smem_bytes(const HnswSearchParams& p) {
     return b;
 }
 int hnsw_max_batch(int deg) { return std::min(HN_MAXB, HN_FMAX / std::max(deg, 1)); }
+template <bool BF16, bool FULL, int FP8, bool I8>
+static int hn_launch(const HnswSearchParams& p, int grid, size_t smem, cudaStream_t st) {
+    if (p.ctas_per_sm >= 3) {
+        if (cudaFuncSetAttribute(hnsw_search_kernel<BF16, FULL, FP8, I8, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 2;
+        hnsw_search_kernel<BF16, FULL, FP8, I8, 3><<<grid, HN_NT, smem, st>>>(p);
+    } else {
+        if (cudaFuncSetAttribute(hnsw_search_kernel<BF16, FULL, FP8, I8, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 2;
+        hnsw_search_kernel<BF16, FULL, FP8, I8, 2><<<grid, HN_NT, smem, st>>>(p);
+    }
+    return 0;
+}
 int launch_hnsw_search(const HnswSearchParams& p, int grid, cudaStream_t st) {
     if (p.nq <= 0) return 0;
     if (p.k + 22 > HN_FMAX || p.deg > 64 || p.batch < 1 || p.batch * p.deg > HN_FMAX || p.batch > HN_MAXB) return 1;
@@ -1372,33 +1387,14 @@ int launch_hnsw_search(const HnswSearchParams& p, int grid, cudaStream_t st) {
     const size_t smem = hnsw_search_smem_bytes(p);
     if (p.tstore == 3) {
         if ((p.tstride & 127) != 0 || 4 * p.k + 24 > HN_FMAX) return 1;
-        if ((p.tstride & 255) == 0) {
-            if (cudaFuncSetAttribute(hnsw_search_kernel<true, false, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 2;
-            hnsw_search_kernel<true, false, 2, true><<<grid, HN_NT, smem, st>>>(p);
-        } else {
-            if (cudaFuncSetAttribute(hnsw_search_kernel<true, false, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 2;
-            hnsw_search_kernel<true, false, 1, true><<<grid, HN_NT, smem, st>>>(p);
-        }
-    } else if (p.tstore == 2) {
-        if ((p.tstride & 127) != 0 || 4 * p.k + 24 > HN_FMAX) return 1;
-        if ((p.tstride & 255) == 0) {
-            if (cudaFuncSetAttribute(hnsw_search_kernel<true, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 2;
-            hnsw_search_kernel<true, false, 2><<<grid, HN_NT, smem, st>>>(p);
-        } else {
-            if (cudaFuncSetAttribute(hnsw_search_kernel<true, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 2;
-            hnsw_search_kernel<true, false, 1><<<grid, HN_NT, smem, st>>>(p);
-        }
-    } else if (p.tstore == 1 && (p.tstride & 255) == 0) {
-        if (cudaFuncSetAttribute(hnsw_search_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 2;
-        hnsw_search_kernel<true, true><<<grid, HN_NT, smem, st>>>(p);
-    } else if (p.tstore == 1) {
-        if (cudaFuncSetAttribute(hnsw_search_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 2;
-        hnsw_search_kernel<true, false><<<grid, HN_NT, smem, st>>>(p);
-    } else {
-        if (cudaFuncSetAttribute(hnsw_search_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return 2;
-        hnsw_search_kernel<false, false><<<grid, HN_NT, smem, st>>>(p);
+        return (p.tstride & 255) == 0 ? hn_launch<true, false, 2, true>(p, grid, smem, st) : hn_launch<true, false, 1, true>(p, grid, smem, st);
     }
-    return 0;
+    if (p.tstore == 2) {
+        if ((p.tstride & 127) != 0 || 4 * p.k + 24 > HN_FMAX) return 1;
+        return (p.tstride & 255) == 0 ? hn_launch<true, false, 2, false>(p, grid, smem, st) : hn_launch<true, false, 1, false>(p, grid, smem, st);
+    }
+    if (p.tstore == 1) return (p.tstride & 255) == 0 ? hn_launch<true, true, 0, false>(p, grid, smem, st) : hn_launch<true, false, 0, false>(p, grid, smem, st);
+    return hn_launch<false, false, 0, false>(p, grid, smem, st);
 }
 
 // ---- traversal copy of the base rows: zero-padded to a multiple of 8 elements, fp32 or bf16 (round to nearest even);

@@ -60,6 +60,7 @@ struct HnswSearchParams {
     int tstride, tstore;      // bytes per traversal row (multiple of 16); 0 = fp32, 1 = bf16, 2 = fp8 e4m3, 3 = int8
     int batch;                // candidates expanded per round (1 = the Java order)
     int profile;              // accumulate thread-0 cycle counters per phase into counters[2..9]
+    int ctas_per_sm;          // CTAs per SM the launch is sized for (2 or 3): selects the kernel build (128 / 80 registers per thread)
     int* qcounter;            // zeroed before the launch: CTAs take their next query with atomicAdd (dynamic balance); NULL = static stride
     int visited_in_smem;
     int prefetch;             // pull fresh rows towards L2 as soon as they are discovered (traversal copy well beyond L2 only)

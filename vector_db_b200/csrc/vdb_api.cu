@@ -704,7 +704,9 @@ int vdb_graph_search_launch(vdb_index* x, HnswSearchParams& p, cudaStream_t st) 
     size_t smem = hnsw_search_smem_bytes(p);
     if (smem > 112 * 1024) { p.visited_in_smem = 0; smem = hnsw_search_smem_bytes(p); }
     if (smem > 227 * 1024) FAIL(VDB_ERR_INVALID, "ef too large for the shared-memory pool");
-    int per_sm = (int)std::max<size_t>(1, std::min<size_t>(2, (227 * 1024) / (smem + 1024)));
+    int per_sm = (int)std::max<size_t>(1, std::min<size_t>(3, (227 * 1024) / (smem + 1024)));
+    if (getenv("VDB_HNSW_TWO_CTAS")) per_sm = std::min(per_sm, 2);
+    p.ctas_per_sm = per_sm;
     int grid = (int)std::min<int64_t>(p.nq, (int64_t)x->num_sms * per_sm);
     if (!p.visited_in_smem) {
         VDB_TRY(x->d_visited.ensure((size_t)grid * ((p.n + 31) / 32), 0, st));
