@@ -727,7 +727,10 @@ FlatGemmPlan flat_gemm_plan(int64_t n, int dim, int k) {
     p.n_pad = ((n + BN - 1) / BN) * BN;
     p.k2 = std::min(2048, round_up_i(std::max(4 * k, k + 128), 128));
     p.k2p = next_pow2(p.k2);
-    p.step = std::max<int64_t>(1, (n + 16383) / 16384);
+    // sample of the threshold pass: 1 row in 32, between 4 096 and 16 384 rows — a fixed 16 384-row sample is 13 % of a 125 k-row
+    // shard (1 M rows over 8 GPUs), and the sample GEMM + threshold selection do not shrink with the shard otherwise
+    const int64_t s_target = std::min<int64_t>(16384, std::max<int64_t>(4096, n / 32));
+    p.step = std::max<int64_t>(1, (n + s_target - 1) / s_target);
     p.S = (int)((n + p.step - 1) / p.step);
     p.S_pad = round_up_i(p.S, BN);
     p.P = next_pow2(p.S);
