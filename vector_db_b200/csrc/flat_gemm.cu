@@ -515,9 +515,26 @@ threshold_select_kernel(const float* __restrict__ scores, int64_t ld, int S, int
         mn = min(mn, key[j]);
     }
     if (s < TS_NT - 1) {
-        s_mins[threadIdx.x] = mn;
-        block_bitonic_sort_u32(s_mins, TS_NT);
-        const uint32_t pivot = s_mins[s];
+        // pivot without a block-wide sort: every warp sorts its 32 per-thread minima in registers (15 shuffle stages); with
+        // j = ceil((s + 1) / 16), at least 16 j >= s + 1 scores lie at or below the LARGEST of the 16 warps' j-th smallest minima.
+        uint32_t v = mn;
+        const int lane = threadIdx.x & 31;
+#pragma unroll
+        for (int k = 2; k <= 32; k <<= 1) {
+#pragma unroll
+            for (int j = k >> 1; j > 0; j >>= 1) {
+                const uint32_t o = __shfl_xor_sync(0xffffffffu, v, j);
+                const bool keepmin = ((lane & j) == 0) == ((lane & k) == 0);
+                v = keepmin ? min(v, o) : max(v, o);
+            }
+        }
+        const int jth = (s + 16) / 16;                                 // ceil((s + 1) / 16), <= 32
+        const uint32_t wj = __shfl_sync(0xffffffffu, v, jth - 1);
+        if (lane == 0) s_mins[threadIdx.x >> 5] = wj;
+        __syncthreads();
+        uint32_t pivot = 0u;
+#pragma unroll
+        for (int w = 0; w < TS_NT / 32; w++) pivot = max(pivot, s_mins[w]);
 #pragma unroll
         for (int j = 0; j < TS_PER; j++)
             if (key[j] <= pivot) {
@@ -527,11 +544,13 @@ threshold_select_kernel(const float* __restrict__ scores, int64_t ld, int S, int
         __syncthreads();
         const int n = (int)s_n;
         if (n <= TS_LCAP) {
-            int Pn = 2;
-            while (Pn < n) Pn <<= 1;
-            for (int i = n + threadIdx.x; i < Pn; i += TS_NT) skeys[i] = 0xffffffffu;
-            block_bitonic_sort_u32(skeys, Pn);
-            if (threadIdx.x == 0) tau[q] = ord2f(skeys[s]);
+            // the s-th (0-based) smallest of the n collected scores: every key counts the keys below it (ties: lower slot first)
+            for (int i = threadIdx.x; i < n; i += TS_NT) {
+                const uint32_t me = skeys[i];
+                int r = 0;
+                for (int t = 0; t < n; t++) { const uint32_t o = skeys[t]; r += (o < me || (o == me && t < i)) ? 1 : 0; }
+                if (r == s) tau[q] = ord2f(me);
+            }
             return;
         }
         __syncthreads();
