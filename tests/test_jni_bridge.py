@@ -234,3 +234,35 @@ def test_bridge_through_mock_jnienv_matches_c_abi(po):
     assert b.nativeSize(b.env, None, h) == -1
     assert b.L.mock_outstanding_elements() == 0
     g.close(); pq.close()
+
+
+@pytest.mark.gpu
+def test_bridge_spreads_one_index_over_devices_from_the_environment(po, monkeypatch):
+    """VECTORDB_DEVICES = vdb_config.n_devices: the Java constructors keep the reference's signatures, the bridge reads the device
+    count at creation; ONE nativeSearchBatch then fans out over the shards and returns the single-index answer bit for bit
+    (on a one-GPU box the shards share the device: VDB_MULTI_SAME_DEVICE)."""
+    import vector_db_b200 as v
+    b = Bridge()
+    n, dim, k, nq = 6000, 48, 12, 33
+    X, Q = po.synth(42, n, dim), po.synth(43, nq, dim)
+    ref = v.NativeFlatIndex(dim, n)
+    ids = np.arange(n, dtype=np.int32)
+    ref.addBatch(ids, X)
+    want_i, want_d = ref.searchBatch(Q, k)
+    ref.close()
+    monkeypatch.setenv("VDB_MULTI_SAME_DEVICE", "1")
+    monkeypatch.setenv("VECTORDB_DEVICES", "3")
+    h = b.nativeCreateFlat(b.env, None, dim, n, 0)
+    monkeypatch.delenv("VECTORDB_DEVICES")
+    assert h > 0
+    ib, vb = b.buf(ids), b.buf(X)
+    b.nativeAddBatch(b.env, None, h, ib, vb, n, dim)
+    assert b.exception() is None and b.nativeSize(b.env, None, h) == n
+    out_i = np.zeros((nq, k), dtype=np.int32); out_d = np.zeros((nq, k), dtype=np.float32)
+    qb, oib, odb = b.buf(Q), b.buf(out_i), b.buf(out_d)
+    assert b.nativeSearchBatch(b.env, None, h, qb, nq, k, dim, oib, odb) == nq and b.exception() is None
+    assert np.array_equal(out_i, want_i) and np.array_equal(out_d.view(np.uint32), want_d.view(np.uint32))
+    # a graph index refuses more than one device (replicas): creation fails the reference's way (handle 0)
+    monkeypatch.setenv("VECTORDB_DEVICES", "2")
+    assert b.nativeCreateHNSWPQ(b.env, None, dim, 5000, 32, 64, 64, 6, 8, 25) == 0
+    b.nativeDestroy(b.env, None, h)
