@@ -137,6 +137,21 @@ def test_multi_device_edge_shapes(v, po, monkeypatch):
         assert np.array_equal(ids, ri) and np.array_equal(bits(d), bits(rd)), (n, g, k)
         assert f.size() == n
         f.close()
+    # add -> search -> add -> search: rows that arrive after the first search go to the last shard (until the next rebuild) — far
+    # beyond an even share of the capacity; the answer stays the single index's
+    n, g, k = 390, 4, 15
+    X = po.synth(42, n, dim)
+    ref = v.NativeFlatIndex(dim, 400)
+    f = v.NativeFlatIndex(dim, 400, n_devices=g)
+    for lo, hi in ((0, 40), (40, 200), (200, 390)):
+        for idx in (ref, f):
+            idx.addBatch(np.arange(lo, hi, dtype=np.int32), X[lo:hi])
+        ri, rd = ref.searchBatch(Q, k)
+        ids, d = f.searchBatch(Q, k)
+        assert np.array_equal(ids, ri) and np.array_equal(bits(d), bits(rd)), hi
+    with pytest.raises(Exception):
+        f.addBatch(np.arange(390, 420, dtype=np.int32), po.synth(44, 30, dim))      # the FRONT index enforces max_elements
+    ref.close(); f.close()
     # PQ + rerank: shortlist (R = 200) longer than every shard (<= 80 rows), k beyond a shard
     n, g, k, R = 301, 5, 90, 200
     X = po.synth(42, n, dim)

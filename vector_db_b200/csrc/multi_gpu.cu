@@ -37,7 +37,8 @@ int vdb_multi_create(vdb_index* f) {
     for (int s = 0; s < g; s++) {
         vdb_config c = f->cfg;
         c.n_devices = 1; c.device = same ? f->cfg.device : f->cfg.device + s;
-        c.max_elements = (int32_t)((f->cfg.max_elements + g - 1) / g + 1);
+        // capacity is a limit, not an allocation: every shard may take the whole index (rows added after the first search all go
+        // to the last shard until the next vdb_build); the front index enforces max_elements
         vdb_index* sh = nullptr;
         VDB_TRY(vdb_create(&c, &sh));
         f->shards.push_back(sh);
