@@ -151,6 +151,9 @@ def test_multi_device_edge_shapes(v, po, monkeypatch):
         assert np.array_equal(ids, ri) and np.array_equal(bits(d), bits(rd)), hi
     with pytest.raises(Exception):
         f.addBatch(np.arange(390, 420, dtype=np.int32), po.synth(44, 30, dim))      # the FRONT index enforces max_elements
+    f.buildIndex()                                                                  # rebuildIndex splits the rows evenly again
+    ids, d = f.searchBatch(Q, k)
+    assert np.array_equal(ids, ri) and np.array_equal(bits(d), bits(rd)) and f.size() == n
     ref.close(); f.close()
     # PQ + rerank: shortlist (R = 200) longer than every shard (<= 80 rows), k beyond a shard
     n, g, k, R = 301, 5, 90, 200

@@ -92,6 +92,23 @@ int vdb_multi_sync(vdb_index* f) {
     for (int s = 0; s < g; s++) { std::lock_guard<std::mutex> lk(f->shards[s]->mu); VDB_TRY(vdb_sync_index_nolock(f->shards[s])); }
     return VDB_OK;
 }
+// vdb_build (rebuildIndex) of a host-backed multi-device index: the rows are split evenly again (rows that arrived after the first
+// search had all gone to the last shard). The shards are recreated and refilled; trained codebooks carry over.
+int vdb_multi_rebuild(vdb_index* f) {
+    if (f->device_only) return vdb_multi_sync(f);
+    std::vector<float> cb;
+    const bool pq = f->cfg.index_type == VDB_INDEX_PQ;
+    if (pq && f->trained) {
+        cb.resize((size_t)f->pq_m * VDB_NCENT * f->sd);
+        VDB_TRY(vdb_get_codebooks(f->shards[0], cb.data()));
+    }
+    vdb_multi_destroy(f);
+    f->ev_front = nullptr;
+    VDB_TRY(vdb_multi_create(f));
+    if (!cb.empty()) for (auto* sh : f->shards) VDB_TRY(vdb_set_codebooks(sh, cb.data()));
+    f->n_distributed = 0;
+    return vdb_multi_sync(f);
+}
 int vdb_multi_fill_synthetic(vdb_index* f, uint64_t seed, int64_t cnt) {
     const int g = (int)f->shards.size();
     if (f->n != 0) MG_FAIL(VDB_ERR_INVALID, "multi-device synthetic fill: the index must be empty");

@@ -557,7 +557,7 @@ extern "C" int vdb_build(vdb_index* x) {
     std::lock_guard<std::mutex> lk(x->mu);
     VDB_CUDA(cudaSetDevice(x->cfg.device));
     const int t = x->cfg.index_type;
-    if (MULTI(x)) return vdb_multi_sync(x);
+    if (MULTI(x)) return vdb_multi_rebuild(x);
     if (t == VDB_INDEX_FLAT || t == VDB_INDEX_PQ) return sync_index(x);     // NativeIndex.buildIndex() is a no-op (NativeIndex.java:84-87)
     if (x->device_only) FAIL(VDB_ERR_INVALID, "graph indexes need host rows");
     const int dim = x->cfg.dim;

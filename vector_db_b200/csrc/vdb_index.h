@@ -171,6 +171,7 @@ int vdb_multi_create(vdb_index* front);
 void vdb_multi_destroy(vdb_index* front);
 int vdb_multi_train(vdb_index* front, const float* samples, int64_t ns);
 int vdb_multi_sync(vdb_index* front);
+int vdb_multi_rebuild(vdb_index* front);
 int vdb_multi_fill_synthetic(vdb_index* front, uint64_t seed, int64_t cnt);
 int vdb_multi_encode_all(vdb_index* front);
 int vdb_multi_search(vdb_index* front, const float* q, bool q_on_device, int64_t nq, int k, int32_t* out_ids, float* out_d, cudaStream_t user_stream);
