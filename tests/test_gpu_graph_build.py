@@ -74,4 +74,12 @@ def test_gpu_built_graph_matches_host_built_graph_statistically(v, po, monkeypat
     assert gg.size() == n + 5
     ids, _ = gg.searchBatch(extra, 10)
     assert sum(int(n + j in ids[j]) for j in range(5)) >= 3                   # a fresh vector is (almost always) its own neighbour
+    # removal + a SECOND device rebuild (the store is compacted, the level stream continues): the index stays sound
+    assert gg.removeVector(3) and gg.removeVector(n + 1)
+    gg.buildIndex()
+    assert gg.size() == n + 3
+    gi2, _ = gg.searchBatch(Q, k)
+    assert not np.isin(gi2, [3, n + 1]).any()
+    keep = ~np.isin(gt, [3]).any(axis=1)                                      # queries whose exact answer lost nothing
+    assert recall(gi2[keep], gt[keep]) >= rh - 0.02, (recall(gi2[keep], gt[keep]), rh)
     gh.close(); gg.close()
