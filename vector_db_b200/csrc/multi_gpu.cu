@@ -151,7 +151,9 @@ static int for_each_shard(vdb_index* f, F fn) {
         if (rc[s] != VDB_OK) msg[s] = vdb_last_error();
     };
     std::vector<std::thread> th;
-    for (int s = 1; s < g; s++) th.emplace_back(run, s);
+    for (int s = 1; s < g; s++) {
+        try { th.emplace_back(run, s); } catch (...) { run(s); }       // no thread to be had: do it here (nothing may throw across the C ABI)
+    }
     run(0);
     for (auto& t : th) t.join();
     cudaSetDevice(f->cfg.device);
