@@ -108,7 +108,7 @@ __global__ void __launch_bounds__(512, 1) lds_gather_pair_kernel(int iters, floa
 }  // namespace
 
 // out[0] = milliseconds per launch (median of `reps`), out[1] = units per launch (bytes gathered / gathers)
-extern "C" int vdb_microbench_device(int32_t kind, int64_t rows, int32_t row_bytes, int32_t work, int32_t reps, double* out) {
+extern "C" int vdb_microbench_device(int32_t kind, int64_t rows, int32_t row_bytes, int32_t work, int32_t reps, double* out) try {
     if (!out || reps <= 0 || reps > 100) { vdb_set_error("vdb_microbench_device: bad arguments"); return VDB_ERR_INVALID; }
     cudaDeviceProp prop; int dev = 0;
     VDB_CUDA(cudaGetDevice(&dev));
@@ -178,4 +178,4 @@ extern "C" int vdb_microbench_device(int32_t kind, int64_t rows, int32_t row_byt
     std::sort(ms.begin(), ms.end());
     out[0] = ms[ms.size() / 2]; out[1] = units;
     return VDB_OK;
-}
+} catch (...) { return vdb_caught("vdb_microbench_device"); }

@@ -35,7 +35,7 @@ struct Header {
 }  // namespace
 int vdb_validate_graph(const int32_t* levels, const int32_t* adj, int64_t n, int max_level, int M, int32_t entry);
 
-extern "C" int vdb_save(vdb_index* x, const char* path) {
+extern "C" int vdb_save(vdb_index* x, const char* path) try {
     if (!x || !path) FAILS(VDB_ERR_INVALID, "vdb_save: bad arguments");
     if (!x->shards.empty()) FAILS(VDB_ERR_INVALID, "vdb_save: not available on a multi-device index (n_devices > 1)");
     if (x->device_only) FAILS(VDB_ERR_INVALID, "vdb_save: device-generated rows are not persisted");
@@ -72,7 +72,7 @@ extern "C" int vdb_save(vdb_index* x, const char* path) {
     }
     if (!ok) FAILS(VDB_ERR_IO, "short write");
     return VDB_OK;
-}
+} catch (...) { return vdb_caught("vdb_save"); }
 
 static int load_impl(vdb_index* x, const char* path) {
     File fh; fh.f = fopen(path, "rb");
@@ -146,7 +146,7 @@ static int load_impl(vdb_index* x, const char* path) {
     return VDB_OK;
 }
 
-extern "C" int vdb_load(vdb_index* x, const char* path) {
+extern "C" int vdb_load(vdb_index* x, const char* path) try {
     if (!x || !path) FAILS(VDB_ERR_INVALID, "vdb_load: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
     VDB_CUDA(cudaSetDevice(x->cfg.device));
@@ -155,4 +155,4 @@ extern "C" int vdb_load(vdb_index* x, const char* path) {
     try { return load_impl(x, path); }
     catch (const std::bad_alloc&) { FAILS(VDB_ERR_IO, "vdb_load: out of memory (corrupt snapshot header?)"); }
     catch (const std::exception& e) { FAILS(VDB_ERR_IO, std::string("vdb_load: ") + e.what()); }
-}
+} catch (...) { return vdb_caught("vdb_load"); }

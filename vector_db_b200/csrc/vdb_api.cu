@@ -16,6 +16,17 @@ static thread_local std::string g_err;
 void vdb_set_error(const std::string& msg) { g_err = msg; }
 #define FAIL(code, msg) do { vdb_set_error(msg); return (code); } while (0)
 
+// Every extern "C" entry point is a function-try-block ending in `catch (...) { return vdb_caught(name); }`: a C++ exception
+// (std::bad_alloc from a host vector, anything else) becomes an error code + message, never unwinds into the caller's frames
+// (a JNI frame, ctypes). Called from inside a catch handler only.
+int vdb_caught(const char* fn) {
+    try { throw; }
+    catch (const std::bad_alloc&) { vdb_set_error(std::string(fn) + ": out of host memory"); }
+    catch (const std::exception& e) { vdb_set_error(std::string(fn) + ": " + e.what()); }
+    catch (...) { vdb_set_error(std::string(fn) + ": unknown C++ exception"); }
+    return VDB_ERR_INVALID;
+}
+
 extern "C" const char* vdb_last_error(void) { return g_err.c_str(); }
 extern "C" const char* vdb_version(void) { return "vector_db_b200 0.1 (sm_100a)"; }
 
@@ -25,7 +36,7 @@ static int recommended_pq_m(int dim) {   // CompressionConfig.recommendedConfig 
     return m;
 }
 
-extern "C" int vdb_default_config(int32_t index_type, int32_t dim, int32_t max_elements, vdb_config* c) {
+extern "C" int vdb_default_config(int32_t index_type, int32_t dim, int32_t max_elements, vdb_config* c) try {
     if (!c || dim <= 0 || max_elements <= 0) FAIL(VDB_ERR_INVALID, "vdb_default_config: bad arguments");
     std::memset(c, 0, sizeof(*c));
     c->dim = dim; c->max_elements = max_elements; c->index_type = index_type;
@@ -42,9 +53,9 @@ extern "C" int vdb_default_config(int32_t index_type, int32_t dim, int32_t max_e
         default: FAIL(VDB_ERR_INVALID, "unknown index_type");
     }
     return VDB_OK;
-}
+} catch (...) { return vdb_caught("vdb_default_config"); }
 
-extern "C" int vdb_create(const vdb_config* cfg, vdb_index** out) {
+extern "C" int vdb_create(const vdb_config* cfg, vdb_index** out) try {
     if (!cfg || !out) FAIL(VDB_ERR_INVALID, "vdb_create: null argument");
     *out = nullptr;
     if (cfg->dim <= 0 || cfg->max_elements <= 0) FAIL(VDB_ERR_INVALID, "dim and max_elements must be positive");
@@ -94,11 +105,11 @@ extern "C" int vdb_create(const vdb_config* cfg, vdb_index** out) {
     }
     *out = x;
     return VDB_OK;
-}
+} catch (...) { return vdb_caught("vdb_create"); }
 #define MULTI(x) (!(x)->shards.empty())
 #define NOT_MULTI(x, what) do { if (MULTI(x)) FAIL(VDB_ERR_INVALID, what ": not available on a multi-device index (n_devices > 1)"); } while (0)
 
-extern "C" int vdb_destroy(vdb_index* x) {
+extern "C" int vdb_destroy(vdb_index* x) try {
     if (!x) return VDB_OK;
     if (MULTI(x)) vdb_multi_destroy(x);
     cudaSetDevice(x->cfg.device);
@@ -116,7 +127,7 @@ extern "C" int vdb_destroy(vdb_index* x) {
     if (x->stream) cudaStreamDestroy(x->stream);
     delete x;
     return VDB_OK;
-}
+} catch (...) { return vdb_caught("vdb_destroy"); }
 
 static inline bool is_graph(const vdb_index* x) { return x->cfg.index_type == VDB_INDEX_HNSW || x->cfg.index_type == VDB_INDEX_HNSW_PQ; }
 extern "C" int64_t vdb_size(const vdb_index* x) { return x ? (is_graph(x) ? x->n_live : x->n) : -1; }   // Java: vectors.size()
@@ -356,7 +367,7 @@ static int sync_index(vdb_index* x) {
 }
 
 // ---- add / train / build ---------------------------------------------------------------------------------------
-extern "C" int vdb_add_batch(vdb_index* x, const int32_t* ids, const float* vecs, int64_t cnt) {
+extern "C" int vdb_add_batch(vdb_index* x, const int32_t* ids, const float* vecs, int64_t cnt) try {
     if (!x || (!vecs && cnt > 0) || cnt < 0) FAIL(VDB_ERR_INVALID, "vdb_add_batch: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
     if (x->device_only) FAIL(VDB_ERR_INVALID, "index holds device-generated rows; host adds are not allowed");
@@ -404,7 +415,7 @@ extern "C" int vdb_add_batch(vdb_index* x, const int32_t* ids, const float* vecs
     }
     x->n += cnt;
     return VDB_OK;
-}
+} catch (...) { return vdb_caught("vdb_add_batch"); }
 
 // first live key of Java's `vectors` map in iteration order, skipping `skip_id` (HnswPqIndex.java:577-584). The map is a
 // ConcurrentHashMap<>(maxElements): table = tableSizeFor(1.5 * maxElements + 1) bins and never resizes (<= maxElements entries
@@ -423,15 +434,15 @@ static int64_t java_first_live_row(const vdb_index* x, int32_t skip_id) {
     return best_row;
 }
 
-extern "C" int vdb_contains(vdb_index* x, int32_t id) {
+extern "C" int vdb_contains(vdb_index* x, int32_t id) try {
     if (!x) return 0;
     std::lock_guard<std::mutex> lk(x->mu);
     if (is_graph(x)) return x->id2row.count(id) ? 1 : 0;
     for (int64_t i = 0; i < (int64_t)x->h_ids.size(); i++) if (x->h_ids[i] == id) return 1;
     return 0;
-}
+} catch (...) { return vdb_caught("vdb_contains"); }
 
-extern "C" int vdb_remove(vdb_index* x, int32_t id, int32_t* removed) {
+extern "C" int vdb_remove(vdb_index* x, int32_t id, int32_t* removed) try {
     if (!x) FAIL(VDB_ERR_INVALID, "vdb_remove: null index");
     if (removed) *removed = 0;
     std::lock_guard<std::mutex> lk(x->mu);
@@ -453,9 +464,9 @@ extern "C" int vdb_remove(vdb_index* x, int32_t id, int32_t* removed) {
     x->any_dead = true; x->dead_dirty = true; x->graph_uploaded = false;
     if (removed) *removed = 1;
     return VDB_OK;
-}
+} catch (...) { return vdb_caught("vdb_remove"); }
 
-extern "C" int vdb_train(vdb_index* x, const float* samples, int64_t ns) {
+extern "C" int vdb_train(vdb_index* x, const float* samples, int64_t ns) try {
     if (!x || !samples) FAIL(VDB_ERR_INVALID, "Invalid training samples");
     std::lock_guard<std::mutex> lk(x->mu);
     if (x->pq_m == 0) FAIL(VDB_ERR_INVALID, "index has no PQ stage");
@@ -464,9 +475,9 @@ extern "C" int vdb_train(vdb_index* x, const float* samples, int64_t ns) {
     VDB_TRY(train_on_device(x, samples, ns));
     x->n_coded = 0;
     return VDB_OK;
-}
+} catch (...) { return vdb_caught("vdb_train"); }
 
-extern "C" int vdb_set_codebooks(vdb_index* x, const float* cb) {
+extern "C" int vdb_set_codebooks(vdb_index* x, const float* cb) try {
     if (!x || !cb || x->pq_m == 0) FAIL(VDB_ERR_INVALID, "vdb_set_codebooks: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
     if (MULTI(x)) { for (auto* sh : x->shards) VDB_TRY(vdb_set_codebooks(sh, cb)); x->trained = true; return VDB_OK; }
@@ -477,24 +488,24 @@ extern "C" int vdb_set_codebooks(vdb_index* x, const float* cb) {
     VDB_CUDA(cudaStreamSynchronize(x->stream));
     x->trained = true; x->n_coded = 0;
     return VDB_OK;
-}
-extern "C" int vdb_get_codebooks(vdb_index* x, float* out) {
+} catch (...) { return vdb_caught("vdb_set_codebooks"); }
+extern "C" int vdb_get_codebooks(vdb_index* x, float* out) try {
     if (!x || !out || !x->trained) FAIL(VDB_ERR_UNTRAINED, "no codebooks");
     std::lock_guard<std::mutex> lk(x->mu);
     if (MULTI(x)) return vdb_get_codebooks(x->shards[0], out);
     VDB_CUDA(cudaSetDevice(x->cfg.device));
     VDB_CUDA(cudaMemcpy(out, x->d_cb.p, (size_t)x->pq_m * VDB_NCENT * x->sd * 4, cudaMemcpyDeviceToHost));
     return VDB_OK;
-}
-extern "C" int vdb_set_codes(vdb_index* x, const uint8_t* codes) {
+} catch (...) { return vdb_caught("vdb_get_codebooks"); }
+extern "C" int vdb_set_codes(vdb_index* x, const uint8_t* codes) try {
     if (!x || !codes || x->pq_m == 0) FAIL(VDB_ERR_INVALID, "vdb_set_codes: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
     NOT_MULTI(x, "vdb_set_codes");
     x->h_codes_override.assign(codes, codes + (size_t)x->n * x->pq_m);
     x->codes_overridden = true; x->n_coded = 0;
     return VDB_OK;
-}
-extern "C" int vdb_get_codes(vdb_index* x, uint8_t* out) {
+} catch (...) { return vdb_caught("vdb_set_codes"); }
+extern "C" int vdb_get_codes(vdb_index* x, uint8_t* out) try {
     if (!x || !out || x->pq_m == 0) FAIL(VDB_ERR_INVALID, "vdb_get_codes: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
     NOT_MULTI(x, "vdb_get_codes");
@@ -502,8 +513,8 @@ extern "C" int vdb_get_codes(vdb_index* x, uint8_t* out) {
     if (x->n_coded < x->n_dev) FAIL(VDB_ERR_UNTRAINED, "codes not available (untrained)");
     VDB_CUDA(cudaMemcpy(out, x->d_codes.p, (size_t)x->n_dev * x->pq_m, cudaMemcpyDeviceToHost));
     return VDB_OK;
-}
-extern "C" int vdb_encode_all(vdb_index* x) {
+} catch (...) { return vdb_caught("vdb_get_codes"); }
+extern "C" int vdb_encode_all(vdb_index* x) try {
     if (!x || x->pq_m == 0) FAIL(VDB_ERR_INVALID, "vdb_encode_all: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
     if (!x->trained) FAIL(VDB_ERR_UNTRAINED, "train first");
@@ -512,7 +523,7 @@ extern "C" int vdb_encode_all(vdb_index* x) {
     VDB_TRY(upload_rows(x));
     x->n_coded = 0; x->raw_rows = 0;
     return encode_pending(x);
-}
+} catch (...) { return vdb_caught("vdb_encode_all"); }
 
 // every level in [0, max_level), every neighbour and the entry point inside [-1, n): a bad id would become an out-of-bounds
 // shared-memory atomic in the beam kernel (sticky CUDA fault), so imported graphs are checked on the host first
@@ -526,7 +537,7 @@ int vdb_validate_graph(const int32_t* levels, const int32_t* adj, int64_t n, int
     return VDB_OK;
 }
 
-extern "C" int vdb_set_graph(vdb_index* x, const int32_t* levels, const int32_t* adj, int32_t max_level, int32_t entry) {
+extern "C" int vdb_set_graph(vdb_index* x, const int32_t* levels, const int32_t* adj, int32_t max_level, int32_t entry) try {
     if (!x || !levels || !adj) FAIL(VDB_ERR_INVALID, "vdb_set_graph: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
     if (!is_graph(x)) FAIL(VDB_ERR_INVALID, "vdb_set_graph: not a graph index");
@@ -539,8 +550,8 @@ extern "C" int vdb_set_graph(vdb_index* x, const int32_t* levels, const int32_t*
     for (int64_t r = 0; r < x->n; r++) x->h_jindex[r] = r;
     x->java_size = x->n; x->any_dead = false; x->dead_dirty = false; x->jindex_rows.clear();
     return VDB_OK;
-}
-extern "C" int vdb_get_graph(vdb_index* x, int32_t* levels, int32_t* adj, int32_t* entry) {
+} catch (...) { return vdb_caught("vdb_set_graph"); }
+extern "C" int vdb_get_graph(vdb_index* x, int32_t* levels, int32_t* adj, int32_t* entry) try {
     if (!x) FAIL(VDB_ERR_INVALID, "vdb_get_graph: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
     VDB_TRY(sync_index(x));
@@ -549,10 +560,10 @@ extern "C" int vdb_get_graph(vdb_index* x, int32_t* levels, int32_t* adj, int32_
     if (adj) for (int l = 0; l < x->g.max_level; l++) std::memcpy(adj + (size_t)l * n * x->g.M, x->g.adj[l].data(), (size_t)n * x->g.M * 4);
     if (entry) *entry = x->g.entry;
     return VDB_OK;
-}
+} catch (...) { return vdb_caught("vdb_get_graph"); }
 
 // rebuildIndex (HnswPqIndex.java:676-718, HnswIndex.java:430-478): train if needed, clear, re-add in ascending id order
-extern "C" int vdb_build(vdb_index* x) {
+extern "C" int vdb_build(vdb_index* x) try {
     if (!x) FAIL(VDB_ERR_INVALID, "vdb_build: null index");
     std::lock_guard<std::mutex> lk(x->mu);
     VDB_CUDA(cudaSetDevice(x->cfg.device));
@@ -632,9 +643,9 @@ extern "C" int vdb_build(vdb_index* x) {
         x->java_size = x->n;
     }
     return sync_index(x);
-}
+} catch (...) { return vdb_caught("vdb_build"); }
 
-extern "C" int vdb_fill_synthetic(vdb_index* x, uint64_t seed, int64_t cnt) {
+extern "C" int vdb_fill_synthetic(vdb_index* x, uint64_t seed, int64_t cnt) try {
     if (!x || cnt <= 0) FAIL(VDB_ERR_INVALID, "vdb_fill_synthetic: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
     if (x->cfg.index_type != VDB_INDEX_FLAT && x->cfg.index_type != VDB_INDEX_PQ) FAIL(VDB_ERR_INVALID, "synthetic fill is for FLAT/PQ indexes");
@@ -655,7 +666,7 @@ extern "C" int vdb_fill_synthetic(vdb_index* x, uint64_t seed, int64_t cnt) {
     x->device_only = true;
     x->n += cnt; x->n_dev = x->n;
     return VDB_OK;
-}
+} catch (...) { return vdb_caught("vdb_fill_synthetic"); }
 
 // ---- search ---------------------------------------------------------------------------------------------------
 static inline int java_search_ef(int64_t n, int k, int ef, int cap) {     // HnswPqIndex.java:616-621 (cap = 5000 there)
@@ -915,15 +926,15 @@ int vdb_search_device_nolock(vdb_index* x, const float* d_q, int64_t nq, int k, 
 }
 int vdb_sync_index_nolock(vdb_index* x) { return sync_index(x); }
 
-extern "C" int vdb_search_batch_device(vdb_index* x, const float* d_q, int64_t nq, int32_t k, int32_t* d_ids, float* d_dists, void* stream) {
+extern "C" int vdb_search_batch_device(vdb_index* x, const float* d_q, int64_t nq, int32_t k, int32_t* d_ids, float* d_dists, void* stream) try {
     if (!x || nq < 0 || k <= 0 || (nq > 0 && (!d_q || !d_ids || !d_dists))) FAIL(VDB_ERR_INVALID, "vdb_search_batch_device: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
     cudaStream_t st = (cudaStream_t)stream;   // verbatim cudaStream_t: NULL is CUDA's legacy default stream
     if (MULTI(x)) return vdb_multi_search(x, d_q, true, nq, k, d_ids, d_dists, st);      // buffers on the front device (cfg.device)
     return search_device_locked(x, d_q, nq, k, d_ids, d_dists, st);
-}
+} catch (...) { return vdb_caught("vdb_search_batch_device"); }
 
-extern "C" int vdb_search_batch(vdb_index* x, const float* q, int64_t nq, int32_t k, int32_t* out_ids, float* out_d) {
+extern "C" int vdb_search_batch(vdb_index* x, const float* q, int64_t nq, int32_t k, int32_t* out_ids, float* out_d) try {
     if (!x || nq < 0 || k <= 0 || (nq > 0 && (!q || !out_ids || !out_d))) FAIL(VDB_ERR_INVALID, "vdb_search_batch: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
     VDB_CUDA(cudaSetDevice(x->cfg.device));
@@ -956,9 +967,9 @@ extern "C" int vdb_search_batch(vdb_index* x, const float* q, int64_t nq, int32_
     std::memcpy(out_ids, x->p_ids.p, (size_t)nq * k * 4);
     std::memcpy(out_d, x->p_d.p, (size_t)nq * k * 4);
     return VDB_OK;
-}
+} catch (...) { return vdb_caught("vdb_search_batch"); }
 
-extern "C" int vdb_get_stats(vdb_index* x, vdb_stats* out) {
+extern "C" int vdb_get_stats(vdb_index* x, vdb_stats* out) try {
     if (!x || !out) FAIL(VDB_ERR_INVALID, "vdb_get_stats: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
     if (MULTI(x)) return vdb_multi_stats(x, out);
@@ -982,10 +993,10 @@ extern "C" int vdb_get_stats(vdb_index* x, vdb_stats* out) {
     x->stats.trav_format = x->trav_eff == 0 ? VDB_TRAV_F32 : (x->trav_eff == 2 ? VDB_TRAV_FP8 : (x->trav_eff == 3 ? VDB_TRAV_INT8 : VDB_TRAV_BF16));
     *out = x->stats;
     return VDB_OK;
-}
+} catch (...) { return vdb_caught("vdb_get_stats"); }
 
 // ---- device-side building blocks ------------------------------------------------------------------------------
-extern "C" int vdb_pq_lut_device(vdb_index* x, const float* d_q, int64_t nq, float* d_lut, void* stream) {
+extern "C" int vdb_pq_lut_device(vdb_index* x, const float* d_q, int64_t nq, float* d_lut, void* stream) try {
     if (!x || !d_q || !d_lut || x->pq_m == 0) FAIL(VDB_ERR_INVALID, "vdb_pq_lut_device: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
     NOT_MULTI(x, "vdb_pq_lut_device");
@@ -994,8 +1005,8 @@ extern "C" int vdb_pq_lut_device(vdb_index* x, const float* d_q, int64_t nq, flo
     launch_pq_lut(d_q, x->d_cb.p, (int)nq, x->cfg.dim, x->pq_m, x->cfg.arith, d_lut, st);
     VDB_CUDA(cudaGetLastError());
     return VDB_OK;
-}
-extern "C" int vdb_adc_scan_device(vdb_index* x, const float* d_lut, float* d_out, void* stream) {
+} catch (...) { return vdb_caught("vdb_pq_lut_device"); }
+extern "C" int vdb_adc_scan_device(vdb_index* x, const float* d_lut, float* d_out, void* stream) try {
     if (!x || !d_lut || !d_out || x->pq_m == 0) FAIL(VDB_ERR_INVALID, "vdb_adc_scan_device: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
     NOT_MULTI(x, "vdb_adc_scan_device");
@@ -1005,10 +1016,10 @@ extern "C" int vdb_adc_scan_device(vdb_index* x, const float* d_lut, float* d_ou
     launch_adc_scan_plain(x->d_codes.p, x->n, x->pq_m, d_lut, d_out, st);
     VDB_CUDA(cudaGetLastError());
     return VDB_OK;
-}
+} catch (...) { return vdb_caught("vdb_adc_scan_device"); }
 // ---- the two PQ phases and the boundary selection as device-level calls: one process per GPU (torch.distributed) runs phase 1,
 //      all-gathers the keys (ONE collective of nq x R x 8 bytes), selects the global boundary, runs phase 2, all-gathers the top-k ----
-extern "C" int vdb_pq_shortlist_device(vdb_index* x, const float* d_q, int64_t nq, int32_t k, uint64_t* d_keys_out, int32_t* shortlist_len, void* stream) {
+extern "C" int vdb_pq_shortlist_device(vdb_index* x, const float* d_q, int64_t nq, int32_t k, uint64_t* d_keys_out, int32_t* shortlist_len, void* stream) try {
     if (!x || !d_q || !d_keys_out || nq <= 0 || k <= 0 || x->cfg.index_type != VDB_INDEX_PQ) FAIL(VDB_ERR_INVALID, "vdb_pq_shortlist_device: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
     NOT_MULTI(x, "vdb_pq_shortlist_device");
@@ -1024,21 +1035,21 @@ extern "C" int vdb_pq_shortlist_device(vdb_index* x, const float* d_q, int64_t n
     VDB_TRY(vdb_pq_phase1(x, d_q, nq, k, st));
     VDB_CUDA(cudaMemcpyAsync(d_keys_out, x->d_keys.p, (size_t)nq * R * 8, cudaMemcpyDeviceToDevice, st));
     return VDB_OK;
-}
-extern "C" int vdb_pq_rerank_device(vdb_index* x, const float* d_q, int64_t nq, int32_t k, const uint64_t* d_kth, int32_t* d_ids, float* d_dists, void* stream) {
+} catch (...) { return vdb_caught("vdb_pq_shortlist_device"); }
+extern "C" int vdb_pq_rerank_device(vdb_index* x, const float* d_q, int64_t nq, int32_t k, const uint64_t* d_kth, int32_t* d_ids, float* d_dists, void* stream) try {
     if (!x || !d_q || !d_ids || !d_dists || nq <= 0 || k <= 0 || x->cfg.index_type != VDB_INDEX_PQ) FAIL(VDB_ERR_INVALID, "vdb_pq_rerank_device: bad arguments");
     std::lock_guard<std::mutex> lk(x->mu);
     NOT_MULTI(x, "vdb_pq_rerank_device");
     cudaStream_t st = (cudaStream_t)stream;
     if (x->n == 0) { launch_keys_to_results(nullptr, 0, k, nq, d_ids, d_dists, st); return VDB_OK; }
     return vdb_pq_phase2(x, d_q, nq, k, d_kth, d_ids, d_dists, st);
-}
-extern "C" int vdb_select_kth_key_device(const uint64_t* d_keys, int32_t g, int64_t nq, int32_t R, uint64_t* d_kth, void* stream) {
+} catch (...) { return vdb_caught("vdb_pq_rerank_device"); }
+extern "C" int vdb_select_kth_key_device(const uint64_t* d_keys, int32_t g, int64_t nq, int32_t R, uint64_t* d_kth, void* stream) try {
     if (!d_keys || !d_kth || g <= 0 || R <= 0 || nq <= 0 || (int64_t)g * R > 16384) FAIL(VDB_ERR_INVALID, "vdb_select_kth_key_device: bad arguments (g x R <= 16384)");
     launch_select_kth_key(d_keys, g, (int)nq, R, R, d_kth, nullptr, (cudaStream_t)stream);
     VDB_CUDA(cudaGetLastError());
     return VDB_OK;
-}
+} catch (...) { return vdb_caught("vdb_select_kth_key_device"); }
 extern "C" int vdb_select_kth_key_ex_device(const uint64_t* d_keys, int32_t g, int64_t nq, int32_t list_len, int32_t rank, uint64_t* d_kth,
                                             int32_t* d_uncertain, void* stream) {
     if (!d_keys || !d_kth || g <= 0 || list_len <= 0 || rank <= 0 || nq <= 0 || (int64_t)g * list_len > 16384 || (int64_t)g * list_len < rank)

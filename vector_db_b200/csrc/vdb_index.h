@@ -167,6 +167,7 @@ int vdb_pq_phase2(vdb_index* x, const float* d_q, int64_t qb, int k, const uint6
 // vdb_api.cu helpers the builder needs
 int vdb_upload_rows_and_traversal_copy(vdb_index* x);
 // multi_gpu.cu
+int vdb_caught(const char* fn);      // catch (...) handler of the extern "C" entry points (vdb_api.cu)
 int vdb_multi_create(vdb_index* front);
 void vdb_multi_destroy(vdb_index* front);
 int vdb_multi_train(vdb_index* front, const float* samples, int64_t ns);
