@@ -2,6 +2,7 @@
 // fp32 reduction orders follow the reference implementations named in SURVEY.md §8a; explicit
 // __fmul_rn/__fadd_rn/__fmaf_rn keep nvcc from contracting or reassociating them.
 #pragma once
+#include <cstdint>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -174,18 +175,42 @@ __device__ __forceinline__ float rescore32(const float* __restrict__ base, int d
     for (int j = 0; j < 8; j++) l[j] = 0.0f;
     const int d8 = dim & ~7;
     const int nchunk = (dim + 31) >> 5;
+    // rows that are whole float4s (dim % 4 == 0, 16-byte aligned base): lane (g = lane / 8, j = lane % 8) loads columns 4j..4j+3 of rows
+    // 4i + g — one 128-bit load instruction covers 4 rows x 32 columns, so a chunk takes 8 loads (and 8 address computations) per lane
+    // instead of 32; the kernels around this are issue-bound, and address arithmetic was half of their instructions. The terms land in
+    // the same tile slots and are summed in the same order as on the scalar path below.
+    const bool vec4 = (dim & 3) == 0 && ((reinterpret_cast<uintptr_t>(base) & 15) == 0) && ((reinterpret_cast<uintptr_t>(sq) & 15) == 0);
+    const int g4 = lane >> 3, j4 = lane & 7;
     for (int c = 0; c < nchunk; c++) {
-        const int col = c * 32 + lane;
-        const bool cok = col < dim;
-        const float qv = cok ? sq[col] : 0.0f;
         __syncwarp();
+        if (vec4) {
+            const int col4 = c * 32 + 4 * j4;
+            const bool cok4 = col4 < dim;
+            const float4 q4 = cok4 ? *reinterpret_cast<const float4*>(sq + col4) : make_float4(0.f, 0.f, 0.f, 0.f);
+            float4 v[8];
 #pragma unroll
-        for (int r0 = 0; r0 < 32; r0 += 16) {
-            float v[16];
+            for (int i = 0; i < 8; i++)
+                v[i] = cok4 ? __ldg(reinterpret_cast<const float4*>(base + (size_t)rows[4 * i + g4] * dim + col4)) : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-            for (int r = 0; r < 16; r++) v[r] = cok ? __ldg(base + (size_t)rows[r0 + r] * dim + col) : 0.0f;
+            for (int i = 0; i < 8; i++) {
+                float* t = tile + (4 * i + g4) * 33 + 4 * j4;
+                t[0] = MODE == 2 ? __fmul_rn(v[i].x, q4.x) : __fsub_rn(q4.x, v[i].x);
+                t[1] = MODE == 2 ? __fmul_rn(v[i].y, q4.y) : __fsub_rn(q4.y, v[i].y);
+                t[2] = MODE == 2 ? __fmul_rn(v[i].z, q4.z) : __fsub_rn(q4.z, v[i].z);
+                t[3] = MODE == 2 ? __fmul_rn(v[i].w, q4.w) : __fsub_rn(q4.w, v[i].w);
+            }
+        } else {
+            const int col = c * 32 + lane;
+            const bool cok = col < dim;
+            const float qv = cok ? sq[col] : 0.0f;
 #pragma unroll
-            for (int r = 0; r < 16; r++) tile[(r0 + r) * 33 + lane] = MODE == 2 ? __fmul_rn(v[r], qv) : __fsub_rn(qv, v[r]);
+            for (int r0 = 0; r0 < 32; r0 += 16) {
+                float v[16];
+#pragma unroll
+                for (int r = 0; r < 16; r++) v[r] = cok ? __ldg(base + (size_t)rows[r0 + r] * dim + col) : 0.0f;
+#pragma unroll
+                for (int r = 0; r < 16; r++) tile[(r0 + r) * 33 + lane] = MODE == 2 ? __fmul_rn(v[r], qv) : __fsub_rn(qv, v[r]);
+            }
         }
         __syncwarp();
         const int lim = min(32, (MODE == 1 ? d8 : dim) - c * 32);
